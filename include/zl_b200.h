@@ -14,6 +14,7 @@
 #ifndef ZL_B200_H
 #define ZL_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -281,6 +282,12 @@ ZL_EXPORT int ZL_FN(passthrough_process)(zl_ctx* ctx, const zl_passthrough_param
 /* Peak scan of one period (lib/AudioLevels.cpp:365-382) + sum of squares, HOST buffers. */
 ZL_EXPORT int ZL_FN(levels_scan)(zl_ctx* ctx, const float* l, const float* r, int64_t n,
                                  int32_t* peak_a, int32_t* peak_b, double* sumsq_a, double* sumsq_b);
+
+/* ---- pinned host memory ------------------------------------------------------------- */
+/* Page-locked host buffers for callers that want full-rate PCIe transfers on zl_read_* / clip upload
+ * (the JACK port buffers of the reference, lib/SamplerSynth.cpp:132-133, are plain shared memory). */
+ZL_EXPORT int ZL_FN(host_alloc)(void** p, size_t bytes);
+ZL_EXPORT int ZL_FN(host_free)(void* p);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,897 @@
+// zl_api.cu — the C ABI of include/zl_b200.h over the sm_100a kernels (host side).
+//
+// This is the drop-in boundary for the hot path of libzl (lib/libzl.h:18-179 is the reference's own C
+// ABI; the functions here are the subset a cgo/ctypes/C++ host binds for the sampler render path).
+// There is NO CPU fallback: without a CUDA device zl_ctx_create returns ZL_ERR_NODEVICE and every
+// compute entry point needs a context.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "zl_device.cuh"
+
+namespace zl {
+cudaError_t launch_render(const RenderParams& P, cudaStream_t stream);
+size_t render_smem_bytes(int B, int V, int nframes);
+cudaError_t launch_thumb_level0(const float*, int, int, int, int, int8_t*, cudaStream_t);
+cudaError_t launch_thumb_bounds(double, double, double, int, int*, cudaStream_t);
+cudaError_t launch_thumb_pixels(const int8_t*, int, int, const int*, int, int8_t*, cudaStream_t);
+cudaError_t launch_thumb_pixels_direct(const float*, int, int, const int*, int, int8_t*, cudaStream_t);
+cudaError_t launch_thumb_raster(const int8_t*, int, int, float, uint8_t*, cudaStream_t);
+cudaError_t launch_passthrough(const zl_passthrough_params&, const float*, const float*, long long, float*, cudaStream_t);
+cudaError_t launch_levels(const float*, const float*, long long, int*, double*, cudaStream_t);
+cudaError_t launch_interleave(const float*, const float*, long long, long long, float*, cudaStream_t);
+}  // namespace zl
+
+using namespace zl;
+
+namespace {
+
+constexpr int kPadFrames = 8;
+
+// Host mirror of one ClipAudioSource + SamplerSynthSound.
+struct ClipHost {
+    bool live = false;
+    float* d_data = nullptr;
+    bool owned = false;
+    int nch = 0;
+    int length = 0;
+    double rate = 0.0;
+    // lib/ClipAudioSource.cpp:63-82,164-168
+    float startS = 0.0f, lengthS = -1.0f, lengthBeats = -1.0f, volume = 0.0f, pan = 0.0f;
+    float a = 0.0f, d = 0.1f, s = 1.0f, r = 0.05f;
+    int root = 60;
+    std::vector<double> slices;
+    // thumbnail
+    int8_t* d_thumb = nullptr;
+    int thumbSpt = 0, nThumb = 0;
+
+    float duration() const { return (float) ((double) length / rate); }
+    float startPosition(int slice) const {                                   // lib/ClipAudioSource.cpp:261-268
+        if (slice > -1 && slice < (int) slices.size()) return (float) (startS + (lengthS * slices[(size_t) slice]));
+        return startS;
+    }
+    float stopPosition(int slice) const {                                    // :270-277
+        if (slice > -1 && slice + 1 < (int) slices.size()) return (float) (startS + (lengthS * slices[(size_t) (slice + 1)]));
+        return startS + lengthS;
+    }
+    void evenSlices(int n) {                                                 // :495-528 from an empty list
+        slices.clear();
+        if (n <= 0) return;
+        double last = 0.0f;
+        double inc = (1.0f - last) / (n - 0);
+        double pos = last + inc;
+        slices.push_back(0.0f);
+        while ((int) slices.size() < n) { slices.push_back(pos); pos += inc; }
+    }
+};
+
+struct Meter { int peakA = 0, peakB = 0; float holdA = 0.0f, holdB = 0.0f; };
+
+struct Pending { int session, bus, block; uint64_t tick; zl_clip_command c; };
+
+uint64_t f2u64_sat(float x) {   // aarch64 fcvtzu semantics, as the device cvt.rzi.u64.f32
+    if (!(x > 0.0f)) return 0;
+    if (x >= 18446744073709551616.0f) return UINT64_MAX;
+    return (uint64_t) x;
+}
+
+float adsr_rate(float distance, float t, double sr) {                        // juce_ADSR.h:232-235
+    return t > 0.0f ? (float) (distance / (t * sr)) : -1.0f;
+}
+
+}  // namespace
+
+struct zl_ctx {
+    zl_config cfg{};
+    int device = 0;
+    cudaStream_t own = nullptr, stream = nullptr;
+    std::string err;
+    std::vector<ClipHost> clips;
+    int sliceStride = 0;                 // ints per clip in the slice-bounds table
+    // device tables
+    ClipDev* d_clips = nullptr;
+    int32_t* d_slice = nullptr;
+    VoiceDev* d_voices = nullptr;
+    BusDev* d_buses = nullptr;
+    CmdDev* d_cmds = nullptr; size_t cmdCap = 0;
+    zl_block_clock* d_clocks = nullptr;
+    double* d_pow2 = nullptr;
+    unsigned long long* d_counters = nullptr;   // [0] voice frames
+    int* d_bnd = nullptr; size_t bndCap = 0;
+    int8_t* d_px = nullptr; size_t pxCap = 0;
+    uint8_t* d_mask = nullptr; size_t maskCap = 0;
+    float* d_tmp = nullptr; size_t tmpCap = 0;  // standalone stages scratch
+    // host mirrors
+    std::vector<ClipDev> h_clips;
+    std::vector<int32_t> h_slice;
+    std::vector<BusDev> h_buses;
+    std::vector<Meter> meters;
+    std::vector<Pending> pending;
+    bool clipsDirty = true, busesDirty = true;
+    // pinned staging
+    void* h_stage = nullptr; size_t stageCap = 0;
+    zl_block_clock* h_clocks = nullptr;   // [2][max_blocks], double-buffered so render stays asynchronous
+    cudaEvent_t clkEv[2] = {nullptr, nullptr};
+    int clkSlot = 0;
+    // outputs of the last render
+    float* d_out[4] = {nullptr, nullptr, nullptr, nullptr};
+    float* d_master = nullptr;
+    int32_t* d_peaks = nullptr; double* d_sumsq = nullptr;
+    int64_t stride = 0; size_t lvlCap = 0;
+    int nblocks = 0, nframes = 0;
+    std::vector<int32_t> h_peaks; std::vector<double> h_sumsq; bool lvlCached = false;
+    uint64_t voiceFrames = 0, dropped = 0, launches = 0;
+    bool vfCached = true;
+
+    int nbus() const { return cfg.n_sessions * cfg.buses_per_session; }
+    int nvoices() const { return nbus() * cfg.voices_per_bus; }
+};
+
+namespace {
+
+int fail(zl_ctx* c, cudaError_t e, const char* what) {
+    if (c) {
+        char buf[256];
+        snprintf(buf, sizeof buf, "%s: %s", what, cudaGetErrorString(e));
+        c->err = buf;
+    }
+    return e == cudaErrorMemoryAllocation ? ZL_ERR_NOMEM : ZL_ERR_CUDA;
+}
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(ctx, e_, #call); } while (0)
+#define BIND() do { if (!ctx) return ZL_ERR_INVALID; cudaError_t e_ = cudaSetDevice(ctx->device); if (e_ != cudaSuccess) return fail(ctx, e_, "cudaSetDevice"); } while (0)
+
+int invalid(zl_ctx* c, const char* what) { if (c) c->err = what; return ZL_ERR_INVALID; }
+
+ClipHost* find_clip(zl_ctx* ctx, int id) {
+    if (!ctx || id < 0 || id >= (int) ctx->clips.size() || !ctx->clips[(size_t) id].live) return nullptr;
+    return &ctx->clips[(size_t) id];
+}
+
+int ensure_stage(zl_ctx* ctx, size_t bytes) {
+    if (bytes <= ctx->stageCap) return ZL_OK;
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    ctx->h_stage = nullptr; ctx->stageCap = 0;
+    const size_t cap = std::max(bytes, (size_t) 1 << 16);
+    CK(cudaMallocHost(&ctx->h_stage, cap));
+    ctx->stageCap = cap;
+    return ZL_OK;
+}
+
+template <typename T>
+int ensure_dev(zl_ctx* ctx, T** p, size_t* cap, size_t count) {
+    if (count <= *cap) return ZL_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr; *cap = 0;
+    CK(cudaMalloc((void**) p, count * sizeof(T)));
+    *cap = count;
+    return ZL_OK;
+}
+
+// Rebuild the device record + slice-bounds rows of one clip from its host parameters.
+void refresh_clip(zl_ctx* ctx, int id) {
+    ClipHost& c = ctx->clips[(size_t) id];
+    ClipDev& d = ctx->h_clips[(size_t) id];
+    memset(&d, 0, sizeof d);
+    d.valid = c.live ? 1 : 0;
+    if (!c.live) { ctx->clipsDirty = true; return; }
+    d.data = c.d_data; d.rate = c.rate; d.nch = c.nch; d.length = c.length;
+    d.srcLen = c.duration() * c.rate;                                        // lib/SamplerSynthVoice.cpp:120
+    d.relDen = c.r * c.rate;                                                 // juce_ADSR.h:138
+    d.lengthInBeats = c.lengthBeats;
+    d.volume = c.volume;
+    d.lPan = (float) (0.5 * (1.0 + c.pan));                                  // lib/SamplerSynthVoice.cpp:193-194
+    d.rPan = (float) (0.5 * (1.0 - c.pan));
+    d.sustain = c.s; d.release = c.r;
+    d.aRate = adsr_rate(1.0f, c.a, c.rate);                                  // juce_ADSR.h:237-239
+    d.dRate = adsr_rate(1.0f - c.s, c.d, c.rate);
+    d.rRate = adsr_rate(c.s, c.r, c.rate);
+    d.root = c.root;
+    d.beatAligned = truncf(c.lengthBeats) == c.lengthBeats ? 1 : 0;
+    d.lengthInTicks = f2u64_sat(c.lengthBeats * 96.0f);
+    d.sliceOff = id * ctx->sliceStride;
+    d.nSliceEntries = (int) c.slices.size() + 1;
+    int32_t* row = ctx->h_slice.data() + (size_t) d.sliceOff;
+    for (int e = 0; e < d.nSliceEntries; ++e) {                              // slice = e - 1
+        row[2 * e] = (int) (c.startPosition(e - 1) * c.rate);                // lib/SamplerSynthSound.cpp:96-99
+        row[2 * e + 1] = (int) (c.stopPosition(e - 1) * c.rate);             // :101-104
+    }
+    ctx->clipsDirty = true;
+}
+
+void fill_params(const ClipHost& c, zl_clip_params* p) {
+    memset(p, 0, sizeof *p);
+    p->start_s = c.startS; p->length_s = c.lengthS; p->length_beats = c.lengthBeats; p->pan = c.pan;
+    p->volume_abs = c.volume; p->attack = c.a; p->decay = c.d; p->sustain = c.s; p->release = c.r;
+    p->root_note = c.root; p->n_slices = (int) c.slices.size(); p->slice_pos = nullptr;
+}
+
+void default_clip_params(zl_ctx* ctx, ClipHost& c) {
+    c.startS = 0.0f; c.lengthBeats = -1.0f; c.pan = 0.0f; c.root = 60;
+    c.a = 0.0f; c.d = 0.1f; c.s = 1.0f; c.r = 0.05f;                         // lib/ClipAudioSource.cpp:164-168
+    c.lengthS = c.duration();                                                // :158
+    // tracktion master fader default (-3 dB) -> volumeAbsolute = decibelsToVolumeFaderPosition
+    // tracktion_engine/modules/tracktion_engine/model/edit/tracktion_Edit.cpp:826, utilities/tracktion_AudioUtilities.cpp:138-141
+    c.volume = std::exp((-3.0f - 6.0f) * (1.0f / 20.0f));
+    c.evenSlices(std::min(16, ctx->cfg.max_slices));                         // lib/ClipAudioSource.cpp:204
+}
+
+int new_clip_slot(zl_ctx* ctx) {
+    // ids are never reused (ClipAudioSource ids only grow, lib/ClipAudioSource.cpp:139-140)
+    if ((int) ctx->clips.size() >= ctx->cfg.max_clips) return -1;
+    ctx->clips.emplace_back();
+    return (int) ctx->clips.size() - 1;
+}
+
+}  // namespace
+
+// =============================================================================================
+extern "C" {
+
+int zl_config_default(zl_config* c) {
+    if (!c) return ZL_ERR_INVALID;
+    memset(c, 0, sizeof *c);
+    c->sample_rate = 48000.0; c->n_sessions = 1; c->buses_per_session = 12; c->voices_per_bus = 8;
+    c->max_clips = 256; c->max_slices = 16; c->max_frames = 1024; c->max_blocks = 64;
+    c->mode = ZL_MODE_Z; c->quirks = ZL_QUIRKS_FAITHFUL; c->outputs = ZL_OUT_ALL; c->device = 0;
+    return ZL_OK;
+}
+
+int zl_ctx_create(const zl_config* cfg, zl_ctx** out) {
+    if (!cfg || !out) return ZL_ERR_INVALID;
+    const int V = cfg->voices_per_bus;
+    if (cfg->n_sessions < 1 || cfg->buses_per_session < 1 || V < 1 || V > 32 || (V & (V - 1)) || cfg->sample_rate <= 0
+        || cfg->max_clips < 1 || cfg->max_slices < 0 || cfg->max_frames < 1 || cfg->max_blocks < 1)
+        return ZL_ERR_INVALID;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1 || cfg->device < 0 || cfg->device >= ndev) {
+        cudaGetLastError();
+        return ZL_ERR_NODEVICE;
+    }
+    zl_ctx* ctx = new zl_ctx;
+    ctx->cfg = *cfg;
+    ctx->device = cfg->device;
+    *out = nullptr;
+#define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { fprintf(stderr, "zl_ctx_create: %s: %s\n", #call, cudaGetErrorString(e_)); zl_ctx_destroy(ctx); return e_ == cudaErrorMemoryAllocation ? ZL_ERR_NOMEM : ZL_ERR_CUDA; } } while (0)
+    CKC(cudaSetDevice(ctx->device));
+    if (render_smem_bytes(cfg->buses_per_session, V, cfg->max_frames) > 227 * 1024) { delete ctx; return ZL_ERR_INVALID; }
+    CKC(cudaStreamCreateWithFlags(&ctx->own, cudaStreamNonBlocking));
+    ctx->stream = ctx->own;
+    ctx->sliceStride = 2 * (cfg->max_slices + 1);
+    ctx->h_clips.assign((size_t) cfg->max_clips, ClipDev{});
+    ctx->h_slice.assign((size_t) cfg->max_clips * ctx->sliceStride, 0);
+    CKC(cudaMalloc((void**) &ctx->d_clips, sizeof(ClipDev) * (size_t) cfg->max_clips));
+    CKC(cudaMalloc((void**) &ctx->d_slice, sizeof(int32_t) * ctx->h_slice.size()));
+    CKC(cudaMalloc((void**) &ctx->d_voices, sizeof(VoiceDev) * (size_t) ctx->nvoices()));
+    CKC(cudaMemsetAsync(ctx->d_voices, 0, sizeof(VoiceDev) * (size_t) ctx->nvoices(), ctx->stream));
+    {   // idle voices: sound = clip = -1
+        std::vector<VoiceDev> init((size_t) std::min(ctx->nvoices(), 4096));
+        memset(init.data(), 0, init.size() * sizeof(VoiceDev));
+        for (auto& v : init) { v.sound = -1; v.clip = -1; v.midiNote = -1; }
+        for (size_t o = 0; o < (size_t) ctx->nvoices(); o += init.size()) {
+            const size_t n = std::min(init.size(), (size_t) ctx->nvoices() - o);
+            CKC(cudaMemcpyAsync(ctx->d_voices + o, init.data(), n * sizeof(VoiceDev), cudaMemcpyHostToDevice, ctx->stream));
+        }
+        CKC(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->h_buses.assign((size_t) ctx->nbus(), BusDev{{1.0f, 1.0f, 1.0f, 0.0f, 0}, 1, 0, 0});   // lib/JackPassthrough.cpp:27-31
+    ctx->meters.assign((size_t) ctx->nbus(), Meter{});
+    CKC(cudaMalloc((void**) &ctx->d_buses, sizeof(BusDev) * (size_t) ctx->nbus()));
+    CKC(cudaMalloc((void**) &ctx->d_clocks, sizeof(zl_block_clock) * 2 * (size_t) cfg->max_blocks));
+    CKC(cudaMallocHost((void**) &ctx->h_clocks, sizeof(zl_block_clock) * 2 * (size_t) cfg->max_blocks));
+    CKC(cudaEventCreateWithFlags(&ctx->clkEv[0], cudaEventDisableTiming));
+    CKC(cudaEventCreateWithFlags(&ctx->clkEv[1], cudaEventDisableTiming));
+    CKC(cudaMalloc((void**) &ctx->d_counters, 8 * sizeof(unsigned long long)));
+    CKC(cudaMemset(ctx->d_counters, 0, 8 * sizeof(unsigned long long)));
+    {
+        double pow2[255];
+        for (int k = -127; k <= 127; ++k) pow2[k + 127] = std::pow(2.0, k / 12.0);   // lib/SamplerSynthVoice.cpp:115
+        CKC(cudaMalloc((void**) &ctx->d_pow2, sizeof pow2));
+        CKC(cudaMemcpy(ctx->d_pow2, pow2, sizeof pow2, cudaMemcpyHostToDevice));
+    }
+#undef CKC
+    *out = ctx;
+    return ZL_OK;
+}
+
+int zl_ctx_destroy(zl_ctx* ctx) {
+    if (!ctx) return ZL_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (ctx->own) cudaStreamSynchronize(ctx->own);
+    for (ClipHost& c : ctx->clips) { if (c.owned && c.d_data) cudaFree(c.d_data); if (c.d_thumb) cudaFree(c.d_thumb); }
+    void* frees[] = {ctx->d_clips, ctx->d_slice, ctx->d_voices, ctx->d_buses, ctx->d_cmds, ctx->d_clocks, ctx->d_pow2,
+                     ctx->d_counters, ctx->d_bnd, ctx->d_px, ctx->d_mask, ctx->d_tmp, ctx->d_out[0], ctx->d_out[1],
+                     ctx->d_out[2], ctx->d_out[3], ctx->d_master, ctx->d_peaks, ctx->d_sumsq};
+    for (void* p : frees) if (p) cudaFree(p);
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    if (ctx->h_clocks) cudaFreeHost(ctx->h_clocks);
+    for (cudaEvent_t e : ctx->clkEv) if (e) cudaEventDestroy(e);
+    if (ctx->own) cudaStreamDestroy(ctx->own);
+    delete ctx;
+    return ZL_OK;
+}
+
+const char* zl_last_error(zl_ctx* ctx) { return ctx ? ctx->err.c_str() : "null ctx"; }
+
+int zl_ctx_set_stream(zl_ctx* ctx, void* s) {
+    if (!ctx) return ZL_ERR_INVALID;
+    ctx->stream = s ? (cudaStream_t) s : ctx->own;
+    return ZL_OK;
+}
+
+int zl_sync(zl_ctx* ctx) {
+    BIND();
+    CK(cudaStreamSynchronize(ctx->stream));
+    return ZL_OK;
+}
+
+// ---- clips ------------------------------------------------------------------------------------
+static int finish_clip(zl_ctx* ctx, int id, int32_t* clip_id) {
+    ClipHost& c = ctx->clips[(size_t) id];
+    c.live = true;
+    default_clip_params(ctx, c);
+    refresh_clip(ctx, id);
+    *clip_id = id;
+    return ZL_OK;
+}
+
+int zl_clip_create_from_pcm(zl_ctx* ctx, const float* const* planar, int32_t nch, int64_t length, double rate, int32_t* clip_id) {
+    BIND();
+    if (!planar || nch < 1 || length < 1 || length > 2147483647LL - 8 || rate <= 0 || !clip_id) return invalid(ctx, "clip_create_from_pcm: bad argument");
+    const int id = new_clip_slot(ctx);
+    if (id < 0) { ctx->err = "clip table full"; return ZL_ERR_STATE; }
+    ClipHost& c = ctx->clips[(size_t) id];
+    c.nch = std::min(2, (int) nch); c.length = (int) length; c.rate = rate; c.owned = true;
+    const long long padded = length + kPadFrames;
+    cudaError_t e = cudaMalloc((void**) &c.d_data, sizeof(float) * (size_t) padded * c.nch);
+    if (e != cudaSuccess) { ctx->clips.pop_back(); return fail(ctx, e, "cudaMalloc(clip)"); }
+    // planar host PCM -> device scratch -> interleaved frames (device-side ingest)
+    float* d_planar = nullptr;
+    e = cudaMalloc((void**) &d_planar, sizeof(float) * (size_t) length * c.nch);
+    if (e != cudaSuccess) { cudaFree(c.d_data); ctx->clips.pop_back(); return fail(ctx, e, "cudaMalloc(clip scratch)"); }
+    for (int ch = 0; ch < c.nch && e == cudaSuccess; ++ch)
+        e = cudaMemcpyAsync(d_planar + (size_t) ch * length, planar[ch], sizeof(float) * (size_t) length, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = launch_interleave(d_planar, c.nch > 1 ? d_planar + length : nullptr, length, padded, c.d_data, ctx->stream);
+    ctx->launches++;
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_planar);
+    if (e != cudaSuccess) { cudaFree(c.d_data); ctx->clips.pop_back(); return fail(ctx, e, "clip upload"); }
+    return finish_clip(ctx, id, clip_id);
+}
+
+int zl_clip_create_from_device(zl_ctx* ctx, const void* d_interleaved, int32_t nch, int64_t length, double rate, int32_t* clip_id) {
+    BIND();
+    if (!d_interleaved || nch < 1 || nch > 2 || length < 1 || length > 2147483647LL - 8 || rate <= 0 || !clip_id)
+        return invalid(ctx, "clip_create_from_device: bad argument (the buffer must hold length + 8 zero-padded frames)");
+    const int id = new_clip_slot(ctx);
+    if (id < 0) { ctx->err = "clip table full"; return ZL_ERR_STATE; }
+    ClipHost& c = ctx->clips[(size_t) id];
+    c.nch = nch; c.length = (int) length; c.rate = rate; c.owned = false;
+    c.d_data = const_cast<float*>(static_cast<const float*>(d_interleaved));
+    return finish_clip(ctx, id, clip_id);
+}
+
+int zl_clip_destroy(zl_ctx* ctx, int32_t id) {
+    BIND();
+    ClipHost* c = find_clip(ctx, id);
+    if (!c) return invalid(ctx, "clip_destroy: unknown clip");
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (c->owned && c->d_data) cudaFree(c->d_data);
+    if (c->d_thumb) cudaFree(c->d_thumb);
+    c->d_data = nullptr; c->d_thumb = nullptr; c->live = false; c->nThumb = 0;
+    refresh_clip(ctx, id);
+    return ZL_OK;
+}
+
+int zl_clip_params_default(zl_ctx* ctx, int32_t id, zl_clip_params* p) {
+    ClipHost* c = find_clip(ctx, id);
+    if (!c || !p) return invalid(ctx, "clip_params_default: bad argument");
+    ClipHost d; d.length = c->length; d.rate = c->rate;
+    default_clip_params(ctx, d);
+    fill_params(d, p);
+    return ZL_OK;
+}
+
+int zl_clip_get_params(zl_ctx* ctx, int32_t id, zl_clip_params* p) {
+    ClipHost* c = find_clip(ctx, id);
+    if (!c || !p) return invalid(ctx, "clip_get_params: bad argument");
+    fill_params(*c, p);
+    return ZL_OK;
+}
+
+int zl_clip_set_params(zl_ctx* ctx, int32_t id, const zl_clip_params* p) {
+    ClipHost* c = find_clip(ctx, id);
+    if (!c || !p) return invalid(ctx, "clip_set_params: bad argument");
+    if (p->n_slices < 0 || p->n_slices > ctx->cfg.max_slices) return invalid(ctx, "clip_set_params: n_slices out of range");
+    c->startS = std::max(0.0f, p->start_s);                                  // lib/ClipAudioSource.cpp:256
+    c->lengthS = p->length_s < 0 ? c->duration() : p->length_s;
+    c->lengthBeats = p->length_beats; c->pan = p->pan; c->volume = p->volume_abs;
+    c->a = p->attack; c->d = p->decay; c->s = p->sustain; c->r = p->release; c->root = p->root_note;
+    if (p->slice_pos) c->slices.assign(p->slice_pos, p->slice_pos + p->n_slices);
+    else c->evenSlices(p->n_slices);
+    refresh_clip(ctx, id);
+    return ZL_OK;
+}
+
+int zl_clip_slice_bounds(zl_ctx* ctx, int32_t id, int32_t slice, int32_t* a, int32_t* b) {
+    ClipHost* c = find_clip(ctx, id);
+    if (!c) return invalid(ctx, "clip_slice_bounds: unknown clip");
+    if (a) *a = (int) (c->startPosition(slice) * c->rate);
+    if (b) *b = (int) (c->stopPosition(slice) * c->rate);
+    return ZL_OK;
+}
+
+// ---- commands ---------------------------------------------------------------------------------
+int zl_clip_command_default(zl_clip_command* c) {                            // lib/ClipCommand.h:14-31
+    if (!c) return ZL_ERR_INVALID;
+    memset(c, 0, sizeof *c);
+    c->clip = -1; c->midi_note = -1; c->midi_channel = -1; c->slice = -1;
+    return ZL_OK;
+}
+
+int zl_command(zl_ctx* ctx, int32_t session, int32_t block, uint64_t tick, const zl_clip_command* cmd) {
+    if (!ctx || !cmd || session < 0 || session >= ctx->cfg.n_sessions || block < 0) return invalid(ctx, "command: bad argument");
+    const int bus = cmd->midi_channel + 2;                                   // lib/SamplerSynth.cpp:330-331
+    if (!find_clip(ctx, cmd->clip) || bus < 0 || bus >= ctx->cfg.buses_per_session) { ctx->dropped++; return ZL_OK; }
+    ctx->pending.push_back(Pending{session, bus, block, tick, *cmd});
+    return ZL_OK;
+}
+
+int zl_bus_set_enabled(zl_ctx* ctx, int32_t s, int32_t b, int32_t en) {
+    if (!ctx || s < 0 || s >= ctx->cfg.n_sessions || b < 0 || b >= ctx->cfg.buses_per_session) return invalid(ctx, "bus_set_enabled: bad argument");
+    ctx->h_buses[(size_t) s * ctx->cfg.buses_per_session + b].enabled = en != 0;
+    ctx->busesDirty = true;
+    return ZL_OK;
+}
+
+int zl_passthrough_set(zl_ctx* ctx, int32_t s, int32_t b, const zl_passthrough_params* p) {
+    if (!ctx || !p || s < 0 || s >= ctx->cfg.n_sessions || b < 0 || b >= ctx->cfg.buses_per_session) return invalid(ctx, "passthrough_set: bad argument");
+    ctx->h_buses[(size_t) s * ctx->cfg.buses_per_session + b].pt = *p;
+    ctx->busesDirty = true;
+    return ZL_OK;
+}
+
+int zl_passthrough_get(zl_ctx* ctx, int32_t s, int32_t b, zl_passthrough_params* p) {
+    if (!ctx || !p || s < 0 || s >= ctx->cfg.n_sessions || b < 0 || b >= ctx->cfg.buses_per_session) return invalid(ctx, "passthrough_get: bad argument");
+    *p = ctx->h_buses[(size_t) s * ctx->cfg.buses_per_session + b].pt;
+    return ZL_OK;
+}
+
+// ---- the hot path -----------------------------------------------------------------------------
+static int ensure_outputs(zl_ctx* ctx, int nblocks, int nframes) {
+    const int64_t n = (int64_t) nblocks * nframes;
+    const size_t NB = (size_t) ctx->nbus();
+    if (n > ctx->stride) {
+        for (int w = 0; w < 4; ++w) { if (ctx->d_out[w]) cudaFree(ctx->d_out[w]); ctx->d_out[w] = nullptr; }
+        if (ctx->d_master) cudaFree(ctx->d_master);
+        ctx->d_master = nullptr;
+        ctx->stride = 0;
+        for (int w = 0; w < 4; ++w)
+            if (ctx->cfg.outputs & (ZL_OUT_RAW << w)) CK(cudaMalloc((void**) &ctx->d_out[w], sizeof(float) * NB * 2 * (size_t) n));
+        if (ctx->cfg.outputs & ZL_OUT_MASTER) CK(cudaMalloc((void**) &ctx->d_master, sizeof(float) * (size_t) ctx->cfg.n_sessions * 2 * (size_t) n));
+        ctx->stride = n;
+    }
+    const size_t lv = (size_t) nblocks * NB * 2;
+    if (lv > ctx->lvlCap) {
+        if (ctx->d_peaks) cudaFree(ctx->d_peaks);
+        if (ctx->d_sumsq) cudaFree(ctx->d_sumsq);
+        ctx->d_peaks = nullptr; ctx->d_sumsq = nullptr; ctx->lvlCap = 0;
+        if (ctx->cfg.outputs & ZL_OUT_LEVELS) CK(cudaMalloc((void**) &ctx->d_peaks, sizeof(int32_t) * lv));
+        if (ctx->cfg.outputs & ZL_OUT_RMS) CK(cudaMalloc((void**) &ctx->d_sumsq, sizeof(double) * lv));
+        ctx->lvlCap = lv;
+    }
+    return ZL_OK;
+}
+
+int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_clock* clocks) {
+    BIND();
+    if (nblocks < 1 || nframes < 1 || !clocks || nblocks > ctx->cfg.max_blocks || nframes > ctx->cfg.max_frames)
+        return invalid(ctx, "render: nblocks/nframes out of range or null clocks");
+    int rc = ensure_outputs(ctx, nblocks, nframes);
+    if (rc != ZL_OK) return rc;
+    cudaStream_t st = ctx->stream;
+    const size_t NB = (size_t) ctx->nbus();
+    // clip table
+    if (ctx->clipsDirty) {
+        CK(cudaMemcpyAsync(ctx->d_clips, ctx->h_clips.data(), sizeof(ClipDev) * ctx->h_clips.size(), cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(ctx->d_slice, ctx->h_slice.data(), sizeof(int32_t) * ctx->h_slice.size(), cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));   // pageable sources: keep the host mirrors free to change
+        ctx->clipsDirty = false;
+    }
+    // commands: stable by arrival, then by block; ring capacity 256 per bus per period (lib/SamplerSynth.cpp:32,332-334)
+    size_t nCmds = 0;
+    if (!ctx->pending.empty()) {
+        std::stable_sort(ctx->pending.begin(), ctx->pending.end(), [](const Pending& a, const Pending& b) { return a.block < b.block; });
+        std::vector<int> count(NB, 0), inBlock(NB, 0), last(NB, -1);
+        std::vector<char> keep(ctx->pending.size(), 0);
+        for (size_t i = 0; i < ctx->pending.size(); ++i) {
+            const Pending& p = ctx->pending[i];
+            const size_t gb = (size_t) p.session * ctx->cfg.buses_per_session + p.bus;
+            if (p.block >= nblocks) { ctx->dropped++; continue; }
+            if (last[gb] != p.block) { last[gb] = p.block; inBlock[gb] = 0; }
+            if (++inBlock[gb] > 256) { ctx->dropped++; continue; }
+            keep[i] = 1; count[gb]++; nCmds++;
+        }
+        rc = ensure_stage(ctx, sizeof(CmdDev) * nCmds);
+        if (rc != ZL_OK) return rc;
+        if (nCmds > ctx->cmdCap) { rc = ensure_dev(ctx, &ctx->d_cmds, &ctx->cmdCap, nCmds + 1024); if (rc != ZL_OK) return rc; }
+        std::vector<int> begin(NB, 0);
+        int acc = 0;
+        for (size_t gb = 0; gb < NB; ++gb) { begin[gb] = acc; ctx->h_buses[gb].cmdBegin = acc; ctx->h_buses[gb].cmdCount = count[gb]; acc += count[gb]; }
+        CmdDev* hc = static_cast<CmdDev*>(ctx->h_stage);
+        for (size_t i = 0; i < ctx->pending.size(); ++i) {
+            if (!keep[i]) continue;
+            const Pending& p = ctx->pending[i];
+            const size_t gb = (size_t) p.session * ctx->cfg.buses_per_session + p.bus;
+            CmdDev& d = hc[begin[gb]++];
+            memset(&d, 0, sizeof d);
+            d.c = p.c; d.block = p.block; d.tick = p.tick;
+        }
+        if (nCmds) {
+            CK(cudaMemcpyAsync(ctx->d_cmds, hc, sizeof(CmdDev) * nCmds, cudaMemcpyHostToDevice, st));
+            CK(cudaStreamSynchronize(st));   // the staging buffer may be reused by the next call
+        }
+        ctx->pending.clear();
+        ctx->busesDirty = true;
+    }
+    if (ctx->busesDirty) {
+        CK(cudaMemcpyAsync(ctx->d_buses, ctx->h_buses.data(), sizeof(BusDev) * NB, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+        for (BusDev& b : ctx->h_buses) { b.cmdBegin = 0; b.cmdCount = 0; }
+        ctx->busesDirty = false;
+    }
+    const int slot = ctx->clkSlot; ctx->clkSlot ^= 1;
+    zl_block_clock* hck = ctx->h_clocks + (size_t) slot * ctx->cfg.max_blocks;
+    zl_block_clock* dck = ctx->d_clocks + (size_t) slot * ctx->cfg.max_blocks;
+    CK(cudaEventSynchronize(ctx->clkEv[slot]));   // the render that used this slot two calls ago is done
+    memcpy(hck, clocks, sizeof(zl_block_clock) * (size_t) nblocks);
+    CK(cudaMemcpyAsync(dck, hck, sizeof(zl_block_clock) * (size_t) nblocks, cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(ctx->d_counters, 0, sizeof(unsigned long long), st));
+
+    RenderParams P{};
+    P.voices = ctx->d_voices; P.clips = ctx->d_clips; P.sliceBounds = ctx->d_slice; P.buses = ctx->d_buses;
+    P.cmds = ctx->d_cmds; P.clocks = dck; P.pow2 = ctx->d_pow2;
+    for (int w = 0; w < 4; ++w) P.out[w] = ctx->d_out[w];
+    P.master = ctx->d_master; P.peaks = ctx->d_peaks; P.sumsq = ctx->d_sumsq;
+    P.voiceFrames = ctx->d_counters;
+    P.outRate = ctx->cfg.sample_rate; P.stride = ctx->stride;
+    P.nSessions = ctx->cfg.n_sessions; P.B = ctx->cfg.buses_per_session; P.V = ctx->cfg.voices_per_bus;
+    P.nClips = (int) ctx->clips.size();
+    P.nblocks = nblocks; P.nframes = nframes; P.mode = ctx->cfg.mode; P.quirks = ctx->cfg.quirks;
+    CK(launch_render(P, st));
+    ctx->launches++;
+    ctx->nblocks = nblocks; ctx->nframes = nframes;
+    ctx->lvlCached = false; ctx->vfCached = false;
+    CK(cudaEventRecord(ctx->clkEv[slot], st));
+    return ZL_OK;
+}
+
+// ---- outputs of the last render ---------------------------------------------------------------
+static int d2h(zl_ctx* ctx, void* dst, const void* src, size_t bytes) {
+    CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return ZL_OK;
+}
+
+int zl_read_bus(zl_ctx* ctx, int32_t s, int32_t b, int32_t which, float* l, float* r, int64_t n) {
+    BIND();
+    if (which < 0 || which > 3 || s < 0 || s >= ctx->cfg.n_sessions || b < 0 || b >= ctx->cfg.buses_per_session) return invalid(ctx, "read_bus: bad argument");
+    const int64_t N = (int64_t) ctx->nblocks * ctx->nframes;
+    if (n != N || !ctx->d_out[which]) { ctx->err = "read_bus: size mismatch or output plane not enabled"; return ZL_ERR_STATE; }
+    const size_t gb = (size_t) s * ctx->cfg.buses_per_session + b;
+    int rc = ZL_OK;
+    if (l) rc = d2h(ctx, l, ctx->d_out[which] + gb * 2 * ctx->stride, sizeof(float) * (size_t) N);
+    if (rc == ZL_OK && r) rc = d2h(ctx, r, ctx->d_out[which] + (gb * 2 + 1) * ctx->stride, sizeof(float) * (size_t) N);
+    if (rc != ZL_OK) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return ZL_OK;
+}
+
+int zl_read_master(zl_ctx* ctx, int32_t s, float* l, float* r, int64_t n) {
+    BIND();
+    if (s < 0 || s >= ctx->cfg.n_sessions) return invalid(ctx, "read_master: bad session");
+    const int64_t N = (int64_t) ctx->nblocks * ctx->nframes;
+    if (n != N || !ctx->d_master) { ctx->err = "read_master: size mismatch or master not enabled"; return ZL_ERR_STATE; }
+    int rc = ZL_OK;
+    if (l) rc = d2h(ctx, l, ctx->d_master + (size_t) s * 2 * ctx->stride, sizeof(float) * (size_t) N);
+    if (rc == ZL_OK && r) rc = d2h(ctx, r, ctx->d_master + ((size_t) s * 2 + 1) * ctx->stride, sizeof(float) * (size_t) N);
+    if (rc != ZL_OK) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return ZL_OK;
+}
+
+int zl_read_master_all(zl_ctx* ctx, float* out, int64_t n) {
+    BIND();
+    if (!out) return invalid(ctx, "read_master_all: null");
+    const int64_t N = (int64_t) ctx->nblocks * ctx->nframes;
+    if (n != N || !ctx->d_master) { ctx->err = "read_master_all: size mismatch or master not enabled"; return ZL_ERR_STATE; }
+    const size_t rows = (size_t) ctx->cfg.n_sessions * 2;
+    CK(cudaMemcpy2DAsync(out, sizeof(float) * (size_t) N, ctx->d_master, sizeof(float) * (size_t) ctx->stride,
+                         sizeof(float) * (size_t) N, rows, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return ZL_OK;
+}
+
+int zl_device_bus_ptr(zl_ctx* ctx, int32_t which, float** p, int64_t* stride) {
+    if (!ctx || which < 0 || which > 3 || !p) return invalid(ctx, "device_bus_ptr: bad argument");
+    if (!ctx->d_out[which]) { ctx->err = "device_bus_ptr: plane not enabled or nothing rendered yet"; return ZL_ERR_STATE; }
+    *p = ctx->d_out[which];
+    if (stride) *stride = ctx->stride;
+    return ZL_OK;
+}
+
+int zl_device_master_ptr(zl_ctx* ctx, float** p, int64_t* stride) {
+    if (!ctx || !p) return invalid(ctx, "device_master_ptr: bad argument");
+    if (!ctx->d_master) { ctx->err = "device_master_ptr: master not enabled or nothing rendered yet"; return ZL_ERR_STATE; }
+    *p = ctx->d_master;
+    if (stride) *stride = ctx->stride;
+    return ZL_OK;
+}
+
+static int cache_levels(zl_ctx* ctx) {
+    if (ctx->lvlCached) return ZL_OK;
+    const size_t lv = (size_t) ctx->nblocks * ctx->nbus() * 2;
+    ctx->h_peaks.assign(lv, 0); ctx->h_sumsq.assign(lv, 0.0);
+    if (lv) {
+        if (ctx->d_peaks) CK(cudaMemcpyAsync(ctx->h_peaks.data(), ctx->d_peaks, sizeof(int32_t) * lv, cudaMemcpyDeviceToHost, ctx->stream));
+        if (ctx->d_sumsq) CK(cudaMemcpyAsync(ctx->h_sumsq.data(), ctx->d_sumsq, sizeof(double) * lv, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->lvlCached = true;
+    return ZL_OK;
+}
+
+int zl_read_block_levels(zl_ctx* ctx, int32_t* peaks, double* sumsq) {
+    BIND();
+    int rc = cache_levels(ctx);
+    if (rc != ZL_OK) return rc;
+    if (peaks) memcpy(peaks, ctx->h_peaks.data(), ctx->h_peaks.size() * sizeof(int32_t));
+    if (sumsq) memcpy(sumsq, ctx->h_sumsq.data(), ctx->h_sumsq.size() * sizeof(double));
+    return ZL_OK;
+}
+
+static float convert_to_dbfs(float raw) {                                    // lib/AudioLevels.cpp:330-341
+    if (raw <= 0) return -200;
+    const float v = 20 * log10f(raw);
+    return v < -200 ? -200 : v;
+}
+static float add_float(const float& a, const float& b) {                     // lib/AudioLevels.cpp:234-236
+    return 10 * log10f(pow(10, a / 10) + pow(10, b / 10));
+}
+
+// AudioLevels::timerCallback for one channel  lib/AudioLevels.cpp:347-412.  The per-sample scan ran on
+// the device inside the render kernel; this is the 20 Hz control-rate tail (decay, dB, hold).
+int zl_levels_tick(zl_ctx* ctx, int32_t s, int32_t b, int32_t block, int32_t isPlayback, zl_levels* out) {
+    BIND();
+    if (!out || s < 0 || s >= ctx->cfg.n_sessions || b < 0 || b >= ctx->cfg.buses_per_session || block >= ctx->nblocks)
+        return invalid(ctx, "levels_tick: bad argument");
+    int rc = cache_levels(ctx);
+    if (rc != ZL_OK) return rc;
+    static const float intToFloatMultiplier{0.00000152587};                  // :349
+    const size_t gb = (size_t) s * ctx->cfg.buses_per_session + b;
+    Meter& m = ctx->meters[gb];
+    m.peakA = std::max(0, m.peakA - 10000);                                  // :359-360
+    m.peakB = std::max(0, m.peakB - 10000);
+    float rmsA = 0, rmsB = 0;
+    if (block >= 0) {
+        const size_t i = ((size_t) block * ctx->nbus() + gb) * 2;
+        m.peakA = std::max(m.peakA, ctx->h_peaks[i]);
+        m.peakB = std::max(m.peakB, ctx->h_peaks[i + 1]);
+        rmsA = (float) std::sqrt(ctx->h_sumsq[i] / ctx->nframes);            // juce_AudioSampleBuffer.h:1095
+        rmsB = (float) std::sqrt(ctx->h_sumsq[i + 1] / ctx->nframes);
+    }
+    const float peakA{m.peakA * intToFloatMultiplier}, peakB{m.peakB * intToFloatMultiplier};   // :385
+    const float dbA{convert_to_dbfs(peakA)}, dbB{convert_to_dbfs(peakB)};
+    memset(out, 0, sizeof *out);
+    out->peak_a = m.peakA; out->peak_b = m.peakB;
+    out->db_a = dbA <= -200 ? -200 : dbA; out->db_b = dbB <= -200 ? -200 : dbB;
+    out->db_sum = isPlayback ? add_float(dbA, dbB) : add_float(out->db_a, out->db_b);   // :394 / :406
+    if (isPlayback) {                                                        // :395-396
+        m.holdA = (peakA >= m.holdA) ? peakA : m.holdA * 0.9f;
+        m.holdB = (peakB >= m.holdB) ? peakB : m.holdB * 0.9f;
+    }
+    out->hold_a = m.holdA; out->hold_b = m.holdB; out->rms_a = rmsA; out->rms_b = rmsB;
+    return ZL_OK;
+}
+
+static int fetch_voices(zl_ctx* ctx, std::vector<VoiceDev>& hv) {
+    hv.resize((size_t) ctx->nvoices());
+    CK(cudaMemcpyAsync(hv.data(), ctx->d_voices, sizeof(VoiceDev) * hv.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return ZL_OK;
+}
+
+int zl_read_voices(zl_ctx* ctx, zl_voice_info* out, int32_t cap) {
+    BIND();
+    if (!out || cap < ctx->nvoices()) return invalid(ctx, "read_voices: capacity too small");
+    std::vector<VoiceDev> hv;
+    int rc = fetch_voices(ctx, hv);
+    if (rc != ZL_OK) return rc;
+    for (size_t i = 0; i < hv.size(); ++i) {
+        const VoiceDev& v = hv[i];
+        zl_voice_info& o = out[i];
+        memset(&o, 0, sizeof o);
+        o.position = v.p; o.pitch_ratio = v.ratio; o.envelope = v.env; o.gain = v.lgain;
+        o.pos_gain = v.posGain; o.pos_progress = v.posProgress; o.playing = (v.flags & VF_PLAYING) ? 1 : 0;
+        o.clip = v.sound; o.adsr_state = v.adsrState; o.midi_note = v.midiNote;
+        o.slice = v.cmd.slice; o.looping = v.cmd.looping;
+    }
+    return ZL_OK;
+}
+
+int zl_read_positions(zl_ctx* ctx, int32_t clip, float* gains, float* progress, int32_t cap, int32_t* count) {
+    BIND();
+    if (!count) return invalid(ctx, "read_positions: null count");
+    std::vector<VoiceDev> hv;
+    int rc = fetch_voices(ctx, hv);
+    if (rc != ZL_OK) return rc;
+    int n = 0;
+    for (const VoiceDev& v : hv)
+        if ((v.flags & VF_PLAYING) && v.clip == clip && (v.flags & VF_HAS_POSID) && n < cap && n < 32) {   // POSITION_COUNT 32
+            if (gains) gains[n] = v.posGain;
+            if (progress) progress[n] = v.posProgress;
+            ++n;
+        }
+    *count = n;
+    return ZL_OK;
+}
+
+int zl_last_voice_frames(zl_ctx* ctx, uint64_t* vf) {
+    BIND();
+    if (!vf) return invalid(ctx, "last_voice_frames: null");
+    if (!ctx->vfCached) {
+        unsigned long long v = 0;
+        CK(cudaMemcpyAsync(&v, ctx->d_counters, sizeof v, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        ctx->voiceFrames = v; ctx->vfCached = true;
+    }
+    *vf = ctx->voiceFrames;
+    return ZL_OK;
+}
+
+int zl_dropped_commands(zl_ctx* ctx, uint64_t* n) { if (!ctx || !n) return ZL_ERR_INVALID; *n = ctx->dropped; return ZL_OK; }
+int zl_launch_count(zl_ctx* ctx, uint64_t* n) { if (!ctx || !n) return ZL_ERR_INVALID; *n = ctx->launches; return ZL_OK; }
+
+// ---- WaveFormItem / juce::AudioThumbnail ------------------------------------------------------
+static int build_thumb(zl_ctx* ctx, ClipHost* c, int spt) {
+    if (c->d_thumb) { cudaFree(c->d_thumb); c->d_thumb = nullptr; }
+    c->thumbSpt = spt;
+    c->nThumb = 1 + c->length / spt;                                         // juce_AudioThumbnail.cpp:666-670
+    const size_t bytes = (size_t) c->nch * c->nThumb * 2;
+    CK(cudaMalloc((void**) &c->d_thumb, bytes));
+    CK(cudaMemsetAsync(c->d_thumb, 0, bytes, ctx->stream));                  // MinMaxValue() = (0,0)
+    CK(launch_thumb_level0(c->d_data, c->nch, spt, c->length / spt, c->nThumb, c->d_thumb, ctx->stream));
+    ctx->launches++;
+    return ZL_OK;
+}
+
+int zl_thumb_build(zl_ctx* ctx, int32_t id, int32_t spt) {
+    BIND();
+    ClipHost* c = find_clip(ctx, id);
+    if (!c || spt < 1) return invalid(ctx, "thumb_build: bad argument");
+    return build_thumb(ctx, c, spt);
+}
+
+int zl_thumb_size(zl_ctx* ctx, int32_t id, int32_t* n, int32_t* nch) {
+    ClipHost* c = find_clip(ctx, id);
+    if (!c || !c->nThumb) { if (ctx) ctx->err = "thumb_size: no thumbnail built"; return ZL_ERR_STATE; }
+    if (n) *n = c->nThumb;
+    if (nch) *nch = c->nch;
+    return ZL_OK;
+}
+
+int zl_thumb_read_level0(zl_ctx* ctx, int32_t id, int8_t* out) {
+    BIND();
+    ClipHost* c = find_clip(ctx, id);
+    if (!c || !c->nThumb || !out) { ctx->err = "thumb_read_level0: no thumbnail built"; return ZL_ERR_STATE; }
+    CK(cudaMemcpyAsync(out, c->d_thumb, (size_t) c->nch * c->nThumb * 2, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return ZL_OK;
+}
+
+// CachedWindow::refillCache on the device; leaves [nch][width][2] in ctx->d_px.  Returns ZL_ERR_INVALID
+// where the reference returns false (juce_AudioThumbnail.cpp:436-441).
+static int refill_cache(zl_ctx* ctx, ClipHost* c, double t0, double t1, int width) {
+    const double rate = c->rate;
+    if (width <= 0) return ZL_ERR_INVALID;
+    const double dt = (t1 - t0) / width;
+    if (dt <= 0.0 || rate <= 0) return ZL_ERR_INVALID;
+    if (!c->nThumb) { int rc = build_thumb(ctx, c, 512); if (rc != ZL_OK) return rc; }   // lib/WaveFormItem.cpp:22
+    int rc = ensure_dev(ctx, &ctx->d_bnd, &ctx->bndCap, (size_t) width + 1);
+    if (rc != ZL_OK) return rc;
+    const size_t pxBytes = (size_t) c->nch * width * 2;
+    rc = ensure_dev(ctx, &ctx->d_px, &ctx->pxCap, pxBytes);
+    if (rc != ZL_OK) return rc;
+    CK(cudaMemsetAsync(ctx->d_px, 0, pxBytes, ctx->stream));
+    if (dt * rate <= c->thumbSpt) {                                          // :459-492
+        CK(launch_thumb_bounds(t0, dt, rate, width, ctx->d_bnd, ctx->stream));
+        CK(launch_thumb_pixels_direct(c->d_data, c->nch, c->length, ctx->d_bnd, width, ctx->d_px, ctx->stream));
+    } else {                                                                 // :493-518
+        CK(launch_thumb_bounds(t0, dt, rate / (double) c->thumbSpt, width, ctx->d_bnd, ctx->stream));
+        CK(launch_thumb_pixels(c->d_thumb, c->nThumb, c->nch, ctx->d_bnd, width, ctx->d_px, ctx->stream));
+    }
+    ctx->launches += 2;
+    return ZL_OK;
+}
+
+int zl_thumb_pixels(zl_ctx* ctx, int32_t id, double t0, double t1, int32_t width, int8_t* out) {
+    BIND();
+    ClipHost* c = find_clip(ctx, id);
+    if (!c || !out) return invalid(ctx, "thumb_pixels: bad argument");
+    int rc = refill_cache(ctx, c, t0, t1, width);
+    if (rc != ZL_OK) return rc;
+    CK(cudaMemcpyAsync(out, ctx->d_px, (size_t) c->nch * width * 2, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return ZL_OK;
+}
+
+int zl_thumb_raster(zl_ctx* ctx, int32_t id, int32_t channel, double t0, double t1, int32_t width, int32_t height,
+                    float zoom, uint8_t* mask) {
+    BIND();
+    ClipHost* c = find_clip(ctx, id);
+    if (!c || !mask || height < 1 || channel < 0 || channel >= c->nch) return invalid(ctx, "thumb_raster: bad argument");
+    int rc = refill_cache(ctx, c, t0, t1, width);
+    if (rc != ZL_OK) return rc;
+    const size_t bytes = (size_t) width * height;
+    rc = ensure_dev(ctx, &ctx->d_mask, &ctx->maskCap, bytes);
+    if (rc != ZL_OK) return rc;
+    CK(cudaMemsetAsync(ctx->d_mask, 0, bytes, ctx->stream));
+    CK(launch_thumb_raster(ctx->d_px + (size_t) channel * width * 2, width, height, zoom, ctx->d_mask, ctx->stream));
+    ctx->launches++;
+    CK(cudaMemcpyAsync(mask, ctx->d_mask, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return ZL_OK;
+}
+
+// ---- standalone stages over caller-owned HOST buffers -------------------------------------------
+int zl_passthrough_process(zl_ctx* ctx, const zl_passthrough_params* p, const float* l, const float* r, int64_t n, float* out6) {
+    BIND();
+    if (!p || !l || !r || !out6 || n < 0) return invalid(ctx, "passthrough_process: bad argument");
+    if (n == 0) return ZL_OK;
+    int rc = ensure_dev(ctx, &ctx->d_tmp, &ctx->tmpCap, (size_t) n * 8);
+    if (rc != ZL_OK) return rc;
+    float* dl = ctx->d_tmp; float* dr = dl + n; float* d6 = dr + n;
+    CK(cudaMemcpyAsync(dl, l, sizeof(float) * (size_t) n, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(dr, r, sizeof(float) * (size_t) n, cudaMemcpyHostToDevice, ctx->stream));
+    CK(launch_passthrough(*p, dl, dr, n, d6, ctx->stream));
+    ctx->launches++;
+    CK(cudaMemcpyAsync(out6, d6, sizeof(float) * (size_t) n * 6, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return ZL_OK;
+}
+
+int zl_levels_scan(zl_ctx* ctx, const float* l, const float* r, int64_t n, int32_t* pa, int32_t* pb, double* sa, double* sb) {
+    BIND();
+    if (!l || !r || n < 0) return invalid(ctx, "levels_scan: bad argument");
+    int rc = ensure_dev(ctx, &ctx->d_tmp, &ctx->tmpCap, (size_t) n * 2 + 16);
+    if (rc != ZL_OK) return rc;
+    float* dl = ctx->d_tmp + 16; float* dr = dl + n;
+    double* dsq = reinterpret_cast<double*>(ctx->d_tmp);        // [0..1] sums, then 2 int peaks
+    int* dpk = reinterpret_cast<int*>(ctx->d_tmp + 4);
+    CK(cudaMemsetAsync(ctx->d_tmp, 0, 16 * sizeof(float), ctx->stream));
+    if (n) {
+        CK(cudaMemcpyAsync(dl, l, sizeof(float) * (size_t) n, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(dr, r, sizeof(float) * (size_t) n, cudaMemcpyHostToDevice, ctx->stream));
+        CK(launch_levels(dl, dr, n, dpk, dsq, ctx->stream));
+        ctx->launches++;
+    }
+    struct { double sq[2]; int pk[2]; } res;
+    CK(cudaMemcpyAsync(&res, ctx->d_tmp, sizeof res, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (pa) *pa = res.pk[0];
+    if (pb) *pb = res.pk[1];
+    if (sa) *sa = res.sq[0];
+    if (sb) *sb = res.sq[1];
+    return ZL_OK;
+}
+
+// ---- pinned host memory for callers that want full-rate transfers -----------------------------
+int zl_host_alloc(void** p, size_t bytes) {
+    if (!p) return ZL_ERR_INVALID;
+    return cudaMallocHost(p, bytes) == cudaSuccess ? ZL_OK : ZL_ERR_NOMEM;
+}
+int zl_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? ZL_OK : ZL_ERR_CUDA; }
+
+}  // extern "C"

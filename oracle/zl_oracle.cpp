@@ -995,6 +995,9 @@ int zlo_levels_scan(zl_ctx*, const float* l, const float* r, int64_t n, int32_t*
     return ZL_OK;
 }
 
+int zlo_host_alloc(void** p, size_t bytes) { if (!p) return ZL_ERR_INVALID; *p = malloc(bytes ? bytes : 1); return *p ? ZL_OK : ZL_ERR_NOMEM; }
+int zlo_host_free(void* p) { free(p); return ZL_OK; }
+
 // ---- oracle-only probes used to pin the restatement against the real JUCE objects --------------
 // ADSR run: noteOn, n_on samples, noteOff, remaining samples. renote != 0: noteOff before every
 // sample of the release part (libzl Q3, lib/SamplerSynthVoice.cpp:253-256).
