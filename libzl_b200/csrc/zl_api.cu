@@ -257,7 +257,6 @@ int zl_ctx_create(const zl_config* cfg, zl_ctx** out) {
     *out = nullptr;
 #define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { fprintf(stderr, "zl_ctx_create: %s: %s\n", #call, cudaGetErrorString(e_)); zl_ctx_destroy(ctx); return e_ == cudaErrorMemoryAllocation ? ZL_ERR_NOMEM : ZL_ERR_CUDA; } } while (0)
     CKC(cudaSetDevice(ctx->device));
-    if (render_smem_bytes(cfg->buses_per_session, V, cfg->max_frames) > 227 * 1024) { delete ctx; return ZL_ERR_INVALID; }
     CKC(cudaStreamCreateWithFlags(&ctx->own, cudaStreamNonBlocking));
     ctx->stream = ctx->own;
     ctx->sliceStride = 2 * (cfg->max_slices + 1);
@@ -490,6 +489,8 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     BIND();
     if (nblocks < 1 || nframes < 1 || !clocks || nblocks > ctx->cfg.max_blocks || nframes > ctx->cfg.max_frames)
         return invalid(ctx, "render: nblocks/nframes out of range or null clocks");
+    if (render_smem_bytes(ctx->cfg.buses_per_session, ctx->cfg.voices_per_bus, nframes) > 227 * 1024)
+        return invalid(ctx, "render: buses x voices x nframes does not fit the 227 KB shared memory of one CTA");
     int rc = ensure_outputs(ctx, nblocks, nframes);
     if (rc != ZL_OK) return rc;
     cudaStream_t st = ctx->stream;

@@ -31,8 +31,6 @@ def test_level0_bit_exact(product, oracle, n, nch, spt):
 
 
 def test_level0_golden_read_max_levels(product, golden, oracle):
-    from test_oracle_golden import test_thumbnail_level0_matches_read_max_levels_golden as check
-    check.__wrapped__(product, golden) if hasattr(check, "__wrapped__") else None
     pcm = golden["rml_pcm"]
     e = Engine(lib=product); c = e.add_clip(pcm); e.thumb_build(c, 512); got = e.thumb_level0(c); e.close()
     e = Engine(lib=oracle); c = e.add_clip(pcm); e.thumb_build(c, 512); exp = e.thumb_level0(c); e.close()
