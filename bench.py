@@ -1,0 +1,415 @@
+#!/usr/bin/env python
+"""bench.py — voice-frames/s of the batched sampler voice render (BASELINE.json metric) on N B200s.
+
+Workload ("cfg2x": BASELINE.json configs[1] shape batched as configs[4]): S independent sessions per GPU,
+each a 128-voice polyphonic SamplerSynth (16 buses x 8 voices) over its own 8 stereo 48 kHz 1 s clips
+(noise / sweep), random pitch ratios 0.5-2.0, ADSR, M/S pan, clip volume, JackPassthrough, per-bus peak
+meters, mixed to one stereo master per session.  One step = one launch of `blocks` JACK periods of 512
+frames for every session, preceded by that step's command stream (one-shot re-triggers).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+N > 1 runs under torchrun (one rank per GPU); sessions are sharded by rank with no data-path collective
+(weak scaling: sessions per GPU fixed), unless --span-mix adds the NCCL stereo-bus reduce.
+Prints ONE JSON line (rank 0).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FRAMES = 512
+BUSES, VOICES, CLIPS_PER_SESSION, CLIP_FRAMES = 16, 8, 8, 48000
+RATE = 48000.0
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--sessions", type=int, default=4096, help="sessions per GPU")
+    ap.add_argument("--blocks", type=int, default=16, help="512-frame periods per step")
+    ap.add_argument("--cpu-sessions", type=int, default=0, help="sessions of the CPU sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--span-mix", type=int, default=0, help="G>1: groups of G GPUs share one mix -> NCCL reduce of the masters")
+    ap.add_argument("--seed", type=int, default=5)
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# workload description (shared by the CUDA arm and the CPU arms so both render the same thing)
+class Workload:
+    def __init__(self, sessions, blocks, steps_total, seed, rank=0):
+        self.S, self.blocks, self.steps_total = sessions, blocks, steps_total
+        rng = np.random.default_rng(seed * 1000 + rank)
+        nclips = sessions * CLIPS_PER_SESSION
+        self.clip_seed = seed * 7919 + rank
+        self.clip_params = dict(
+            attack=rng.uniform(0, 0.05, nclips).astype(np.float32), decay=rng.uniform(0, 0.2, nclips).astype(np.float32),
+            sustain=rng.uniform(0.3, 1.0, nclips).astype(np.float32), release=rng.uniform(0.01, 0.2, nclips).astype(np.float32),
+            pan=rng.uniform(-1, 1, nclips).astype(np.float32), volume=rng.uniform(0.5, 1.0, nclips).astype(np.float32))
+        from libzl_b200.engine import default_commands
+        nv = sessions * BUSES * VOICES
+        # initial polyphony: 6 looping + 2 one-shot voices per bus
+        c = default_commands(nv)
+        sess = np.repeat(np.arange(sessions, dtype=np.int32), BUSES * VOICES)
+        bus = np.tile(np.repeat(np.arange(BUSES, dtype=np.int32), VOICES), sessions)
+        slot = np.tile(np.arange(VOICES, dtype=np.int32), sessions * BUSES)
+        c["clip"] = sess * CLIPS_PER_SESSION + rng.integers(0, CLIPS_PER_SESSION, nv)
+        c["midi_channel"] = bus - 2
+        c["midi_note"] = 60 + rng.integers(-12, 13, nv)
+        c["start_playback"] = 1
+        c["looping"] = (slot < 6).astype(np.int32)
+        c["change_volume"] = 1
+        c["volume"] = rng.uniform(0.25, 1.0, nv).astype(np.float32)
+        # distinct notes per bus slot so commands stay non-equivalent (ClipCommand::equivalentTo)
+        self.init = (sess, np.zeros(nv, np.int32), np.zeros(nv, np.uint64), c)
+        # per-step command stream: one one-shot start per bus at a random period of the step; it takes the
+        # first free voice of the bus or is dropped when all 8 are busy (lib/SamplerSynth.cpp:204-215)
+        self.steps = []
+        nb = sessions * BUSES
+        for _ in range(steps_total):
+            k = default_commands(nb)
+            s2 = np.repeat(np.arange(sessions, dtype=np.int32), BUSES)
+            k["clip"] = s2 * CLIPS_PER_SESSION + rng.integers(0, CLIPS_PER_SESSION, nb)
+            k["midi_channel"] = np.tile(np.arange(BUSES, dtype=np.int32), sessions) - 2
+            k["midi_note"] = 60 + rng.integers(-12, 13, nb)
+            k["start_playback"] = 1
+            k["change_volume"] = 1
+            k["volume"] = rng.uniform(0.25, 1.0, nb).astype(np.float32)
+            self.steps.append((s2, rng.integers(0, blocks, nb).astype(np.int32), np.zeros(nb, np.uint64), k))
+
+    def clip_pcm_numpy(self, first, count):
+        """Interleaved [count, CLIP_FRAMES + 8, 2] float32 (zero padded) for clips first..first+count-1."""
+        out = np.zeros((count, CLIP_FRAMES + 8, 2), np.float32)
+        t = np.arange(CLIP_FRAMES) / RATE
+        ph = 2 * np.pi * (20.0 * t + (20000.0 - 20.0) * t * t / 2.0)
+        for i in range(count):
+            cid = first + i
+            if cid % 2 == 0:
+                out[i, :CLIP_FRAMES] = np.random.default_rng(self.clip_seed * 100003 + cid).uniform(-1, 1, (CLIP_FRAMES, 2))
+            else:
+                g = 0.4 + 0.4 * ((cid * 2654435761) % 1000) / 1000.0
+                out[i, :CLIP_FRAMES, 0] = g * np.sin(ph)
+                out[i, :CLIP_FRAMES, 1] = g * np.sin(ph + np.pi / 2)
+        return out
+
+    def configure_clip(self, e, cid):
+        p = self.clip_params
+        e.set_clip_params(cid, attack=float(p["attack"][cid]), decay=float(p["decay"][cid]), sustain=float(p["sustain"][cid]),
+                          release=float(p["release"][cid]), pan=float(p["pan"][cid]), volume_abs=float(p["volume"][cid]),
+                          length_beats=1.5, root_note=60)
+
+
+def clocks_for(e, step, blocks):
+    return e.make_clocks(blocks, FRAMES, RATE, first_block=step * blocks)
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        busy = [x for x in sm if x > 0]
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, torch copy read+write)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def run_cuda(args, rank, world, local_rank):
+    import torch
+    import libzl_b200
+    from libzl_b200 import _capi as K
+    from libzl_b200.engine import Engine
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    S, NB = args.sessions, args.blocks
+    total_steps = args.warmup + args.steps
+    wl = Workload(S, NB, total_steps * 2 + 2, args.seed, rank)
+    outputs = K.ZL_OUT_RAW | K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS
+    e = Engine(lib=libzl_b200.load(), n_sessions=S, buses_per_session=BUSES, voices_per_bus=VOICES,
+               max_clips=S * CLIPS_PER_SESSION, max_frames=FRAMES, max_blocks=NB, outputs=outputs, device=local_rank)
+    stream = torch.cuda.current_stream()
+    e.set_stream(stream.cuda_stream)
+    # clips: generated on the device (synthetic noise / sweep), adopted zero-copy by the clip table
+    nclips = S * CLIPS_PER_SESSION
+    g = torch.Generator(device=dev); g.manual_seed(wl.clip_seed)
+    pcm = torch.zeros((nclips, CLIP_FRAMES + 8, 2), dtype=torch.float32, device=dev)
+    chunk = 1024
+    t = torch.arange(CLIP_FRAMES, device=dev, dtype=torch.float64) / RATE
+    ph = 2 * torch.pi * (20.0 * t + (20000.0 - 20.0) * t * t / 2.0)
+    sweep = torch.stack([torch.sin(ph), torch.sin(ph + torch.pi / 2)], dim=1).to(torch.float32)
+    for c0 in range(0, nclips, chunk):
+        n = min(chunk, nclips - c0)
+        blk = pcm[c0:c0 + n, :CLIP_FRAMES]
+        blk.uniform_(-1.0, 1.0, generator=g)
+        gains = (0.4 + 0.4 * torch.rand(n, generator=g, device=dev)).view(n, 1, 1)
+        odd = (torch.arange(c0, c0 + n, device=dev) % 2 == 1).view(n, 1, 1)
+        blk.copy_(torch.where(odd, gains * sweep.unsqueeze(0), blk))
+    torch.cuda.synchronize()
+    base = pcm.data_ptr()
+    clip_bytes = (CLIP_FRAMES + 8) * 2 * 4
+    for cid in range(nclips):
+        got = e.add_clip_device(base + cid * clip_bytes, 2, CLIP_FRAMES, RATE)
+        assert got == cid
+        wl.configure_clip(e, cid)
+    e.command_batch(*wl.init)
+
+    n_per_step = NB * FRAMES
+    out_bytes = (S * BUSES * 2 * n_per_step * 4) + (S * 2 * n_per_step * 4) + NB * S * BUSES * 2 * 4
+    state_bytes = 2 * S * BUSES * VOICES * 224
+
+    def step(i, read_back=None):
+        e.command_batch(*wl.steps[i])
+        e.render(NB, FRAMES, clocks_for(e, i, NB))
+        if read_back is not None:
+            e._chk(e.lib.read_master_all(e.ctx, read_back, n_per_step), "read_master_all")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing ("value") -----------------------------------------------------
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    launches0 = e.launch_count()
+    vf0, src0 = e.total_counters()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    ev[0].record(stream)
+    for k in range(args.steps):
+        step(args.warmup + k)
+        ev[k + 1].record(stream)
+    barrier()
+    elapsed_ms = ev[0].elapsed_time(ev[-1])
+    kernel_launches = e.launch_count() - launches0
+    clocks = sampler.stop() if sampler else None
+    step_ms = [ev[k].elapsed_time(ev[k + 1]) for k in range(args.steps)]
+    vf1, src1 = e.total_counters()
+    timed_vf, timed_src = vf1 - vf0, src1 - src0
+    # ---- e2e: same steps through the C ABI with host buffers (commands from pinned host memory H2D, master D2H)
+    hostp = C.c_void_p()
+    e._chk(e.lib.host_alloc(C.byref(hostp), S * 2 * n_per_step * 4), "host_alloc")
+    host_master = C.cast(hostp, C.POINTER(C.c_float))
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        step(total_steps + k, read_back=host_master)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    e2e_vf = e.total_counters()[0] - vf1
+    h2d = wl.steps[0][3].nbytes + wl.steps[0][0].nbytes * 2 + wl.steps[0][2].nbytes + NB * 40
+    d2h = S * 2 * n_per_step * 4
+    e.lib.host_free(hostp)
+    return dict(e=e, elapsed_ms=elapsed_ms, step_ms=step_ms, timed_vf=timed_vf, timed_src=timed_src, launches=kernel_launches,
+                clocks=clocks, e2e_s=e2e_s, e2e_vf=e2e_vf, h2d=h2d, d2h=d2h, out_bytes=out_bytes, state_bytes=state_bytes,
+                dist=dist, dev=dev, wl=wl, keep=pcm)
+
+
+# ------------------------------------------------------------------------------------------------
+def run_cpu(args, sessions, steps, warmup, threads=None):
+    """The reference's CPU implementation of the path (oracle port of lib/SamplerSynthVoice.cpp::process etc.,
+    built like the reference with contraction on: oracle/liboracle_fma.so) on a bounded sample of the workload."""
+    from oracle import loader
+    from libzl_b200 import _capi as K
+    from libzl_b200.engine import Engine
+    lib = loader.load_oracle(fma=True)
+    threads = threads or os.cpu_count() or 1
+    NB = args.blocks
+    wl = Workload(sessions, NB, warmup + steps + 1, args.seed, rank=0)
+    outputs = K.ZL_OUT_RAW | K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS
+    e = Engine(lib=lib, n_sessions=sessions, buses_per_session=BUSES, voices_per_bus=VOICES,
+               max_clips=sessions * CLIPS_PER_SESSION, max_frames=FRAMES, max_blocks=NB, outputs=outputs)
+    lib.dll.zlo_set_threads(e.ctx, threads)
+    nclips = sessions * CLIPS_PER_SESSION
+    for c0 in range(0, nclips, 64):
+        n = min(64, nclips - c0)
+        pcm = wl.clip_pcm_numpy(c0, n)
+        for i in range(n):
+            cid = e.add_clip(np.ascontiguousarray(pcm[i, :CLIP_FRAMES].T), RATE)
+            wl.configure_clip(e, cid)
+    e.command_batch(*wl.init)
+    for i in range(warmup):
+        e.command_batch(*wl.steps[i]); e.render(NB, FRAMES, clocks_for(e, i, NB))
+    vf0 = e.total_counters()[0]
+    t0 = time.perf_counter()
+    for k in range(steps):
+        e.command_batch(*wl.steps[warmup + k]); e.render(NB, FRAMES, clocks_for(e, warmup + k, NB))
+    dt = time.perf_counter() - t0
+    vf = e.total_counters()[0] - vf0
+    e.close()
+    return vf, dt, threads
+
+
+def cpu_sample_size(args):
+    if args.cpu_sessions:
+        return args.cpu_sessions
+    return max(16, 16 * (os.cpu_count() or 1))
+
+
+def latency_probe(local_rank, iters=1500):
+    """p50 of one 512-frame period of ONE 128-voice session (configs[1]): host call -> master on the host."""
+    import libzl_b200
+    from libzl_b200 import _capi as K
+    from libzl_b200.engine import Engine
+    wl = Workload(1, 1, iters + 20, 99, 0)
+    e = Engine(lib=libzl_b200.load(), n_sessions=1, buses_per_session=BUSES, voices_per_bus=VOICES, max_clips=8,
+               max_frames=FRAMES, max_blocks=1, outputs=K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS, device=local_rank)
+    pcm = wl.clip_pcm_numpy(0, CLIPS_PER_SESSION)
+    for i in range(CLIPS_PER_SESSION):
+        cid = e.add_clip(np.ascontiguousarray(pcm[i, :CLIP_FRAMES].T), RATE)
+        wl.configure_clip(e, cid)
+    e.command_batch(*wl.init)
+    hostp = C.c_void_p()
+    e._chk(e.lib.host_alloc(C.byref(hostp), 2 * FRAMES * 4), "host_alloc")
+    hp = C.cast(hostp, C.POINTER(C.c_float))
+    ts = []
+    for i in range(iters + 20):
+        clk = clocks_for(e, i, 1)
+        t0 = time.perf_counter()
+        e.lib.render(e.ctx, 1, FRAMES, clk)
+        e.lib.read_master_all(e.ctx, hp, FRAMES)
+        ts.append(time.perf_counter() - t0)
+    e.lib.host_free(hostp)
+    e.close()
+    ts = sorted(ts[20:])
+    return {"p50_us": round(1e6 * ts[len(ts) // 2], 2), "p99_us": round(1e6 * ts[int(len(ts) * 0.99)], 2),
+            "what": "one 512-frame period of one 128-voice session: zl_render + zl_read_master_all to pinned host"}
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus > 1 and world == 1 and args.impl == "ours":
+        # convenience: relaunch under torchrun (the driver launches torchrun itself)
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    workload = (f"cfg2x{args.sessions}: {args.sessions} independent 128-voice polyphonic sessions per GPU (BASELINE configs[1] "
+                f"shape = 16 buses x 8 voices, batched as configs[4] offline render), {args.blocks} periods x {FRAMES} frames per step")
+    config = {"workload": workload, "sessions_per_gpu": args.sessions, "buses": BUSES, "voices_per_bus": VOICES,
+              "frames": FRAMES, "blocks_per_step": args.blocks, "mode": "Z (libzl process(), quirks faithful)",
+              "outputs": "raw bus + master + peak meters", "parallelism": f"sessions sharded over {args.gpus} GPU(s), no collective",
+              "l2": "inputs (clip PCM 3 MB/session) larger than L2; no flush needed"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        sessions = cpu_sample_size(args)
+        vf, dt, th = run_cpu(args, sessions, args.steps, min(args.warmup, 1))
+        v = vf / dt
+        line = {"impl": "reference", "metric": "voice_frames_per_s", "value": v, "unit": "voice-frames/s", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32 (f64 positions)", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": v, "unit": "voice-frames/s", "cores": th, "kind": "port",
+                                 "sample": f"{sessions} sessions x {args.blocks} periods x {FRAMES} frames per step, {args.steps} steps "
+                                           "(oracle port built -O3 -mfma -ffp-contract=fast; libzl itself needs Qt5/JACK and cannot be built here)"},
+                "e2e": {"value": v, "unit": "voice-frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line), flush=True)
+        return
+
+    import torch
+    r = run_cuda(args, rank, world, local_rank)
+    elapsed = torch.tensor([r["elapsed_ms"], r["e2e_s"] * 1e3], dtype=torch.float64, device=r["dev"])
+    counts = torch.tensor([r["timed_vf"], r["e2e_vf"], r["timed_src"]], dtype=torch.float64, device=r["dev"])
+    if r["dist"] is not None:
+        r["dist"].all_reduce(elapsed, op=r["dist"].ReduceOp.MAX)
+        r["dist"].all_reduce(counts, op=r["dist"].ReduceOp.SUM)
+    el_ms, e2e_ms = elapsed.tolist()
+    vf, e2e_vf, src = counts.tolist()
+    if rank == 0:
+        peak, peak_src = peaks()
+        # roofline of the dominant kernel (render_kernel): algorithmic bytes per launch / mean launch duration
+        alg_bytes = (4.0 * r["timed_src"] / args.steps) + r["out_bytes"] + r["state_bytes"]
+        mean_ms = statistics.mean(r["step_ms"])
+        ach = alg_bytes / (mean_ms * 1e-3) / 1e9
+        line = {"metric": "voice_frames_per_s", "value": vf / (el_ms * 1e-3), "unit": "voice-frames/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": el_ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32 (f64 positions)", "data": "synthetic", "config": config,
+                "clocks": r["clocks"], "gpu_launches": r["launches"],
+                "e2e": {"value": e2e_vf / (e2e_ms * 1e-3), "unit": "voice-frames/s", "h2d_bytes_per_step": r["h2d"],
+                        "d2h_bytes_per_step": r["d2h"], "what": "zl_command_batch + zl_render + zl_read_master_all (master of every session to pinned host)"},
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                             "peak_source": peak_src, "frac_of_nominal_8TBs": ach / 8000.0,
+                             "algorithmic_bytes_per_launch": alg_bytes, "bytes_per_voice_frame": alg_bytes / (r["timed_vf"] / args.steps),
+                             "kernel": "zl::render_kernel", "kernel_ms": mean_ms},
+                "voice_frames_per_step": vf / args.steps / world}
+        if world == 1 and not args.no_latency:
+            try:
+                line["latency"] = latency_probe(local_rank)
+            except Exception as ex:   # noqa: BLE001
+                line["latency"] = {"error": str(ex)}
+        if world == 1 and not args.no_cpu_baseline:
+            sessions = cpu_sample_size(args)
+            cvf, cdt, th = run_cpu(args, sessions, 2, 1)
+            line["cpu_baseline"] = {"value": cvf / cdt, "unit": "voice-frames/s", "cores": th, "kind": "port",
+                                    "sample": f"{sessions} sessions x {args.blocks} periods x {FRAMES} frames, 2 steps (oracle port, -O3 -mfma contraction on)"}
+        print(json.dumps(line), flush=True)
+    if r["dist"] is not None:
+        r["dist"].barrier()
+        r["dist"].destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -204,6 +204,9 @@ ZL_EXPORT int ZL_FN(clip_slice_bounds)(zl_ctx* ctx, int32_t clip_id, int32_t sli
  * (SamplerChannel::process drain, lib/SamplerSynth.cpp:118-122; handleCommand :187-230). */
 ZL_EXPORT int ZL_FN(command)(zl_ctx* ctx, int32_t session, int32_t block_offset,
                              uint64_t timestamp_tick, const zl_clip_command* cmd);
+/* n commands at once (the per-period command stream of an offline render): arrays of length n. */
+ZL_EXPORT int ZL_FN(command_batch)(zl_ctx* ctx, int32_t n, const int32_t* sessions, const int32_t* block_offsets,
+                                   const uint64_t* timestamp_ticks, const zl_clip_command* cmds);
 ZL_EXPORT int ZL_FN(clip_command_default)(zl_clip_command* cmd);
 /* SamplerSynth::setChannelEnabled  lib/SamplerSynth.cpp:343-351 (bus = channel + 2). */
 ZL_EXPORT int ZL_FN(bus_set_enabled)(zl_ctx* ctx, int32_t session, int32_t bus, int32_t enabled);
@@ -247,6 +250,12 @@ ZL_EXPORT int ZL_FN(read_voices)(zl_ctx* ctx, zl_voice_info* out, int32_t capaci
  * (lib/ClipAudioSourcePositionsModel.cpp:160-173, before hysteresis) + up to 32 (gain,progress). */
 ZL_EXPORT int ZL_FN(read_positions)(zl_ctx* ctx, int32_t clip_id, float* gains, float* progress,
                                     int32_t capacity, int32_t* count);
+/* Source PCM floats spanned by the voices of the last render (unique samples incl. the +1 tap, summed per
+ * voice per block; the algorithmic read traffic of SURVEY.md 8d is 4x this). */
+ZL_EXPORT int ZL_FN(last_source_floats)(zl_ctx* ctx, uint64_t* n);
+/* Running totals over the life of the context (voice-frames, source floats): lets a caller account a
+ * sequence of asynchronous renders with one read. */
+ZL_EXPORT int ZL_FN(total_counters)(zl_ctx* ctx, uint64_t* voice_frames, uint64_t* source_floats);
 /* Number of voice-frames rendered by the last render (active voices x frames actually produced). */
 ZL_EXPORT int ZL_FN(last_voice_frames)(zl_ctx* ctx, uint64_t* voice_frames);
 /* Number of commands dropped (ring overflow lib/SamplerSynth.cpp:332-334 / unknown clip :330). */

@@ -81,6 +81,9 @@ SIGNATURES = {
     "clip_slice_bounds": (C.c_int, [_ctx, C.c_int32, C.c_int32, _P(C.c_int32), _P(C.c_int32)]),
     "command": (C.c_int, [_ctx, C.c_int32, C.c_int32, C.c_uint64, _P(zl_clip_command)]),
     "clip_command_default": (C.c_int, [_P(zl_clip_command)]),
+    "command_batch": (C.c_int, [_ctx, C.c_int32, _P(C.c_int32), _P(C.c_int32), _P(C.c_uint64), _P(zl_clip_command)]),
+    "last_source_floats": (C.c_int, [_ctx, _P(C.c_uint64)]),
+    "total_counters": (C.c_int, [_ctx, _P(C.c_uint64), _P(C.c_uint64)]),
     "bus_set_enabled": (C.c_int, [_ctx, C.c_int32, C.c_int32, C.c_int32]),
     "passthrough_set": (C.c_int, [_ctx, C.c_int32, C.c_int32, _P(zl_passthrough_params)]),
     "passthrough_get": (C.c_int, [_ctx, C.c_int32, C.c_int32, _P(zl_passthrough_params)]),

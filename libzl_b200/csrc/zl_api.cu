@@ -439,6 +439,13 @@ int zl_command(zl_ctx* ctx, int32_t session, int32_t block, uint64_t tick, const
     return ZL_OK;
 }
 
+int zl_command_batch(zl_ctx* ctx, int32_t n, const int32_t* s, const int32_t* b, const uint64_t* t, const zl_clip_command* c) {
+    if (!ctx || n < 0 || (n && (!s || !b || !t || !c))) return invalid(ctx, "command_batch: bad argument");
+    ctx->pending.reserve(ctx->pending.size() + (size_t) n);
+    for (int i = 0; i < n; ++i) { int rc = zl_command(ctx, s[i], b[i], t[i], &c[i]); if (rc != ZL_OK) return rc; }
+    return ZL_OK;
+}
+
 int zl_bus_set_enabled(zl_ctx* ctx, int32_t s, int32_t b, int32_t en) {
     if (!ctx || s < 0 || s >= ctx->cfg.n_sessions || b < 0 || b >= ctx->cfg.buses_per_session) return invalid(ctx, "bus_set_enabled: bad argument");
     ctx->h_buses[(size_t) s * ctx->cfg.buses_per_session + b].enabled = en != 0;
@@ -550,7 +557,7 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     CK(cudaEventSynchronize(ctx->clkEv[slot]));   // the render that used this slot two calls ago is done
     memcpy(hck, clocks, sizeof(zl_block_clock) * (size_t) nblocks);
     CK(cudaMemcpyAsync(dck, hck, sizeof(zl_block_clock) * (size_t) nblocks, cudaMemcpyHostToDevice, st));
-    CK(cudaMemsetAsync(ctx->d_counters, 0, sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(ctx->d_counters, 0, 2 * sizeof(unsigned long long), st));
 
     RenderParams P{};
     P.voices = ctx->d_voices; P.clips = ctx->d_clips; P.sliceBounds = ctx->d_slice; P.buses = ctx->d_buses;
@@ -749,6 +756,26 @@ int zl_last_voice_frames(zl_ctx* ctx, uint64_t* vf) {
         ctx->voiceFrames = v; ctx->vfCached = true;
     }
     *vf = ctx->voiceFrames;
+    return ZL_OK;
+}
+
+int zl_total_counters(zl_ctx* ctx, uint64_t* vf, uint64_t* sf) {
+    BIND();
+    unsigned long long v[2] = {0, 0};
+    CK(cudaMemcpyAsync(v, ctx->d_counters + 2, sizeof v, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (vf) *vf = v[0];
+    if (sf) *sf = v[1];
+    return ZL_OK;
+}
+
+int zl_last_source_floats(zl_ctx* ctx, uint64_t* n) {
+    BIND();
+    if (!n) return invalid(ctx, "last_source_floats: null");
+    unsigned long long v = 0;
+    CK(cudaMemcpyAsync(&v, ctx->d_counters + 1, sizeof v, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    *n = v;
     return ZL_OK;
 }
 

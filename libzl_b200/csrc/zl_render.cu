@@ -22,7 +22,7 @@ struct __align__(16) RenderSmem {
     double sqPart[kWarps][2];
     int vpeak[32];                 // per-voice block peak (float bits, >= 0)
     VoiceBlock vb[32];
-    unsigned long long vframes;
+    unsigned long long vframes, vsrc;
 };
 
 __device__ __forceinline__ float lerp_gain_z(float a, float b, float ia, float alpha, float g, float env, float vol, bool q1) {
@@ -69,7 +69,7 @@ render_kernel(const RenderParams P) {
         const uint32_t* src = reinterpret_cast<const uint32_t*>(P.voices + (size_t) s * NV);
         uint32_t* dst = reinterpret_cast<uint32_t*>(sv);
         for (int i = tid; i < (int) (sizeof(VoiceDev) * NV / 4); i += kThreads) dst[i] = src[i];
-        if (tid == 0) sm->vframes = 0;
+        if (tid == 0) { sm->vframes = 0; sm->vsrc = 0; }
     }
     __syncthreads();
 
@@ -96,7 +96,7 @@ render_kernel(const RenderParams P) {
                 if (lane < V) {
                     VoiceDev v = bv[lane];                                    // registers for the walk
                     VoiceBlock vb;
-                    vb.nrend = 0; vb.data = nullptr; vb.nch = 0; vb.sampleDuration = 0;
+                    vb.nrend = 0; vb.srcFloats = 0; vb.data = nullptr; vb.nch = 0; vb.sampleDuration = 0;
                     vb.lgain = vb.rgain = vb.vol = vb.lPan = vb.rPan = 0.0f;
                     int n = 0;
                     if (bus.enabled && (v.flags & VF_PLAYING)) {              // :136-140
@@ -106,7 +106,7 @@ render_kernel(const RenderParams P) {
                     bv[lane] = v;
                     sm->vb[lane] = vb;
                     sm->vpeak[lane] = 0;
-                    if (n) atomicAdd(&sm->vframes, (unsigned long long) n);
+                    if (n) { atomicAdd(&sm->vframes, (unsigned long long) n); atomicAdd(&sm->vsrc, (unsigned long long) vb.srcFloats); }
                 }
             }
             __syncthreads();
@@ -255,7 +255,10 @@ render_kernel(const RenderParams P) {
         uint32_t* dst = reinterpret_cast<uint32_t*>(P.voices + (size_t) s * NV);
         const uint32_t* src = reinterpret_cast<const uint32_t*>(sv);
         for (int i = tid; i < (int) (sizeof(VoiceDev) * NV / 4); i += kThreads) dst[i] = src[i];
-        if (tid == 0 && sm->vframes) atomicAdd(P.voiceFrames, sm->vframes);
+        if (tid == 0 && sm->vframes) {
+            atomicAdd(P.voiceFrames, sm->vframes); atomicAdd(P.voiceFrames + 1, sm->vsrc);
+            atomicAdd(P.voiceFrames + 2, sm->vframes); atomicAdd(P.voiceFrames + 3, sm->vsrc);
+        }
     }
 }
 

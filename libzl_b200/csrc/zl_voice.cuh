@@ -51,13 +51,14 @@ struct VoiceBlock {
     int32_t sampleDuration;   // length - 1                              lib/SamplerSynthVoice.cpp:191
     float lgain, rgain, vol, lPan, rPan;
     int32_t nrend;            // frames rendered in this block (loop ran for frames [0, nrend))
+    uint32_t srcFloats;       // source floats spanned in this block (unique samples incl. the +1 tap)
 };
 
 // One block of SamplerSynthVoice::process (lib/SamplerSynthVoice.cpp:174-270), frame by frame, writing
 // the per-frame (pos, alpha, env) the gather consumes.  Returns frames rendered.
 __device__ inline int voice_walk_z(VoiceDev& v, const RenderParams& P, const zl_block_clock& ck, int nframes,
                                    int* tpos, float* talpha, float* tenv, VoiceBlock& vb) {
-    vb.nrend = 0;
+    vb.nrend = 0; vb.srcFloats = 0;
     if (v.sound < 0) return 0;
     const ClipDev& snd = P.clips[v.sound];
     if (!(snd.length > 0 && (v.flags & VF_HAS_CMD))) return 0;
@@ -78,8 +79,12 @@ __device__ inline int voice_walk_z(VoiceDev& v, const RenderParams& P, const zl_
     vb.lgain = v.lgain; vb.rgain = v.rgain; vb.vol = c.volume; vb.lPan = c.lPan; vb.rPan = c.rPan;
     bool releaseArmed = false;
     int rendered = 0;
+    int spanStart = (int) v.p, lastPos = spanStart;
+    uint32_t span = 0;
     for (int frame = 0; frame < nframes; ++frame) {
         const int pos = (int) v.p;
+        if (pos < lastPos) { span += (uint32_t) (lastPos + 2 - spanStart); spanStart = pos; }   // loop wrap
+        lastPos = pos;
         tpos[frame] = pos;
         talpha[frame] = __double2float_rn(__dsub_rn(v.p, (double) pos));
         tenv[frame] = adsr_next(v);
@@ -104,6 +109,8 @@ __device__ inline int voice_walk_z(VoiceDev& v, const RenderParams& P, const zl_
         }
         if (v.adsrState == kIdle) { voice_stop(v, false); break; }
     }
+    span += (uint32_t) (lastPos + 2 - spanStart);
+    vb.srcFloats = span * (uint32_t) snd.nch;
     vb.nrend = rendered;
     return rendered;
 }
@@ -111,15 +118,18 @@ __device__ inline int voice_walk_z(VoiceDev& v, const RenderParams& P, const zl_
 // One block of juce::SamplerVoice::renderNextBlock (juce_Sampler.cpp:117-163).
 __device__ inline int voice_walk_j(VoiceDev& v, const RenderParams& P, int nframes,
                                    int* tpos, float* talpha, float* tenv, VoiceBlock& vb) {
-    vb.nrend = 0;
+    vb.nrend = 0; vb.srcFloats = 0;
     if (v.sound < 0) return 0;
     const ClipDev& snd = P.clips[v.sound];
     vb.data = snd.data; vb.nch = snd.nch; vb.sampleDuration = snd.length - 1;
     vb.lgain = v.lgain; vb.rgain = v.rgain; vb.vol = 1.0f; vb.lPan = 0.0f; vb.rPan = 0.0f;
     const double lenD = (double) snd.length;
     int rendered = 0;
+    const int spanStart = (int) v.p;
+    int lastPos = spanStart;
     for (int frame = 0; frame < nframes; ++frame) {
         const int pos = (int) v.p;
+        lastPos = pos;
         tpos[frame] = pos;
         talpha[frame] = __double2float_rn(__dsub_rn(v.p, (double) pos));
         tenv[frame] = adsr_next(v);
@@ -127,6 +137,7 @@ __device__ inline int voice_walk_j(VoiceDev& v, const RenderParams& P, int nfram
         v.p = __dadd_rn(v.p, v.ratio);
         if (v.p > lenD) { voice_stop(v, false); break; }
     }
+    vb.srcFloats = (uint32_t) (lastPos + 2 - spanStart) * (uint32_t) snd.nch;
     vb.nrend = rendered;
     return rendered;
 }

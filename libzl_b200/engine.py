@@ -18,6 +18,18 @@ def _fp(a):
     return a.ctypes.data_as(C.POINTER(C.c_float))
 
 
+# numpy view of zl_clip_command (include/zl_b200.h; lib/ClipCommand.h:11-31)
+CMD_DTYPE = np.dtype([(n, np.float32 if t is C.c_float else np.int32) for n, t in K.zl_clip_command._fields_])
+assert CMD_DTYPE.itemsize == C.sizeof(K.zl_clip_command)
+
+
+def default_commands(n):
+    """n commands with ClipCommand's defaults (clip -1, note -1, channel -1, slice -1)."""
+    c = np.zeros(n, CMD_DTYPE)
+    c["clip"] = -1; c["midi_note"] = -1; c["midi_channel"] = -1; c["slice"] = -1
+    return c
+
+
 class Engine:
     def __init__(self, lib=None, **cfg):
         if lib is None:
@@ -122,6 +134,20 @@ class Engine:
             setattr(c, k, v)
         self._chk(self.lib.command(self.ctx, session, block, tick, C.byref(c)), "command")
 
+    def command_batch(self, sessions, blocks, ticks, cmds):
+        """sessions/blocks: int32 arrays, ticks: uint64 array, cmds: numpy structured array with the layout
+        of zl_clip_command (see CMD_DTYPE) — one call for a whole period's command stream."""
+        n = len(sessions)
+        sessions = np.ascontiguousarray(sessions, np.int32)
+        blocks = np.ascontiguousarray(blocks, np.int32)
+        ticks = np.ascontiguousarray(ticks, np.uint64)
+        cmds = np.ascontiguousarray(cmds, CMD_DTYPE)
+        assert len(blocks) == n and len(ticks) == n and len(cmds) == n
+        self._chk(self.lib.command_batch(self.ctx, n, sessions.ctypes.data_as(C.POINTER(C.c_int32)),
+                                         blocks.ctypes.data_as(C.POINTER(C.c_int32)),
+                                         ticks.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                         cmds.ctypes.data_as(C.POINTER(K.zl_clip_command))), "command_batch")
+
     def play(self, clip, loop=False, midi_channel=-2, note=60, volume=1.0, slice_=None, session=0, block=0, tick=0):
         """ClipAudioSource::play (lib/ClipAudioSource.cpp:415-429)."""
         f = dict(clip=clip, midi_channel=midi_channel, midi_note=note, change_volume=1, volume=volume,
@@ -212,6 +238,16 @@ class Engine:
         v = C.c_uint64()
         self._chk(self.lib.last_voice_frames(self.ctx, C.byref(v)), "last_voice_frames")
         return v.value
+
+    def source_floats(self):
+        v = C.c_uint64()
+        self._chk(self.lib.last_source_floats(self.ctx, C.byref(v)), "last_source_floats")
+        return v.value
+
+    def total_counters(self):
+        a, b = C.c_uint64(), C.c_uint64()
+        self._chk(self.lib.total_counters(self.ctx, C.byref(a), C.byref(b)), "total_counters")
+        return a.value, b.value
 
     def dropped_commands(self):
         v = C.c_uint64()

@@ -465,7 +465,7 @@ struct zl_ctx {
     std::vector<float> master;                // [nsess][2][n]
     std::vector<int32_t> peaks;               // [nblocks][nbus][2]
     std::vector<double> sumsq;
-    uint64_t voiceFrames = 0, dropped = 0;
+    uint64_t voiceFrames = 0, dropped = 0, totalVoiceFrames = 0;
 };
 
 namespace {
@@ -788,6 +788,13 @@ int zlo_command(zl_ctx* ctx, int32_t session, int32_t block, uint64_t tick, cons
     ctx->pending.push_back(PendingCommand{session, bus, block, tick, *cmd});
     return ZL_OK;
 }
+int zlo_command_batch(zl_ctx* ctx, int32_t n, const int32_t* s, const int32_t* b, const uint64_t* t, const zl_clip_command* c) {
+    if (!ctx || n < 0 || (n && (!s || !b || !t || !c))) return ZL_ERR_INVALID;
+    for (int i = 0; i < n; ++i) { int rc = zlo_command(ctx, s[i], b[i], t[i], &c[i]); if (rc != ZL_OK) return rc; }
+    return ZL_OK;
+}
+int zlo_total_counters(zl_ctx* ctx, uint64_t* vf, uint64_t* sf) { if (!ctx) return ZL_ERR_INVALID; if (vf) *vf = ctx->totalVoiceFrames; if (sf) *sf = 0; return ZL_OK; }
+int zlo_last_source_floats(zl_ctx*, uint64_t* n) { if (!n) return ZL_ERR_INVALID; *n = 0; return ZL_OK; }
 int zlo_bus_set_enabled(zl_ctx* ctx, int32_t s, int32_t b, int32_t en) {
     if (!ctx || s < 0 || s >= ctx->cfg.n_sessions || b < 0 || b >= ctx->cfg.buses_per_session) return ZL_ERR_INVALID;
     ctx->channels[(size_t) s * (size_t) ctx->cfg.buses_per_session + (size_t) b].enabled = en != 0; return ZL_OK;
@@ -838,6 +845,7 @@ int zlo_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_clo
     }
     ctx->voiceFrames = 0;
     for (uint64_t v : vf) ctx->voiceFrames += v;
+    ctx->totalVoiceFrames += ctx->voiceFrames;
     ctx->pending.clear();
     return ZL_OK;
 }
