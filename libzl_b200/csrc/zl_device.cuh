@@ -109,20 +109,20 @@ __device__ __forceinline__ int juce_round_to_int(double v) {
 
 // ---------------------------------------------------------------------------------------------
 // juce::ADSR on the voice record   JUCE/juce_audio_basics/utilities/juce_ADSR.h
-__device__ __forceinline__ void adsr_reset(VoiceDev& v) { v.env = 0.0f; v.adsrState = kIdle; }          // :107-111
+template <class VT> __device__ __forceinline__ void adsr_reset(VT& v) { v.env = 0.0f; v.adsrState = kIdle; }          // :107-111
 
-__device__ __forceinline__ void adsr_set_parameters(VoiceDev& v, const ClipDev& c) {                    // :76-83 (state is idle here)
+template <class VT> __device__ __forceinline__ void adsr_set_parameters(VT& v, const ClipDev& c) {                    // :76-83 (state is idle here)
     v.aRate = c.aRate; v.dRate = c.dRate; v.rRate = c.rRate; v.sustain = c.sustain; v.release = c.release;
     v.relDen = c.relDen;
 }
 
-__device__ __forceinline__ void adsr_note_on(VoiceDev& v) {                           // :114-129
+template <class VT> __device__ __forceinline__ void adsr_note_on(VT& v) {                           // :114-129
     if (v.aRate > 0.0f) v.adsrState = kAttack;
     else if (v.dRate > 0.0f) { v.env = 1.0f; v.adsrState = kDecay; }
     else v.adsrState = kSustain;
 }
 
-__device__ __forceinline__ void adsr_note_off(VoiceDev& v) {                          // :132-146
+template <class VT> __device__ __forceinline__ void adsr_note_off(VT& v) {                          // :132-146
     if (v.adsrState != kIdle) {
         if (v.release > 0.0f) {
             v.rRate = __double2float_rn(__ddiv_rn((double) v.env, v.relDen));
@@ -133,13 +133,13 @@ __device__ __forceinline__ void adsr_note_off(VoiceDev& v) {                    
     }
 }
 
-__device__ __forceinline__ void adsr_next_state(VoiceDev& v) {                        // :249-257
+template <class VT> __device__ __forceinline__ void adsr_next_state(VT& v) {                        // :249-257
     if (v.adsrState == kAttack) v.adsrState = (v.dRate > 0.0f ? kDecay : kSustain);
     else if (v.adsrState == kDecay) v.adsrState = kSustain;
     else if (v.adsrState == kRelease) adsr_reset(v);
 }
 
-__device__ __forceinline__ float adsr_next(VoiceDev& v) {                             // :153-191
+template <class VT> __device__ __forceinline__ float adsr_next(VT& v) {                             // :153-191
     const int st = v.adsrState;
     if (st == kIdle) return 0.0f;
     if (st == kAttack) {
@@ -177,7 +177,7 @@ __device__ __forceinline__ bool cmd_equivalent(const zl_clip_command& a, const z
 }
 
 // SamplerSynthVoice::stopNote   lib/SamplerSynthVoice.cpp:146-169  (J: juce_Sampler.cpp:100-111)
-__device__ __forceinline__ void voice_stop(VoiceDev& v, bool allowTailOff) {
+template <class VT> __device__ __forceinline__ void voice_stop(VT& v, bool allowTailOff) {
     if (allowTailOff) {
         adsr_note_off(v);
     } else {
