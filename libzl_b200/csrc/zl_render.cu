@@ -6,30 +6,44 @@
 // -> JackPassthroughPrivate::process (lib/JackPassthrough.cpp:45-115) -> AudioLevels peak scan
 // (lib/AudioLevels.cpp:357-385) -> JACK port mix of the dry outputs (master).
 //
-// Work decomposition (stage 2).  Thread t of the CTA owns voice t of the session for the whole launch
+// Work decomposition (stage 3).  Thread t of the CTA owns voice t of the session for the whole launch
 // (bus = t / V, slot = t % V); its state machine lives in registers.  A warp therefore owns 32 voices =
 // 32/V whole buses, and everything up to the bus outputs is warp-local:
-//   W  each lane steps ITS voice through the next tile of 32 frames with the reference's exact recurrences
-//      (f64 position, f32 ADSR, loop / release / stop events) and leaves (pos, alpha, env) per frame in the
-//      warp's shared-memory tile table (row = voice, 33 columns: conflict-free both ways);
-//   G  the warp turns 90 degrees: lane = frame.  For each of its buses it walks the voices in slot order
-//      (the serial += order of the reference), gathers both interpolation taps from the HBM-resident clip
-//      (lanes read consecutive source frames -> coalesced), applies gain / envelope / M-S pan, keeps the bus
-//      accumulators in registers and runs the passthrough + meter epilogue on them; 128-byte coalesced stores.
-// Only the per-session master mix crosses warps (one double-buffered shared stage + one barrier per tile).
+//   W  each lane PLANS its voice's next tile of kT frames in O(1): the f64 position recurrence p += ratio is
+//      exact-linear inside a binade (zl_voice.cuh), so a tile is at most two (p0, R) segments broken at binade
+//      crossings / loop wraps / the stop position; the envelope is a constant while the ADSR sits in sustain and
+//      is stepped frame by frame into a shared-memory row only while it attacks, decays or releases.  Tiles a
+//      voice cannot express that way (p < 1, rounding ties, tiny loops) make the warp drop to 32-frame tiles in
+//      which that lane walks its positions frame by frame into a shared-memory slot;
+//   G  the warp turns 90 degrees: lane = frame.  For each of its buses it walks the voices in slot order (the
+//      serial += order of the reference), evaluates p = p0 + k*R with one DFMA, splits it into (pos, alpha),
+//      gathers both taps from the HBM-resident clip (lanes read consecutive source frames -> coalesced), applies
+//      gain / envelope / M-S pan, keeps the bus accumulators in registers and runs the passthrough + meter
+//      epilogue on them; 128-byte coalesced stores.
+// Only the per-session master mix crosses warps (one shared stage + two barriers per tile).
 #include "zl_voice.cuh"
 
 namespace zl {
 
-constexpr int kTile = 32;            // frames per tile == lanes per warp
-constexpr int kCols = kTile + 1;     // column 0 carries the previous tile's last frame (quirk Q2 reads frame j-1)
+constexpr int kT = 64;               // frames per tile in the regular mode (multiple of 32)
+constexpr int kNC = kT / 32;         // 32-frame chunks per tile
+constexpr int kShort = 32;           // frames per tile when some lane of the warp needs the per-frame position walk
+constexpr int kTblFloats = (32 * (kT + 1) > 32 * 33 * 3) ? 32 * (kT + 1) : 32 * 33 * 3;
+
+// What G needs to know about one voice for one tile (shared memory, 48 bytes = 3 x LDS.128).
+struct __align__(16) TileDesc {
+    double p0a, Ra, p0b, Rb;         // position segments a: frames [0, cb), b: frames [cb, nrend)
+    int32_t cb;
+    int32_t nrend;                   // frames of the tile this voice renders
+    float envConst;
+    int32_t kind;                    // bit 0: envelope from the table row; bit 1: positions from the slot row
+};
 
 struct __align__(16) WarpSmem {
-    int   tp[32 * kCols];            // (int) sourceSamplePosition per voice-frame
-    float ta[32 * kCols];            // alpha
-    float te[32 * kCols];            // ADSR envelope value
+    // regular tiles: te[32][kT + 1] envelope rows.  short tiles: te[32][33] followed by ps[32][33] f64 position slots.
+    float tbl[kTblFloats];
+    TileDesc td[32];
     VoiceGather vg[32];
-    int   rng[32];                   // valid table columns of the voice in this tile: lo | hi << 8
     int   vpeak[32];                 // per-voice block peak of l + r (float bits, >= 0)   :213-216
     int   busPk[64];                 // per-bus block peaks [bus][2]
     double busSq[64];                // per-bus block sums of squares [bus][2]
@@ -43,29 +57,28 @@ __device__ __forceinline__ float lerp_gain_z(float a, float b, float ia, float a
 }
 
 // One voice-frame: both taps, interpolation, gains, (Z) M/S pan.  J: juce_Sampler.cpp:128-152, Z: :198-211
-template <bool JMODE, bool Q1>
+template <bool JMODE, bool Q1, bool STEREO>
 __device__ __forceinline__ void gather_voice(const VoiceGather& g, int pos, float alpha, float env, float& l, float& r) {
     const float ia = __fsub_rn(1.0f, alpha);
     if (JMODE) {
-        float a0, a1, b0, b1;
-        if (g.nch > 1) {
+        if (STEREO) {
             const float2 a = __ldg(reinterpret_cast<const float2*>(g.data) + pos);
             const float2 b = __ldg(reinterpret_cast<const float2*>(g.data) + pos + 1);
-            a0 = a.x; a1 = a.y; b0 = b.x; b1 = b.y;
+            l = __fadd_rn(__fmul_rn(a.x, ia), __fmul_rn(b.x, alpha));
+            r = __fadd_rn(__fmul_rn(a.y, ia), __fmul_rn(b.y, alpha));
         } else {
-            a0 = a1 = __ldg(g.data + pos); b0 = b1 = __ldg(g.data + pos + 1);
+            const float a = __ldg(g.data + pos), b = __ldg(g.data + pos + 1);
+            l = __fadd_rn(__fmul_rn(a, ia), __fmul_rn(b, alpha));
+            r = l;
         }
-        l = __fadd_rn(__fmul_rn(a0, ia), __fmul_rn(b0, alpha));
-        r = g.nch > 1 ? __fadd_rn(__fmul_rn(a1, ia), __fmul_rn(b1, alpha)) : l;
         const float ge = __fmul_rn(g.gain, env);
         l = __fmul_rn(l, ge);
         r = __fmul_rn(r, ge);
         return;
     }
-    const bool inRange = g.sampleDuration > pos;
     l = 0.0f; r = 0.0f;
-    if (inRange) {
-        if (g.nch > 1) {
+    if (g.sampleDuration > pos) {
+        if (STEREO) {
             const float2 a = __ldg(reinterpret_cast<const float2*>(g.data) + pos);
             const float2 b = __ldg(reinterpret_cast<const float2*>(g.data) + pos + 1);
             l = lerp_gain_z<Q1>(a.x, b.x, ia, alpha, g.gain, env, g.vol);
@@ -82,6 +95,55 @@ __device__ __forceinline__ void gather_voice(const VoiceGather& g, int pos, floa
     r = __fsub_rn(__fmul_rn(g.rPan, m), sd);
 }
 
+// One voice x one tile in G: lane = frame within each 32-frame chunk.  Everything the branches test is warp-uniform.
+template <bool JMODE, bool Q1, bool STEREO>
+__device__ __forceinline__ float gather_tile(const TileDesc& d, const VoiceGather& g, const float* terow, const double* psrow,
+                                             int lane, double laneD, float (&accL)[kNC], float (&accR)[kNC]) {
+    float vmax = 0.0f;
+    const bool single = d.cb >= d.nrend && !(d.kind & 2);
+#pragma unroll
+    for (int ch = 0; ch < kNC; ++ch) {
+        const int c = ch * 32 + lane;
+        if (c < d.nrend) {
+            double p;
+            if (single) p = __fma_rn(__dadd_rn(laneD, (double) (ch * 32)), d.Ra, d.p0a);
+            else if (d.kind & 2) p = psrow[c];
+            else {
+                const bool sb = c >= d.cb;
+                p = __fma_rn((double) (c - (sb ? d.cb : 0)), sb ? d.Rb : d.Ra, sb ? d.p0b : d.p0a);
+            }
+            // (int) p and p - (int) p without int<->f64 conversions: p + 2^52 rounded down is floor(p) + 2^52
+            const double t = __dadd_rd(p, 4503599627370496.0);
+            const int pos = __double2loint(t);
+            const float alpha = __double2float_rn(__dsub_rn(p, __dsub_rn(t, 4503599627370496.0)));
+            const float env = (d.kind & 1) ? terow[c] : d.envConst;
+            float l, r;
+            gather_voice<JMODE, Q1, STEREO>(g, pos, alpha, env, l, r);
+            accL[ch] = __fadd_rn(accL[ch], l);
+            accR[ch] = __fadd_rn(accR[ch], r);
+            vmax = fmaxf(vmax, __fadd_rn(l, r));
+        }
+    }
+    return vmax;
+}
+
+// Fire-and-forget L2 prefetch of the source span the voice will read in its NEXT tile (one bulk request per voice:
+// UBLKPF).  The gather's loads then hit L2 instead of waiting on HBM; the HBM requests of 32 voices x all resident
+// warps are in flight while the current tile is being computed.
+__device__ __forceinline__ void prefetch_span_l2(const float* data, int nch, int clipFrames, double p, double ratio, int frames) {
+    const int first = (int) p;
+    int last = first + (int) (ratio * (double) frames) + 2;
+    last = min(last, clipFrames + 7);
+    if (last <= first) return;
+    const size_t fb = (size_t) nch * sizeof(float);
+    uintptr_t a = reinterpret_cast<uintptr_t>(data) + (size_t) first * fb;
+    uintptr_t e = reinterpret_cast<uintptr_t>(data) + (size_t) (last + 1) * fb;
+    a &= ~uintptr_t(15);
+    const unsigned bytes = (unsigned) ((e - a) & ~uintptr_t(15));
+    if (bytes == 0) return;
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(a), "r"(bytes) : "memory");
+}
+
 // JackPassthroughPrivate::process for one output pair   lib/JackPassthrough.cpp:58-111
 __device__ __forceinline__ void passthrough_pair(const zl_passthrough_params& p, float amt, float inL, float inR,
                                                  float& oL, float& oR) {
@@ -96,6 +158,20 @@ __device__ __forceinline__ int peak_int(float x) {   // lib/AudioLevels.cpp:365-
     return __float2int_rz(fabsf(__fmul_rn(131072.0f, x)));
 }
 
+
+// What a position plan may change before it is accepted.
+struct PlanUndo {
+    double p; uint64_t nextLoopTick, nextLoopUsecs; int32_t fWrap, spanStart, lastPos; uint32_t span;
+};
+__device__ __forceinline__ void plan_save(PlanUndo& u, const VoiceHot& h, const VoiceBlockCtl& b) {
+    u.p = h.p; u.nextLoopTick = h.nextLoopTick; u.nextLoopUsecs = h.nextLoopUsecs;
+    u.fWrap = b.fWrap; u.spanStart = b.spanStart; u.lastPos = b.lastPos; u.span = b.span;
+}
+__device__ __forceinline__ void plan_restore(const PlanUndo& u, VoiceHot& h, VoiceBlockCtl& b) {
+    h.p = u.p; h.nextLoopTick = u.nextLoopTick; h.nextLoopUsecs = u.nextLoopUsecs;
+    b.fWrap = u.fWrap; b.spanStart = u.spanStart; b.lastPos = u.lastPos; b.span = u.span;
+}
+
 // CFG = mode << 3 | quirks (quirks forced to 0 in J-mode): compile-time so the frame loops carry no mode tests.
 // MAXT: 256 (sessions of up to 256 voices, <= 128 registers) or 1024.
 template <int CFG, int MAXT>
@@ -103,6 +179,7 @@ __global__ void __launch_bounds__(MAXT, MAXT == 256 ? 2 : 1)
 render_kernel(const RenderParams P) {
     constexpr bool JMODE = (CFG >> 3) == ZL_MODE_J;
     constexpr bool Q1 = (CFG & ZL_Q1_TAP_GAIN) != 0, Q2 = (CFG & ZL_Q2_PREINC) != 0, Q3 = (CFG & ZL_Q3_RENOTEOFF) != 0;
+    constexpr int QS = Q2 ? 1 : 0;                        // frame f lands at output index f + QS   :218-221
     extern __shared__ __align__(16) unsigned char smemRaw[];
     const int s = blockIdx.x;
     const int B = P.B, V = P.V, NV = B * V;
@@ -112,7 +189,7 @@ render_kernel(const RenderParams P) {
     const unsigned FULL = 0xffffffffu;
 
     WarpSmem& ws = reinterpret_cast<WarpSmem*>(smemRaw)[warp];
-    float* stage = reinterpret_cast<float*>(smemRaw + sizeof(WarpSmem) * nwarps);   // [2][B][2][32] master staging
+    float* stage = reinterpret_cast<float*>(smemRaw + sizeof(WarpSmem) * nwarps);   // [B][2][kT] master staging
 
     // ownership: this lane's voice / bus; the warp's buses
     const bool hasVoice = tid < NV;
@@ -133,7 +210,7 @@ render_kernel(const RenderParams P) {
         cmdCur = bus.cmdBegin; cmdEnd = cmdCur + bus.cmdCount; busEnabled = bus.enabled;
     }
     unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
-    int stageBuf = 0;
+    const double laneD = (double) lane;
 
     for (int blk = 0; blk < P.nblocks; ++blk) {
         const zl_block_clock ck = P.clocks[blk];
@@ -159,7 +236,7 @@ render_kernel(const RenderParams P) {
         // ---- block prelude -------------------------------------------------------------------------------
         VoiceBlockCtl bc;
         bc.stopD = 0.0; bc.startD = 0.0; bc.relStart = 0.0; bc.usPerFrame = 0.0; bc.lengthInTicks = 0; bc.fWrap = nframes;
-        bc.beatAligned = 0; bc.spanStart = 0; bc.lastPos = 0; bc.span = 0; bc.nch = 0; bc.releaseArmed = 0;
+        bc.beatAligned = 0; bc.spanStart = 0; bc.lastPos = 0; bc.span = 0; bc.nch = 0; bc.clipFrames = 0; bc.releaseArmed = 0;
         bool active = false;
         {
             VoiceGather g;
@@ -172,82 +249,117 @@ render_kernel(const RenderParams P) {
             ws.busSq[lane] = 0.0; ws.busSq[lane + 32] = 0.0;
         }
         const bool walked = active;
-        bool carryValid = false;
         int nrendBlock = 0;
-        int* tp = ws.tp + lane * kCols;
-        float* ta = ws.ta + lane * kCols;
-        float* te = ws.te + lane * kCols;
         __syncwarp();
 
-        for (int j0 = 0; j0 < nframes; j0 += kTile) {
-            const int n = min(kTile, nframes - j0);
-            // ---- W: owner lanes step their voices through the tile --------------------------------------
+        for (int t0 = 0; t0 < nframes; t0 += kT) {
+            // ---- W: every lane plans its voice's tile ----------------------------------------------------
+            const int nT = min(kT, nframes - t0);
+            PosPlan pl;
+            pl.p0a = 0.0; pl.Ra = 0.0; pl.p0b = 0.0; pl.Rb = 0.0; pl.cb = nT; pl.nPos = 0; pl.kRel = INT_MAX; pl.stopped = 0; pl.irregular = 0;
+            PlanUndo undo;
+            plan_save(undo, h, bc);
+            if (active) plan_positions<JMODE>(h, bc, ck, t0, nT, nframes, pl);
+            // a lane that cannot express its tile in closed form makes the warp cover it in 32-frame sub-tiles
+            const bool shortTile = __any_sync(FULL, active && pl.irregular);
+            if (shortTile && active) plan_restore(undo, h, bc);
+            const int nn = shortTile ? kShort : nT;
+            const int teStride = shortTile ? 33 : kT + 1;
+            float* te = ws.tbl + lane * teStride;
+            double* ps = reinterpret_cast<double*>(ws.tbl + 32 * 33) + lane * 33;
+          for (int s0 = 0; s0 < nT; s0 += nn) {
+            const int n = min(nn, nT - s0);
+            if (shortTile && active) {
+                plan_save(undo, h, bc);
+                plan_positions<JMODE>(h, bc, ck, t0 + s0, n, nframes, pl);
+                if (pl.irregular) {
+                    plan_restore(undo, h, bc);
+                    walk_positions<JMODE>(h, bc, ck, t0 + s0, n, nframes, ps, pl);
+                }
+            }
             int cnt = 0;
-            if (active) {
-                if (JMODE) cnt = voice_walk_tile_j(h, bc, n, tp + 1, ta + 1, te + 1, active);
-                else cnt = voice_walk_tile_z<Q3>(h, bc, ck, j0, n, nframes, tp + 1, ta + 1, te + 1, active);
+            {
+                TileDesc d;
+                d.p0a = pl.p0a; d.Ra = pl.Ra; d.p0b = pl.p0b; d.Rb = pl.Rb; d.cb = pl.cb; d.nrend = 0; d.envConst = 0.0f; d.kind = 0;
+                if (active) {
+                    bool fromTable, ended;
+                    cnt = plan_envelope<JMODE, Q3>(h, bc, pl, te, d.envConst, fromTable, ended);
+                    d.nrend = cnt;
+                    d.kind = (fromTable ? 1 : 0) | (pl.irregular ? 2 : 0);
+                    if (ended && cnt < pl.nPos) {                          // the ADSR ran out before the tile did: p is frame cnt's
+                        if (pl.irregular) h.p = ps[cnt];
+                        else h.p = cnt >= pl.cb ? __fma_rn((double) (cnt - pl.cb), pl.Rb, pl.p0b) : __fma_rn((double) cnt, pl.Ra, pl.p0a);
+                    }
+                    if (pl.stopped || ended) { voice_stop(h, false); active = false; }
+                    else prefetch_span_l2(ws.vg[lane].data, bc.nch, bc.clipFrames, h.p, h.ratio, kT);
+                }
+                ws.td[lane] = d;
             }
             nrendBlock += cnt;
-            ws.rng[lane] = ((Q2 && carryValid) ? 0 : 1) | ((1 + cnt) << 8);
             __syncwarp();
 
-            // ---- G: lane = frame --------------------------------------------------------------------------
-            const int j = j0 + lane;                        // output index in the block
-            const int col = Q2 ? lane : lane + 1;           // Q2: frame f lands at index f + 1   :218-221
+            // ---- G: lane = frame -----------------------------------------------------------------------------
             for (int bl = 0; bl < busesPerWarp; ++bl) {
                 const int wb = warpBus0 + bl;               // bus of the session
                 if (wb >= B) break;
                 const int gbw = s * B + wb;
-                float accL = 0.0f, accR = 0.0f;
+                float accL[kNC], accR[kNC];
+#pragma unroll
+                for (int ch = 0; ch < kNC; ++ch) { accL[ch] = 0.0f; accR[ch] = 0.0f; }
                 for (int vs = 0; vs < V; ++vs) {
                     const int row = bl * V + vs;
-                    const int rg = ws.rng[row];
-                    const int lo = rg & 0xff, hi = rg >> 8;
-                    if (hi <= lo) continue;                                    // warp-uniform: voice silent in this tile
+                    const TileDesc d = ws.td[row];
+                    if (d.nrend <= 0) continue;                                // warp-uniform: voice silent in this tile
                     const VoiceGather g = ws.vg[row];
-                    float vpk = 0.0f;
-                    if (col >= lo && col < hi) {
-                        float l, r;
-                        gather_voice<JMODE, Q1>(g, ws.tp[row * kCols + col], ws.ta[row * kCols + col], ws.te[row * kCols + col], l, r);
-                        accL = __fadd_rn(accL, l);
-                        accR = __fadd_rn(accR, r);
-                        vpk = __fadd_rn(l, r);
-                    }
+                    const float* terow = ws.tbl + row * teStride;
+                    const double* psrow = reinterpret_cast<const double*>(ws.tbl + 32 * 33) + row * 33;
+                    const float vmax = g.nch > 1 ? gather_tile<JMODE, Q1, true>(d, g, terow, psrow, lane, laneD, accL, accR)
+                                                 : gather_tile<JMODE, Q1, false>(d, g, terow, psrow, lane, laneD, accL, accR);
                     if (!JMODE) {                                              // block peak of the voice  :213-216
-                        int pk = max(0, __float_as_int(vpk));
-                        pk = __reduce_max_sync(FULL, pk);
-                        if (lane == 0 && pk > ws.vpeak[row]) ws.vpeak[row] = pk;
+                        const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));   // vmax >= +0: int order == float order
+                        if (lane == 0) atomicMax(&ws.vpeak[row], pk);
                     }
                 }
                 // raw SamplerChannel ports, then JackPassthrough, meters, master staging
                 const zl_passthrough_params pt = P.buses[gbw].pt;
-                float dL = 0.0f, dR = 0.0f;
                 int pkL = 0, pkR = 0;
                 double sqL = 0.0, sqR = 0.0;
-                if (j < nframes) {
-                    if (P.out[0]) {
-                        P.out[0][((int64_t) gbw * 2) * P.stride + off + j] = accL;
-                        P.out[0][((int64_t) gbw * 2 + 1) * P.stride + off + j] = accR;
+#pragma unroll
+                for (int ch = 0; ch < kNC; ++ch) {
+                    const int c = ch * 32 + lane;
+                    const int j = t0 + s0 + c + QS;                            // output index in the block
+                    float dL = 0.0f, dR = 0.0f;
+                    if (c < n && j < nframes) {
+                        const int64_t o = off + j;
+                        if (P.out[0]) {
+                            P.out[0][((int64_t) gbw * 2) * P.stride + o] = accL[ch];
+                            P.out[0][((int64_t) gbw * 2 + 1) * P.stride + o] = accR[ch];
+                        }
+                        passthrough_pair(pt, pt.dry_amount, accL[ch], accR[ch], dL, dR);
+                        if (P.out[1]) {
+                            P.out[1][((int64_t) gbw * 2) * P.stride + o] = dL;
+                            P.out[1][((int64_t) gbw * 2 + 1) * P.stride + o] = dR;
+                        }
+                        float xL, xR;
+                        if (P.out[2]) {
+                            passthrough_pair(pt, pt.wet_fx1_amount, accL[ch], accR[ch], xL, xR);
+                            P.out[2][((int64_t) gbw * 2) * P.stride + o] = xL;
+                            P.out[2][((int64_t) gbw * 2 + 1) * P.stride + o] = xR;
+                        }
+                        if (P.out[3]) {
+                            passthrough_pair(pt, pt.wet_fx2_amount, accL[ch], accR[ch], xL, xR);
+                            P.out[3][((int64_t) gbw * 2) * P.stride + o] = xL;
+                            P.out[3][((int64_t) gbw * 2 + 1) * P.stride + o] = xR;
+                        }
+                        pkL = max(pkL, peak_int(dL)); pkR = max(pkR, peak_int(dR));
+                        sqL += (double) __fmul_rn(dL, dL);                     // juce_AudioSampleBuffer.h:1087-1095
+                        sqR += (double) __fmul_rn(dR, dR);
                     }
-                    passthrough_pair(pt, pt.dry_amount, accL, accR, dL, dR);
-                    if (P.out[1]) {
-                        P.out[1][((int64_t) gbw * 2) * P.stride + off + j] = dL;
-                        P.out[1][((int64_t) gbw * 2 + 1) * P.stride + off + j] = dR;
-                    }
-                    float xL, xR;
-                    if (P.out[2]) {
-                        passthrough_pair(pt, pt.wet_fx1_amount, accL, accR, xL, xR);
-                        P.out[2][((int64_t) gbw * 2) * P.stride + off + j] = xL;
-                        P.out[2][((int64_t) gbw * 2 + 1) * P.stride + off + j] = xR;
-                    }
-                    if (P.out[3]) {
-                        passthrough_pair(pt, pt.wet_fx2_amount, accL, accR, xL, xR);
-                        P.out[3][((int64_t) gbw * 2) * P.stride + off + j] = xL;
-                        P.out[3][((int64_t) gbw * 2 + 1) * P.stride + off + j] = xR;
-                    }
-                    pkL = peak_int(dL); pkR = peak_int(dR);
-                    sqL = (double) __fmul_rn(dL, dL);                          // juce_AudioSampleBuffer.h:1087-1095
-                    sqR = (double) __fmul_rn(dR, dR);
+                    if (P.master && c < nn) { stage[((size_t) wb * 2) * kT + s0 + c] = dL; stage[((size_t) wb * 2 + 1) * kT + s0 + c] = dR; }
+                }
+                if (Q2 && t0 + s0 == 0 && lane == 0) {                              // index 0 is never accumulated into (:218): stays zero
+                    for (int w = 0; w < 4; ++w)
+                        if (P.out[w]) { P.out[w][((int64_t) gbw * 2) * P.stride + off] = 0.0f; P.out[w][((int64_t) gbw * 2 + 1) * P.stride + off] = 0.0f; }
                 }
                 if (P.peaks) {
                     pkL = __reduce_max_sync(FULL, pkL);
@@ -261,40 +373,26 @@ render_kernel(const RenderParams P) {
                     }
                     if (lane == 0) { ws.busSq[bl * 2] += sqL; ws.busSq[bl * 2 + 1] += sqR; }
                 }
-                if (P.master) {
-                    float* st = stage + ((size_t) (stageBuf * B + wb) * 2) * kTile;
-                    st[lane] = dL; st[kTile + lane] = dR;
-                }
             }
             __syncwarp();
-            // ---- carry the tile's last frame into column 0 for the next tile (Q2) ----------------------------
-            if (Q2) {
-                tp[0] = tp[kTile]; ta[0] = ta[kTile]; te[0] = te[kTile];
-                carryValid = cnt == kTile;
-            }
+          }
             // ---- JACK port mix of the session (sum of the dry outs in bus order) ------------------------------
             if (P.master) {
                 __syncthreads();
-                for (int t2 = tid; t2 < 2 * kTile; t2 += blockDim.x) {
-                    const int ch = t2 >> 5, ln = t2 & 31;
-                    const float* st = stage + (size_t) stageBuf * B * 2 * kTile + ch * kTile + ln;
+                for (int t2 = tid; t2 < 2 * kT; t2 += blockDim.x) {
+                    const int ch = t2 / kT, c = t2 - ch * kT;
+                    const float* st = stage + ch * kT + c;
                     float m = st[0];
-                    for (int b2 = 1; b2 < B; ++b2) m = __fadd_rn(m, st[(size_t) b2 * 2 * kTile]);
-                    if (j0 + ln < nframes) P.master[((int64_t) s * 2 + ch) * P.stride + off + j0 + ln] = m;
+                    for (int b2 = 1; b2 < B; ++b2) m = __fadd_rn(m, st[(size_t) b2 * 2 * kT]);
+                    const int j = t0 + c + QS;
+                    if (c < nT && j < nframes) P.master[((int64_t) s * 2 + ch) * P.stride + off + j] = m;
+                    if (Q2 && t0 == 0 && c == 0) P.master[((int64_t) s * 2 + ch) * P.stride + off] = 0.0f;
                 }
-                stageBuf ^= 1;
+                __syncthreads();
             }
         }
 
         // ---- block epilogue ----------------------------------------------------------------------------------
-        if (!JMODE && Q2 && (nframes % kTile) == 0 && nrendBlock == nframes) {
-            // The frame rendered last lands at index nframes (one past the JACK buffer, :218-221): no output lane
-            // took it, but it still counts for the voice's block peak (:213-216).  Its table entry is in column 32.
-            float l, r;
-            gather_voice<JMODE, Q1>(ws.vg[lane], tp[kTile], ta[kTile], te[kTile], l, r);
-            const int pk = max(0, __float_as_int(__fadd_rn(l, r)));
-            if (pk > ws.vpeak[lane]) ws.vpeak[lane] = pk;
-        }
         if (walked) {
             nVoiceFrames += (unsigned long long) nrendBlock;
             if (nrendBlock > 0) nSrcFloats += (unsigned long long) (bc.span + (uint32_t) (bc.lastPos + 2 - bc.spanStart)) * (unsigned) bc.nch;
@@ -334,7 +432,7 @@ size_t render_smem_bytes(int B, int V, int nframes) {
     (void) nframes;
     const int nv = B * V;
     if (nv > 1024) return (size_t) 1 << 30;                 // one thread per voice of the session: reported as "does not fit"
-    return sizeof(WarpSmem) * (size_t) (render_threads(B, V) / 32) + sizeof(float) * 2 * (size_t) B * 2 * kTile;
+    return sizeof(WarpSmem) * (size_t) (render_threads(B, V) / 32) + sizeof(float) * (size_t) B * 2 * kT;
 }
 
 template <int CFG, int MAXT>

@@ -1,6 +1,7 @@
 // zl_voice.cuh — per-voice state machine (exact, frame-by-frame recurrences, register-resident between tiles)
 // and the in-kernel SamplerChannel::handleCommand.  Used by the render kernel in zl_render.cu.
 #pragma once
+#include <limits.h>
 #include "zl_device.cuh"
 
 namespace zl {
@@ -91,7 +92,7 @@ struct VoiceBlockCtl {
     int32_t beatAligned;
     int32_t spanStart, lastPos;   // algorithmic source-span accounting
     uint32_t span;
-    int32_t nch;
+    int32_t nch, clipFrames;
     int32_t releaseArmed;     // Q3 fixed: noteOff() once per block instead of on every frame of the release window
 };
 
@@ -121,10 +122,12 @@ __device__ __forceinline__ bool voice_block_begin(VoiceHot& h, const RenderParam
     if (h.sound < 0) return false;
     const ClipDev& snd = P.clips[h.sound];
     g.data = snd.data; g.nch = snd.nch; g.sampleDuration = snd.length - 1; g.gain = h.gain;
-    b.nch = snd.nch; b.releaseArmed = 0; b.span = 0; b.spanStart = (int) h.p; b.lastPos = b.spanStart;
+    b.nch = snd.nch; b.clipFrames = snd.length; b.releaseArmed = 0; b.span = 0; b.spanStart = (int) h.p; b.lastPos = b.spanStart;
     if (JMODE) {
         g.vol = 1.0f; g.lPan = 0.0f; g.rPan = 0.0f;
-        b.stopD = (double) snd.length;                                        // juce_Sampler.cpp:155
+        // juce_Sampler.cpp:155 stops when p > length; stored as the next double up so every mode tests p >= stopD
+        b.stopD = __longlong_as_double(__double_as_longlong((double) snd.length) + 1);
+        b.startD = 0.0; b.relStart = 0.0; b.beatAligned = 0; b.fWrap = nframes;
         return true;
     }
     if (!(snd.length > 0 && (h.flags & VF_HAS_CMD))) return false;            // :176-177
@@ -144,66 +147,170 @@ __device__ __forceinline__ bool voice_block_begin(VoiceHot& h, const RenderParam
     return true;
 }
 
-// `n` frames of the block starting at block frame `f0`, frame by frame, exactly as the reference steps them:
-// writes (pos, alpha, env) of each rendered frame at tp/ta/te[i] and returns how many were rendered;
-// `active` goes false when the voice ends inside the tile.   lib/SamplerSynthVoice.cpp:197-262
-template <bool Q3>
-__device__ __forceinline__ int voice_walk_tile_z(VoiceHot& h, VoiceBlockCtl& b, const zl_block_clock& ck, int f0, int n, int nframes,
-                                                 int* tp, float* ta, float* te, bool& active) {
-    int i = 0;
-    for (; i < n; ) {
-        const int pos = (int) h.p;
-        tp[i] = pos;
-        ta[i] = __double2float_rn(__dsub_rn(h.p, (double) pos));
-        te[i] = adsr_next(h);
-        const int frame = f0 + i;
-        ++i;
-        b.lastPos = pos;
-        h.p = __dadd_rn(h.p, h.ratio);                                        // :223
-        if (h.looping) {
-            bool wrap = false;
-            if (b.beatAligned) {
-                if (frame == b.fWrap) {                                       // :232-236
-                    h.nextLoopTick = h.nextLoopTick + b.lengthInTicks;
-                    const uint64_t diff = h.nextLoopTick - ck.playhead;
-                    h.nextLoopUsecs = ck.playhead_usecs + diff * ck.subbeat_usecs;
-                    b.fWrap = first_wrap_frame(ck, b.usPerFrame, h.nextLoopUsecs, frame + 1, nframes);
-                    wrap = true;
-                }
-            } else if (h.p >= b.stopD) {                                      // :243-247
-                wrap = true;
-            }
-            if (wrap) {
-                h.p = b.startD;
-                if ((int) b.startD < pos) {                                   // backward jump: close the span, open a new one
-                    b.span += (uint32_t) (pos + 2 - b.spanStart); b.spanStart = (int) b.startD; b.lastPos = b.spanStart - 2;
-                }
-            }
-        } else {
-            if (h.p >= b.stopD) { voice_stop(h, false); active = false; return i; }    // :249-251
-            else if (h.p >= b.relStart) {                                     // :253-256 (Q3: re-armed on every frame)
-                if (Q3 || !b.releaseArmed) { adsr_note_off(h); b.releaseArmed = 1; }
-            }
-        }
-        if (h.adsrState == kIdle) { voice_stop(h, false); active = false; return i; }  // :258-261
-    }
-    return i;
+
+// ---------------------------------------------------------------------------------------------
+// Closed-form position segments.
+//
+// The reference advances the source position with  p = RN(p + ratio)  in f64 once per frame (:223).  While p
+// stays inside one binade [2^e, 2^(e+1)) every p is a multiple of u = 2^(e-52), so RN(p + ratio) = p + R with
+// R = ratio rounded to a multiple of u — the SAME R for every step (ties excepted: |ratio - R| = u/2 rounds by
+// the parity of p).  Hence  p_k = p_0 + k*R  exactly, and a DFMA evaluates it exactly because the true value is
+// representable.  A tile of frames is therefore described by at most two (p0, R) segments, broken at binade
+// crossings and loop wraps, where ONE real DADD + the reference's event tests are executed; the rare tiles
+// that need more (p < 1, ties, tiny loops) fall back to the per-frame walk below.  Bit-exact by construction.
+struct PosPlan {
+    double p0a, Ra, p0b, Rb;
+    int32_t cb;               // first tile frame of segment b (>= n: unused)
+    int32_t nPos;             // frames the position logic renders in this tile (voice stops after frame nPos-1 if stopped)
+    int32_t kRel;             // Z one-shot: first increment k (after tile frame k-1) with p_k >= relStart; INT_MAX: none
+    int32_t stopped;          // the position logic ended the voice (:249-251 / juce_Sampler.cpp:155-159)
+    int32_t irregular;        // not expressible: use the per-frame walk
+};
+
+// R for the binade of p, or false when the closed form does not apply.
+__device__ __forceinline__ bool binade_step(double p, double ratio, double& R, double& top) {
+    if (!(p >= 1.0)) return false;
+    const int hi = __double2hiint(p);
+    top = __hiloint2double((hi & 0x7ff00000) + 0x00100000, 0);            // 2^(e+1)
+    if (!(ratio < __dmul_rn(top, 0.25))) return false;                       // binade shorter than ~2 frames
+    const double M = __dmul_rn(top, 0.75);                                  // 1.5 * 2^e: ulp(M) = u
+    R = __dsub_rn(__dadd_rn(M, ratio), M);
+    const double u = __dmul_rn(top, 1.1102230246251565e-16);                // 2^(e+1) * 2^-53 = u
+    if (__dmul_rn(fabs(__dsub_rn(ratio, R)), 2.0) == u) return false;       // tie: rounding would depend on p's parity
+    return R > 0.0;
 }
 
-// J-mode: juce::SamplerVoice::renderNextBlock   juce_Sampler.cpp:128-161
-__device__ __forceinline__ int voice_walk_tile_j(VoiceHot& h, VoiceBlockCtl& b, int n, int* tp, float* ta, float* te, bool& active) {
-    int i = 0;
-    for (; i < n; ) {
-        const int pos = (int) h.p;
-        tp[i] = pos;
-        ta[i] = __double2float_rn(__dsub_rn(h.p, (double) pos));
-        te[i] = adsr_next(h);
-        ++i;
-        b.lastPos = pos;
-        h.p = __dadd_rn(h.p, h.ratio);
-        if (h.p > b.stopD) { voice_stop(h, false); active = false; return i; }
+// Smallest k in [1, kmax] with p + k*R >= lim, or kmax + 1.  p + k*R is exact while < top (see above).
+__device__ __forceinline__ int first_k_reaching(double p, double R, double lim, int kmax) {
+    if (__fma_rn((double) kmax, R, p) < lim) return kmax + 1;
+    int k = (int) __ddiv_rn(__dsub_rn(lim, p), R);
+    k = max(1, min(kmax, k));
+    while (k > 1 && __fma_rn((double) (k - 1), R, p) >= lim) --k;
+    while (k < kmax && __fma_rn((double) k, R, p) < lim) ++k;
+    return k;
+}
+
+// The increment after block frame `frame` whose position was `plast`: the reference's :223-251 (J: :154-159) for
+// one frame, position side only.  Returns true when the voice ends here.
+template <bool JMODE>
+__device__ __forceinline__ bool pos_explicit_step(VoiceHot& h, VoiceBlockCtl& b, const zl_block_clock& ck, double plast, int frame,
+                                                  int nframes, int kInc, int& kRel) {
+    const int pos = (int) plast;
+    b.lastPos = pos;
+    double pn = __dadd_rn(plast, h.ratio);
+    if (!JMODE && h.looping) {
+        bool wrap = false;
+        if (b.beatAligned) {
+            if (frame == b.fWrap) {                                           // :232-236
+                h.nextLoopTick = h.nextLoopTick + b.lengthInTicks;
+                const uint64_t diff = h.nextLoopTick - ck.playhead;
+                h.nextLoopUsecs = ck.playhead_usecs + diff * ck.subbeat_usecs;
+                b.fWrap = first_wrap_frame(ck, b.usPerFrame, h.nextLoopUsecs, frame + 1, nframes);
+                wrap = true;
+            }
+        } else if (pn >= b.stopD) wrap = true;                                // :243-247
+        if (wrap) {
+            pn = b.startD;
+            if ((int) b.startD < pos) {                                       // backward jump: close the span, open a new one
+                b.span += (uint32_t) (pos + 2 - b.spanStart); b.spanStart = (int) b.startD; b.lastPos = b.spanStart - 2;
+            }
+        }
+        h.p = pn;
+        return false;
     }
-    return i;
+    h.p = pn;
+    if (pn >= b.stopD) return true;                                           // :249-251 / J :155-159
+    if (!JMODE && kRel == INT_MAX && pn >= b.relStart) kRel = kInc;           // :253
+    return false;
+}
+
+// Plans the positions of tile frames [0, n) (block frames f0 ..) from h.p; advances h.p / loop clock / span.
+template <bool JMODE>
+__device__ __forceinline__ void plan_positions(VoiceHot& h, VoiceBlockCtl& b, const zl_block_clock& ck, int f0, int n, int nframes,
+                                               PosPlan& pl) {
+    pl.cb = n; pl.nPos = n; pl.kRel = INT_MAX; pl.stopped = 0; pl.irregular = 0;
+    pl.p0a = h.p; pl.Ra = 0.0; pl.p0b = 0.0; pl.Rb = 0.0;
+    const bool looping = !JMODE && h.looping;
+    const bool oneShotZ = !JMODE && !h.looping;
+    int c = 0, nseg = 0;
+    while (c < n) {
+        double R, top;
+        if (nseg == 2 || !binade_step(h.p, h.ratio, R, top)) { pl.irregular = 1; return; }
+        const double p = h.p;
+        if (nseg == 0) { pl.p0a = p; pl.Ra = R; } else { pl.p0b = p; pl.Rb = R; pl.cb = c; }
+        ++nseg;
+        const int mMax = n - c;
+        int mCap = mMax;
+        if (looping && b.beatAligned) mCap = min(mCap, b.fWrap - (f0 + c) + 1);      // the wrap frame ends its segment
+        const bool wrapsOrStops = !(looping && b.beatAligned);                          // p_k >= stopD is an event
+        const double lim = wrapsOrStops ? fmin(top, b.stopD) : top;
+        const double q = __fma_rn((double) mCap, R, p);
+        if (q < lim && mCap == mMax) {
+            // the whole rest of the tile is one event-free run; q is exactly the next tile's first position
+            if (oneShotZ && pl.kRel == INT_MAX && q >= b.relStart) pl.kRel = c + first_k_reaching(p, R, b.relStart, mMax);
+            b.lastPos = (int) __fma_rn((double) (mMax - 1), R, p);
+            h.p = q;
+            return;
+        }
+        const int k1 = first_k_reaching(p, R, lim, mCap);
+        const int m = min(k1, mCap);                                                    // frames in this segment; >= 1
+        if (oneShotZ && pl.kRel == INT_MAX && m > 1 && __fma_rn((double) (m - 1), R, p) >= b.relStart)
+            pl.kRel = c + first_k_reaching(p, R, b.relStart, m - 1);
+        const double plast = __fma_rn((double) (m - 1), R, p);
+        if (pos_explicit_step<JMODE>(h, b, ck, plast, f0 + c + m - 1, nframes, c + m, pl.kRel)) {
+            pl.nPos = c + m; pl.stopped = 1;
+            return;
+        }
+        c += m;
+    }
+}
+
+// Fallback: the same tile, frame by frame, writing each frame's position to tpd[i] (shared-memory slot).
+template <bool JMODE>
+__device__ __forceinline__ void walk_positions(VoiceHot& h, VoiceBlockCtl& b, const zl_block_clock& ck, int f0, int n, int nframes,
+                                               double* tpd, PosPlan& pl) {
+    pl.cb = n; pl.nPos = n; pl.kRel = INT_MAX; pl.stopped = 0; pl.irregular = 1;
+    for (int i = 0; i < n; ++i) {
+        const double p = h.p;
+        tpd[i] = p;
+        if (pos_explicit_step<JMODE>(h, b, ck, p, f0 + i, nframes, i + 1, pl.kRel)) { pl.nPos = i + 1; pl.stopped = 1; return; }
+    }
+}
+
+// Envelope of tile frames [0, nPos): constant when the ADSR sits in sustain (or, J-mode, idle) and no noteOff lands
+// inside; otherwise stepped frame by frame into te[].  Applies the release logic of :253-261.  Returns the frames
+// rendered (<= nPos) and sets `ended` when the ADSR going idle ends the voice (:258-261).
+template <bool JMODE, bool Q3>
+__device__ __forceinline__ int plan_envelope(VoiceHot& h, VoiceBlockCtl& b, const PosPlan& pl, float* te, float& envConst,
+                                             bool& fromTable, bool& ended) {
+    ended = false; fromTable = false;
+    const int nPos = pl.nPos;
+    const int lastNoteOffInc = pl.stopped ? nPos - 1 : nPos;      // the increment that stops the voice fires no noteOff
+    if (JMODE) {
+        if (h.adsrState == kIdle) { envConst = 0.0f; return nPos; }
+        if (h.adsrState == kSustain) { h.env = h.sustain; envConst = h.sustain; return nPos; }
+        fromTable = true;
+        for (int i = 0; i < nPos; ++i) te[i] = adsr_next(h);
+        return nPos;
+    }
+    if (h.adsrState == kSustain && pl.kRel >= nPos) {
+        h.env = h.sustain; envConst = h.sustain;
+        if (pl.kRel <= lastNoteOffInc) {                           // noteOff right after the tile's last frame
+            if (Q3 || !b.releaseArmed) { adsr_note_off(h); b.releaseArmed = 1; }
+            if (h.adsrState == kIdle) ended = true;
+        }
+        return nPos;
+    }
+    fromTable = true;
+    for (int i = 0; i < nPos; ++i) {
+        te[i] = adsr_next(h);
+        const int k = i + 1;
+        if (k >= pl.kRel && k <= lastNoteOffInc) {
+            if (Q3 || !b.releaseArmed) { adsr_note_off(h); b.releaseArmed = 1; }
+        }
+        if (h.adsrState == kIdle && !(pl.stopped && k == nPos)) { ended = true; return k; }
+    }
+    return nPos;
 }
 
 }  // namespace zl
