@@ -260,6 +260,10 @@ ZL_EXPORT int ZL_FN(total_counters)(zl_ctx* ctx, uint64_t* voice_frames, uint64_
 ZL_EXPORT int ZL_FN(last_voice_frames)(zl_ctx* ctx, uint64_t* voice_frames);
 /* Number of commands dropped (ring overflow lib/SamplerSynth.cpp:332-334 / unknown clip :330). */
 ZL_EXPORT int ZL_FN(dropped_commands)(zl_ctx* ctx, uint64_t* n);
+/* Optional device timing of the render kernel alone (bench.py roofline): while enabled, every zl_render brackets its
+ * kernel launch with CUDA events on the context stream; zl_kernel_time returns and clears the sum (ms) and count. */
+ZL_EXPORT int ZL_FN(kernel_timing)(zl_ctx* ctx, int32_t enable);
+ZL_EXPORT int ZL_FN(kernel_time)(zl_ctx* ctx, double* total_ms, uint64_t* launches);
 /* Kernel launches issued by this context so far (bench `gpu_launches`). */
 ZL_EXPORT int ZL_FN(launch_count)(zl_ctx* ctx, uint64_t* n);
 

@@ -10,7 +10,7 @@ from . import _capi
 from ._capi import *  # noqa: F401,F403  (constants + PODs)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libzl_b200.so")
+LIB_PATH = os.environ.get("ZL_B200_LIB") or os.path.join(_HERE, "libzl_b200.so")   # env: kernel-variant experiments
 _lib = None
 
 

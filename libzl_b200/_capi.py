@@ -100,6 +100,8 @@ SIGNATURES = {
     "last_voice_frames": (C.c_int, [_ctx, _P(C.c_uint64)]),
     "dropped_commands": (C.c_int, [_ctx, _P(C.c_uint64)]),
     "launch_count": (C.c_int, [_ctx, _P(C.c_uint64)]),
+    "kernel_timing": (C.c_int, [_ctx, C.c_int32]),
+    "kernel_time": (C.c_int, [_ctx, _P(C.c_double), _P(C.c_uint64)]),
     "thumb_build": (C.c_int, [_ctx, C.c_int32, C.c_int32]),
     "thumb_size": (C.c_int, [_ctx, C.c_int32, _P(C.c_int32), _P(C.c_int32)]),
     "thumb_read_level0": (C.c_int, [_ctx, C.c_int32, _P(C.c_int8)]),

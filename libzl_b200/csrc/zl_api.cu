@@ -114,9 +114,14 @@ struct zl_ctx {
     bool clipsDirty = true, busesDirty = true;
     // pinned staging
     void* h_stage = nullptr; size_t stageCap = 0;
-    zl_block_clock* h_clocks = nullptr;   // [2][max_blocks], double-buffered so render stays asynchronous
+    zl_block_clock* h_clocks = nullptr;   // unused since the slots below carry the clocks
     cudaEvent_t clkEv[2] = {nullptr, nullptr};
     int clkSlot = 0;
+    // per-launch input (clocks | per-bus command ranges | commands), double-buffered in pinned memory so zl_render
+    // never waits for the device: slot k is rewritten only after the render that used it two calls ago finished
+    void* h_slot[2] = {nullptr, nullptr}; void* d_slot[2] = {nullptr, nullptr}; size_t slotCap[2] = {0, 0};
+    // optional kernel timing (bench roofline): event pairs around each render_kernel launch
+    bool timing = false; std::vector<cudaEvent_t> tev; double timedMs = 0.0; uint64_t timedLaunches = 0;
     // outputs of the last render
     float* d_out[4] = {nullptr, nullptr, nullptr, nullptr};
     float* d_master = nullptr;
@@ -149,16 +154,6 @@ int invalid(zl_ctx* c, const char* what) { if (c) c->err = what; return ZL_ERR_I
 ClipHost* find_clip(zl_ctx* ctx, int id) {
     if (!ctx || id < 0 || id >= (int) ctx->clips.size() || !ctx->clips[(size_t) id].live) return nullptr;
     return &ctx->clips[(size_t) id];
-}
-
-int ensure_stage(zl_ctx* ctx, size_t bytes) {
-    if (bytes <= ctx->stageCap) return ZL_OK;
-    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
-    ctx->h_stage = nullptr; ctx->stageCap = 0;
-    const size_t cap = std::max(bytes, (size_t) 1 << 16);
-    CK(cudaMallocHost(&ctx->h_stage, cap));
-    ctx->stageCap = cap;
-    return ZL_OK;
 }
 
 template <typename T>
@@ -307,6 +302,8 @@ int zl_ctx_destroy(zl_ctx* ctx) {
     for (void* p : frees) if (p) cudaFree(p);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     if (ctx->h_clocks) cudaFreeHost(ctx->h_clocks);
+    for (int k = 0; k < 2; ++k) { if (ctx->h_slot[k]) cudaFreeHost(ctx->h_slot[k]); if (ctx->d_slot[k]) cudaFree(ctx->d_slot[k]); }
+    for (cudaEvent_t e : ctx->tev) cudaEventDestroy(e);
     for (cudaEvent_t e : ctx->clkEv) if (e) cudaEventDestroy(e);
     if (ctx->own) cudaStreamDestroy(ctx->own);
     delete ctx;
@@ -511,10 +508,13 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     }
     // commands: stable by arrival, then by block; ring capacity 256 per bus per period (lib/SamplerSynth.cpp:32,332-334)
     size_t nCmds = 0;
+    std::vector<int> count, begin;
+    std::vector<char> keep;
     if (!ctx->pending.empty()) {
         std::stable_sort(ctx->pending.begin(), ctx->pending.end(), [](const Pending& a, const Pending& b) { return a.block < b.block; });
-        std::vector<int> count(NB, 0), inBlock(NB, 0), last(NB, -1);
-        std::vector<char> keep(ctx->pending.size(), 0);
+        count.assign(NB, 0); begin.assign(NB, 0);
+        std::vector<int> inBlock(NB, 0), last(NB, -1);
+        keep.assign(ctx->pending.size(), 0);
         for (size_t i = 0; i < ctx->pending.size(); ++i) {
             const Pending& p = ctx->pending[i];
             const size_t gb = (size_t) p.session * ctx->cfg.buses_per_session + p.bus;
@@ -523,13 +523,35 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
             if (++inBlock[gb] > 256) { ctx->dropped++; continue; }
             keep[i] = 1; count[gb]++; nCmds++;
         }
-        rc = ensure_stage(ctx, sizeof(CmdDev) * nCmds);
-        if (rc != ZL_OK) return rc;
-        if (nCmds > ctx->cmdCap) { rc = ensure_dev(ctx, &ctx->d_cmds, &ctx->cmdCap, nCmds + 1024); if (rc != ZL_OK) return rc; }
-        std::vector<int> begin(NB, 0);
+    }
+    if (ctx->busesDirty) {
+        CK(cudaMemcpyAsync(ctx->d_buses, ctx->h_buses.data(), sizeof(BusDev) * NB, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));   // pageable source
+        ctx->busesDirty = false;
+    }
+    // one pinned slot = clocks | ranges | commands, one H2D copy, no host wait on the device
+    const int slot = ctx->clkSlot; ctx->clkSlot ^= 1;
+    const size_t offRanges = (sizeof(zl_block_clock) * (size_t) nblocks + 15) & ~size_t(15);
+    const size_t offCmds = offRanges + (nCmds ? ((sizeof(int32_t) * 2 * NB + 15) & ~size_t(15)) : 0);
+    const size_t slotBytes = offCmds + sizeof(CmdDev) * nCmds;
+    CK(cudaEventSynchronize(ctx->clkEv[slot]));   // the render that used this slot two calls ago is done
+    if (slotBytes > ctx->slotCap[slot]) {
+        if (ctx->h_slot[slot]) cudaFreeHost(ctx->h_slot[slot]);
+        if (ctx->d_slot[slot]) cudaFree(ctx->d_slot[slot]);
+        ctx->h_slot[slot] = nullptr; ctx->d_slot[slot] = nullptr; ctx->slotCap[slot] = 0;
+        const size_t cap = slotBytes + slotBytes / 2 + 4096;
+        CK(cudaMallocHost(&ctx->h_slot[slot], cap));
+        CK(cudaMalloc(&ctx->d_slot[slot], cap));
+        ctx->slotCap[slot] = cap;
+    }
+    unsigned char* hs = static_cast<unsigned char*>(ctx->h_slot[slot]);
+    unsigned char* ds = static_cast<unsigned char*>(ctx->d_slot[slot]);
+    memcpy(hs, clocks, sizeof(zl_block_clock) * (size_t) nblocks);
+    if (nCmds) {
+        int32_t* hr = reinterpret_cast<int32_t*>(hs + offRanges);
         int acc = 0;
-        for (size_t gb = 0; gb < NB; ++gb) { begin[gb] = acc; ctx->h_buses[gb].cmdBegin = acc; ctx->h_buses[gb].cmdCount = count[gb]; acc += count[gb]; }
-        CmdDev* hc = static_cast<CmdDev*>(ctx->h_stage);
+        for (size_t gb = 0; gb < NB; ++gb) { begin[gb] = acc; hr[2 * gb] = acc; hr[2 * gb + 1] = count[gb]; acc += count[gb]; }
+        CmdDev* hc = reinterpret_cast<CmdDev*>(hs + offCmds);
         for (size_t i = 0; i < ctx->pending.size(); ++i) {
             if (!keep[i]) continue;
             const Pending& p = ctx->pending[i];
@@ -538,30 +560,16 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
             memset(&d, 0, sizeof d);
             d.c = p.c; d.block = p.block; d.tick = p.tick;
         }
-        if (nCmds) {
-            CK(cudaMemcpyAsync(ctx->d_cmds, hc, sizeof(CmdDev) * nCmds, cudaMemcpyHostToDevice, st));
-            CK(cudaStreamSynchronize(st));   // the staging buffer may be reused by the next call
-        }
-        ctx->pending.clear();
-        ctx->busesDirty = true;
     }
-    if (ctx->busesDirty) {
-        CK(cudaMemcpyAsync(ctx->d_buses, ctx->h_buses.data(), sizeof(BusDev) * NB, cudaMemcpyHostToDevice, st));
-        CK(cudaStreamSynchronize(st));
-        for (BusDev& b : ctx->h_buses) { b.cmdBegin = 0; b.cmdCount = 0; }
-        ctx->busesDirty = false;
-    }
-    const int slot = ctx->clkSlot; ctx->clkSlot ^= 1;
-    zl_block_clock* hck = ctx->h_clocks + (size_t) slot * ctx->cfg.max_blocks;
-    zl_block_clock* dck = ctx->d_clocks + (size_t) slot * ctx->cfg.max_blocks;
-    CK(cudaEventSynchronize(ctx->clkEv[slot]));   // the render that used this slot two calls ago is done
-    memcpy(hck, clocks, sizeof(zl_block_clock) * (size_t) nblocks);
-    CK(cudaMemcpyAsync(dck, hck, sizeof(zl_block_clock) * (size_t) nblocks, cudaMemcpyHostToDevice, st));
+    ctx->pending.clear();
+    CK(cudaMemcpyAsync(ds, hs, slotBytes, cudaMemcpyHostToDevice, st));
     CK(cudaMemsetAsync(ctx->d_counters, 0, 2 * sizeof(unsigned long long), st));
+    const zl_block_clock* dck = reinterpret_cast<const zl_block_clock*>(ds);
 
     RenderParams P{};
     P.voices = ctx->d_voices; P.clips = ctx->d_clips; P.sliceBounds = ctx->d_slice; P.buses = ctx->d_buses;
-    P.cmds = ctx->d_cmds; P.clocks = dck; P.pow2 = ctx->d_pow2;
+    P.cmds = reinterpret_cast<const CmdDev*>(ds + offCmds); P.clocks = dck; P.pow2 = ctx->d_pow2;
+    P.cmdRange = nCmds ? reinterpret_cast<const int32_t*>(ds + offRanges) : nullptr;
     for (int w = 0; w < 4; ++w) P.out[w] = ctx->d_out[w];
     P.master = ctx->d_master; P.peaks = ctx->d_peaks; P.sumsq = ctx->d_sumsq;
     P.voiceFrames = ctx->d_counters;
@@ -569,7 +577,16 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     P.nSessions = ctx->cfg.n_sessions; P.B = ctx->cfg.buses_per_session; P.V = ctx->cfg.voices_per_bus;
     P.nClips = (int) ctx->clips.size();
     P.nblocks = nblocks; P.nframes = nframes; P.mode = ctx->cfg.mode; P.quirks = ctx->cfg.quirks;
-    CK(launch_render(P, st));
+    if (ctx->timing) {
+        cudaEvent_t e0, e1;
+        CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+        CK(cudaEventRecord(e0, st));
+        CK(launch_render(P, st));
+        CK(cudaEventRecord(e1, st));
+        ctx->tev.push_back(e0); ctx->tev.push_back(e1);
+    } else {
+        CK(launch_render(P, st));
+    }
     ctx->launches++;
     ctx->nblocks = nblocks; ctx->nframes = nframes;
     ctx->lvlCached = false; ctx->vfCached = false;
@@ -780,6 +797,26 @@ int zl_last_source_floats(zl_ctx* ctx, uint64_t* n) {
 }
 
 int zl_dropped_commands(zl_ctx* ctx, uint64_t* n) { if (!ctx || !n) return ZL_ERR_INVALID; *n = ctx->dropped; return ZL_OK; }
+int zl_kernel_timing(zl_ctx* ctx, int32_t enable) {
+    if (!ctx) return ZL_ERR_INVALID;
+    ctx->timing = enable != 0;
+    return ZL_OK;
+}
+int zl_kernel_time(zl_ctx* ctx, double* total_ms, uint64_t* launches) {
+    BIND();
+    for (size_t i = 0; i + 1 < ctx->tev.size(); i += 2) {
+        CK(cudaEventSynchronize(ctx->tev[i + 1]));
+        float ms = 0.0f;
+        CK(cudaEventElapsedTime(&ms, ctx->tev[i], ctx->tev[i + 1]));
+        ctx->timedMs += ms; ctx->timedLaunches++;
+        cudaEventDestroy(ctx->tev[i]); cudaEventDestroy(ctx->tev[i + 1]);
+    }
+    ctx->tev.clear();
+    if (total_ms) *total_ms = ctx->timedMs;
+    if (launches) *launches = ctx->timedLaunches;
+    ctx->timedMs = 0.0; ctx->timedLaunches = 0;
+    return ZL_OK;
+}
 int zl_launch_count(zl_ctx* ctx, uint64_t* n) { if (!ctx || !n) return ZL_ERR_INVALID; *n = ctx->launches; return ZL_OK; }
 
 // ---- WaveFormItem / juce::AudioThumbnail ------------------------------------------------------

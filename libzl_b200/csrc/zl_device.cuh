@@ -82,6 +82,7 @@ struct RenderParams {
     const int32_t* sliceBounds;
     BusDev* buses;           // [nbus]
     const CmdDev* cmds;
+    const int32_t* cmdRange; // [nbus][2] = (first command, count) of this launch per bus, or nullptr: no commands
     const zl_block_clock* clocks;   // [nblocks]
     const double* pow2;      // pow(2, k/12), k = -127..127 (host libm, like the reference's std::pow)
     float* out[4];           // raw, dry, fx1, fx2 planes [nbus][2][stride] or nullptr

@@ -25,26 +25,40 @@
 
 namespace zl {
 
-constexpr int kT = 64;               // frames per tile in the regular mode (multiple of 32)
+#ifndef ZL_MINB
+#define ZL_MINB 2
+#endif
+#ifndef ZL_KT
+#define ZL_KT 64
+#endif
+#ifndef ZL_VPW_SMALL
+#define ZL_VPW_SMALL 16
+#endif
+constexpr int kT = ZL_KT;            // frames per tile in the regular mode (multiple of 32)
 constexpr int kNC = kT / 32;         // 32-frame chunks per tile
 constexpr int kShort = 32;           // frames per tile when some lane of the warp needs the per-frame position walk
-constexpr int kTblFloats = (32 * (kT + 1) > 32 * 33 * 3) ? 32 * (kT + 1) : 32 * 33 * 3;
 
-// What G needs to know about one voice for one tile (shared memory, 48 bytes = 3 x LDS.128).
+// What G needs to know about one voice for one tile (shared memory, 64 bytes = 4 x LDS.128).
 struct __align__(16) TileDesc {
     double p0a, Ra, p0b, Rb;         // position segments a: frames [0, cb), b: frames [cb, nrend)
-    int32_t cb;
-    int32_t nrend;                   // frames of the tile this voice renders
-    float envConst;
-    int32_t kind;                    // bit 0: envelope from the table row; bit 1: positions from the slot row
+    float e0a, Ea, e0b, Eb;          // envelope segments a: frames [0, ce), b: frames [ce, ct); frames >= ct: table row
+    int32_t cb, ce, ct;
+    int32_t nrend;                   // frames of the tile this voice renders; bit 30: positions from the slot row
 };
+constexpr int kSlotBit = 1 << 30;
 
+// VPW = voices per warp (16 or 32): fewer voices per warp = more warps per session = more latency hiding.
+template <int VPW>
 struct __align__(16) WarpSmem {
-    // regular tiles: te[32][kT + 1] envelope rows.  short tiles: te[32][33] followed by ps[32][33] f64 position slots.
+    // regular tiles: te[VPW][kT + 1] envelope rows.  short tiles: te[VPW][33] followed by ps[VPW][33] f64 position slots.
+    static constexpr int kTblFloats = (VPW * (kT + 1) > VPW * 33 * 3) ? VPW * (kT + 1) : VPW * 33 * 3;
     float tbl[kTblFloats];
-    TileDesc td[32];
-    VoiceGather vg[32];
-    int   vpeak[32];                 // per-voice block peak of l + r (float bits, >= 0)   :213-216
+    TileDesc td[VPW];
+    VoiceGather vg[VPW];
+    VoiceHot hot[VPW];               // the voices' state machines between tiles (registers only while a lane plans)
+    VoiceBlockCtl ctl[VPW];
+    unsigned long long cntFrames[VPW], cntSrc[VPW];   // voice-frames / algorithmic source floats of the launch
+    int   vpeak[VPW];                // per-voice block peak of l + r (float bits, >= 0)   :213-216
     int   busPk[64];                 // per-bus block peaks [bus][2]
     double busSq[64];                // per-bus block sums of squares [bus][2]
 };
@@ -56,69 +70,84 @@ __device__ __forceinline__ float lerp_gain_z(float a, float b, float ia, float a
     return __fmul_rn(__fmul_rn(__fmul_rn(__fadd_rn(__fmul_rn(a, ia), __fmul_rn(b, alpha)), g), env), vol);
 }
 
-// One voice-frame: both taps, interpolation, gains, (Z) M/S pan.  J: juce_Sampler.cpp:128-152, Z: :198-211
-template <bool JMODE, bool Q1, bool STEREO>
-__device__ __forceinline__ void gather_voice(const VoiceGather& g, int pos, float alpha, float env, float& l, float& r) {
-    const float ia = __fsub_rn(1.0f, alpha);
-    if (JMODE) {
-        if (STEREO) {
-            const float2 a = __ldg(reinterpret_cast<const float2*>(g.data) + pos);
-            const float2 b = __ldg(reinterpret_cast<const float2*>(g.data) + pos + 1);
-            l = __fadd_rn(__fmul_rn(a.x, ia), __fmul_rn(b.x, alpha));
-            r = __fadd_rn(__fmul_rn(a.y, ia), __fmul_rn(b.y, alpha));
-        } else {
-            const float a = __ldg(g.data + pos), b = __ldg(g.data + pos + 1);
-            l = __fadd_rn(__fmul_rn(a, ia), __fmul_rn(b, alpha));
-            r = l;
-        }
-        const float ge = __fmul_rn(g.gain, env);
-        l = __fmul_rn(l, ge);
-        r = __fmul_rn(r, ge);
-        return;
-    }
-    l = 0.0f; r = 0.0f;
-    if (g.sampleDuration > pos) {
-        if (STEREO) {
-            const float2 a = __ldg(reinterpret_cast<const float2*>(g.data) + pos);
-            const float2 b = __ldg(reinterpret_cast<const float2*>(g.data) + pos + 1);
-            l = lerp_gain_z<Q1>(a.x, b.x, ia, alpha, g.gain, env, g.vol);
-            r = lerp_gain_z<Q1>(a.y, b.y, ia, alpha, g.gain, env, g.vol);
-        } else {
-            const float a = __ldg(g.data + pos), b = __ldg(g.data + pos + 1);
-            l = lerp_gain_z<Q1>(a, b, ia, alpha, g.gain, env, g.vol);
-            r = l;
-        }
-    }
-    const float m = __fmul_rn(0.5f, __fadd_rn(l, r));   // :208 (0.5*(l+r) in f64 is exact)
-    const float sd = __fsub_rn(l, r);
-    l = __fadd_rn(__fmul_rn(g.lPan, m), sd);
-    r = __fsub_rn(__fmul_rn(g.rPan, m), sd);
-}
+// The gather of one voice x one tile is split in two so the loads of several voice-steps are in flight together:
+// gather_issue computes (pos, alpha, env) per lane-frame and issues both tap loads; gather_finish does the arithmetic.
+struct Taps {
+    float2 a[kNC], b[kNC];           // taps at pos and pos + 1 (mono: .y duplicates .x, so r == l falls out of the same math)
+    float alpha[kNC], env[kNC];
+    unsigned ok;                     // bit ch: this lane's frame of chunk ch is rendered
+};
 
-// One voice x one tile in G: lane = frame within each 32-frame chunk.  Everything the branches test is warp-uniform.
-template <bool JMODE, bool Q1, bool STEREO>
-__device__ __forceinline__ float gather_tile(const TileDesc& d, const VoiceGather& g, const float* terow, const double* psrow,
-                                             int lane, double laneD, float (&accL)[kNC], float (&accR)[kNC]) {
-    float vmax = 0.0f;
-    const bool single = d.cb >= d.nrend && !(d.kind & 2);
+template <bool JMODE>
+__device__ __forceinline__ void gather_issue(const TileDesc& d, const VoiceGather& g, const float* terow, const double* psrow,
+                                             int lane, double laneD, Taps& t) {
+    t.ok = 0;
+    const int nrend = d.nrend & ~kSlotBit;
+    const bool slotPos = (d.nrend & kSlotBit) != 0;
+    const bool single = d.cb >= nrend && !slotPos;
+    const bool envConst = d.ce >= nrend && d.ct >= nrend && d.Ea == 0.0f;
 #pragma unroll
     for (int ch = 0; ch < kNC; ++ch) {
         const int c = ch * 32 + lane;
-        if (c < d.nrend) {
-            double p;
-            if (single) p = __fma_rn(__dadd_rn(laneD, (double) (ch * 32)), d.Ra, d.p0a);
-            else if (d.kind & 2) p = psrow[c];
-            else {
-                const bool sb = c >= d.cb;
-                p = __fma_rn((double) (c - (sb ? d.cb : 0)), sb ? d.Rb : d.Ra, sb ? d.p0b : d.p0a);
+        const bool v = c < nrend;
+        double p;
+        if (single) p = __fma_rn(__dadd_rn(laneD, (double) (ch * 32)), d.Ra, d.p0a);
+        else if (slotPos) p = v ? psrow[c] : 0.0;
+        else {
+            const bool sb = c >= d.cb;
+            p = __fma_rn((double) (c - (sb ? d.cb : 0)), sb ? d.Rb : d.Ra, sb ? d.p0b : d.p0a);
+        }
+        // (int) p and p - (int) p without int<->f64 conversions: p + 2^52 rounded down is floor(p) + 2^52
+        const double fl = __dadd_rd(p, 4503599627370496.0);
+        const int pos = __double2loint(fl);
+        t.alpha[ch] = __double2float_rn(__dsub_rn(p, __dsub_rn(fl, 4503599627370496.0)));
+        float env;
+        if (envConst) env = d.e0a;
+        else if (c >= d.ct) env = v ? terow[c] : 0.0f;
+        else {
+            const bool sb = c >= d.ce;
+            env = __fmaf_rn((float) (c - (sb ? d.ce : 0)), sb ? d.Eb : d.Ea, sb ? d.e0b : d.e0a);   // exact: see zl_voice.cuh
+        }
+        t.env[ch] = env;
+        const bool inR = v && (JMODE || g.sampleDuration > pos);      // Z: taps outside the sample read as 0  (:204-205)
+        t.a[ch] = make_float2(0.0f, 0.0f); t.b[ch] = t.a[ch];
+        if (inR) {
+            if (g.nch > 1) {
+                t.a[ch] = __ldg(reinterpret_cast<const float2*>(g.data) + pos);
+                t.b[ch] = __ldg(reinterpret_cast<const float2*>(g.data) + pos + 1);
+            } else {
+                const float a = __ldg(g.data + pos), b = __ldg(g.data + pos + 1);
+                t.a[ch] = make_float2(a, a); t.b[ch] = make_float2(b, b);
             }
-            // (int) p and p - (int) p without int<->f64 conversions: p + 2^52 rounded down is floor(p) + 2^52
-            const double t = __dadd_rd(p, 4503599627370496.0);
-            const int pos = __double2loint(t);
-            const float alpha = __double2float_rn(__dsub_rn(p, __dsub_rn(t, 4503599627370496.0)));
-            const float env = (d.kind & 1) ? terow[c] : d.envConst;
-            float l, r;
-            gather_voice<JMODE, Q1, STEREO>(g, pos, alpha, env, l, r);
+        }
+        if (v) t.ok |= 1u << ch;
+    }
+}
+
+// Interpolation, gains, (Z) M/S pan, bus accumulate.  J: juce_Sampler.cpp:128-152, Z: lib/SamplerSynthVoice.cpp:198-221
+template <bool JMODE, bool Q1>
+__device__ __forceinline__ float gather_finish(const VoiceGather& g, const Taps& t, float (&accL)[kNC], float (&accR)[kNC]) {
+    float vmax = 0.0f;
+#pragma unroll
+    for (int ch = 0; ch < kNC; ++ch) {
+        const float alpha = t.alpha[ch], env = t.env[ch];
+        const float ia = __fsub_rn(1.0f, alpha);
+        float l, r;
+        if (JMODE) {
+            l = __fadd_rn(__fmul_rn(t.a[ch].x, ia), __fmul_rn(t.b[ch].x, alpha));
+            r = __fadd_rn(__fmul_rn(t.a[ch].y, ia), __fmul_rn(t.b[ch].y, alpha));
+            const float ge = __fmul_rn(g.gain, env);
+            l = __fmul_rn(l, ge);
+            r = __fmul_rn(r, ge);
+        } else {
+            l = lerp_gain_z<Q1>(t.a[ch].x, t.b[ch].x, ia, alpha, g.gain, env, g.vol);
+            r = lerp_gain_z<Q1>(t.a[ch].y, t.b[ch].y, ia, alpha, g.gain, env, g.vol);
+            const float m = __fmul_rn(0.5f, __fadd_rn(l, r));   // :208 (0.5*(l+r) in f64 is exact)
+            const float sd = __fsub_rn(l, r);
+            l = __fadd_rn(__fmul_rn(g.lPan, m), sd);
+            r = __fsub_rn(__fmul_rn(g.rPan, m), sd);
+        }
+        if (t.ok & (1u << ch)) {
             accL[ch] = __fadd_rn(accL[ch], l);
             accR[ch] = __fadd_rn(accR[ch], r);
             vmax = fmaxf(vmax, __fadd_rn(l, r));
@@ -173,9 +202,9 @@ __device__ __forceinline__ void plan_restore(const PlanUndo& u, VoiceHot& h, Voi
 }
 
 // CFG = mode << 3 | quirks (quirks forced to 0 in J-mode): compile-time so the frame loops carry no mode tests.
-// MAXT: 256 (sessions of up to 256 voices, <= 128 registers) or 1024.
-template <int CFG, int MAXT>
-__global__ void __launch_bounds__(MAXT, MAXT == 256 ? 2 : 1)
+// MAXT: 256 threads (3 CTAs per SM, <= 85 registers) or 1024.
+template <int CFG, int MAXT, int VPW>
+__global__ void __launch_bounds__(MAXT, MAXT == 256 ? ZL_MINB : 1)
 render_kernel(const RenderParams P) {
     constexpr bool JMODE = (CFG >> 3) == ZL_MODE_J;
     constexpr bool Q1 = (CFG & ZL_Q1_TAP_GAIN) != 0, Q2 = (CFG & ZL_Q2_PREINC) != 0, Q3 = (CFG & ZL_Q3_RENOTEOFF) != 0;
@@ -188,38 +217,50 @@ render_kernel(const RenderParams P) {
     const int nwarps = blockDim.x >> 5;
     const unsigned FULL = 0xffffffffu;
 
-    WarpSmem& ws = reinterpret_cast<WarpSmem*>(smemRaw)[warp];
-    float* stage = reinterpret_cast<float*>(smemRaw + sizeof(WarpSmem) * nwarps);   // [B][2][kT] master staging
+    WarpSmem<VPW>& ws = reinterpret_cast<WarpSmem<VPW>*>(smemRaw)[warp];
+    // master chain: pre[warp][buf][ch][kT] running sums handed from warp to warp, pub/con[warp] sequence flags
+    float* pre = reinterpret_cast<float*>(smemRaw + sizeof(WarpSmem<VPW>) * nwarps);
+    volatile int* pub = reinterpret_cast<volatile int*>(pre + (size_t) nwarps * 4 * kT);
+    volatile int* con = pub + nwarps;
+    // this warp's dry outs of the current tile, [bus of the warp][ch][kT], until the chain reaches it
+    float* own = reinterpret_cast<float*>(const_cast<int*>(con + nwarps)) + (size_t) warp * (VPW / P.V) * 2 * kT;
 
     // ownership: this lane's voice / bus; the warp's buses
-    const bool hasVoice = tid < NV;
-    const int bi = tid / V, slot = tid - bi * V;          // bus within the session, voice slot within the bus
+    const int vIdx = warp * VPW + lane;                   // lanes >= VPW own no voice; they only help in G
+    const bool ownsRow = lane < VPW;
+    const bool hasVoice = ownsRow && vIdx < NV;
+    const int bi = vIdx / V, slot = vIdx - bi * V;        // bus within the session, voice slot within the bus
     const int gb = s * B + bi;
-    const int busesPerWarp = 32 / V;
+    const int busesPerWarp = VPW / V;
     const int warpBus0 = warp * busesPerWarp;
-    VoiceDev* rec = P.voices + (size_t) s * NV + tid;
-
-    VoiceHot h;
-    h.p = 0.0; h.ratio = 0.0; h.relDen = 1.0; h.srcLen = 1.0; h.nextLoopTick = 0; h.nextLoopUsecs = 0;
-    h.env = 0.f; h.rRate = 0.f; h.aRate = 0.f; h.dRate = 0.f; h.sustain = 0.f; h.release = 0.f; h.gain = 0.f;
-    h.posGain = 0.f; h.posProgress = 0.f; h.adsrState = kIdle; h.flags = 0; h.sound = -1; h.clip = -1; h.slice = -1; h.looping = 0;
-    int cmdCur = 0, cmdEnd = 0, busEnabled = 0;
-    if (hasVoice) {
-        hot_load(h, *rec);
-        const BusDev& bus = P.buses[gb];
-        cmdCur = bus.cmdBegin; cmdEnd = cmdCur + bus.cmdCount; busEnabled = bus.enabled;
-    }
-    unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
+    VoiceDev* rec = P.voices + (size_t) s * NV + vIdx;
     const double laneD = (double) lane;
 
+    int cmdCur = 0, cmdEnd = 0, busEnabled = 0;
+    if (ownsRow) {
+        VoiceHot h;
+        h.p = 0.0; h.ratio = 0.0; h.relDen = 1.0; h.srcLen = 1.0; h.nextLoopTick = 0; h.nextLoopUsecs = 0;
+        h.env = 0.f; h.rRate = 0.f; h.aRate = 0.f; h.dRate = 0.f; h.sustain = 0.f; h.release = 0.f; h.gain = 0.f;
+        h.posGain = 0.f; h.posProgress = 0.f; h.adsrState = kIdle; h.flags = 0; h.sound = -1; h.clip = -1; h.slice = -1; h.looping = 0;
+        if (hasVoice) {
+            hot_load(h, *rec);
+            if (P.cmdRange) { cmdCur = P.cmdRange[2 * gb]; cmdEnd = cmdCur + P.cmdRange[2 * gb + 1]; }
+            busEnabled = P.buses[gb].enabled;
+        }
+        ws.hot[lane] = h;
+        ws.cntFrames[lane] = 0; ws.cntSrc[lane] = 0;
+    }
+    if (tid < nwarps) { pub[tid] = 0; con[tid] = 0; }
+    __syncthreads();
+    int tileSeq = 0;
+
     for (int blk = 0; blk < P.nblocks; ++blk) {
-        const zl_block_clock ck = P.clocks[blk];
         const int64_t off = (int64_t) blk * nframes;
 
         // ---- commands of this block: SamplerChannel::process ring drain   lib/SamplerSynth.cpp:118-122 ----------
         const bool hasCmd = hasVoice && cmdCur < cmdEnd && P.cmds[cmdCur].block == blk;
         if (__any_sync(FULL, hasCmd)) {
-            if (hasCmd) hot_store(h, *rec);
+            if (hasCmd) hot_store(ws.hot[lane], *rec);
             __syncwarp();
             if (hasCmd) {
                 int cur = cmdCur;
@@ -230,68 +271,81 @@ render_kernel(const RenderParams P) {
                 cmdCur = cur;
             }
             __syncwarp();
-            if (hasCmd) hot_load(h, *rec);
+            if (hasCmd) hot_load(ws.hot[lane], *rec);
         }
 
         // ---- block prelude -------------------------------------------------------------------------------
-        VoiceBlockCtl bc;
-        bc.stopD = 0.0; bc.startD = 0.0; bc.relStart = 0.0; bc.usPerFrame = 0.0; bc.lengthInTicks = 0; bc.fWrap = nframes;
-        bc.beatAligned = 0; bc.spanStart = 0; bc.lastPos = 0; bc.span = 0; bc.nch = 0; bc.clipFrames = 0; bc.releaseArmed = 0;
         bool active = false;
-        {
+        if (ownsRow) {
+            const zl_block_clock ck = P.clocks[blk];
+            VoiceHot h = ws.hot[lane];
+            VoiceBlockCtl bc;
+            bc.stopD = 0.0; bc.startD = 0.0; bc.relStart = 0.0; bc.usPerFrame = 0.0; bc.lengthInTicks = 0; bc.fWrap = nframes;
+            bc.beatAligned = 0; bc.spanStart = 0; bc.lastPos = 0; bc.span = 0; bc.nch = 0; bc.clipFrames = 0; bc.releaseArmed = 0;
             VoiceGather g;
             g.data = nullptr; g.sampleDuration = 0; g.nch = 0; g.gain = g.vol = g.lPan = g.rPan = 0.0f;
             if (hasVoice && busEnabled && (h.flags & VF_PLAYING))                       // :136-140
                 active = voice_block_begin<JMODE>(h, P, ck, nframes, bc, g);
-            ws.vg[lane] = g;
-            ws.vpeak[lane] = 0;
-            ws.busPk[lane] = 0; ws.busPk[lane + 32] = 0;
-            ws.busSq[lane] = 0.0; ws.busSq[lane + 32] = 0.0;
+            ws.hot[lane] = h; ws.ctl[lane] = bc;
+            ws.vg[lane] = g; ws.vpeak[lane] = 0;
         }
+        ws.busPk[lane] = 0; ws.busPk[lane + 32] = 0;
+        ws.busSq[lane] = 0.0; ws.busSq[lane + 32] = 0.0;
         const bool walked = active;
         int nrendBlock = 0;
         __syncwarp();
 
         for (int t0 = 0; t0 < nframes; t0 += kT) {
-            // ---- W: every lane plans its voice's tile ----------------------------------------------------
             const int nT = min(kT, nframes - t0);
-            PosPlan pl;
-            pl.p0a = 0.0; pl.Ra = 0.0; pl.p0b = 0.0; pl.Rb = 0.0; pl.cb = nT; pl.nPos = 0; pl.kRel = INT_MAX; pl.stopped = 0; pl.irregular = 0;
-            PlanUndo undo;
-            plan_save(undo, h, bc);
-            if (active) plan_positions<JMODE>(h, bc, ck, t0, nT, nframes, pl);
-            // a lane that cannot express its tile in closed form makes the warp cover it in 32-frame sub-tiles
-            const bool shortTile = __any_sync(FULL, active && pl.irregular);
-            if (shortTile && active) plan_restore(undo, h, bc);
+            ++tileSeq;
+            // ---- W: every owner lane plans its voice's tile (state comes from / returns to shared memory) ---------
+            // A lane that cannot express its tile in closed form makes the warp cover it in 32-frame sub-tiles.
+            bool irregular = false;
+            if (active) {
+                const zl_block_clock ck = P.clocks[blk];
+                VoiceHot h = ws.hot[lane];
+                VoiceBlockCtl bc = ws.ctl[lane];
+                PosPlan pl;
+                plan_positions<JMODE>(h, bc, ck, t0, nT, nframes, pl);
+                irregular = pl.irregular != 0;
+            }
+            const bool shortTile = __any_sync(FULL, irregular);
             const int nn = shortTile ? kShort : nT;
             const int teStride = shortTile ? 33 : kT + 1;
-            float* te = ws.tbl + lane * teStride;
-            double* ps = reinterpret_cast<double*>(ws.tbl + 32 * 33) + lane * 33;
           for (int s0 = 0; s0 < nT; s0 += nn) {
             const int n = min(nn, nT - s0);
-            if (shortTile && active) {
-                plan_save(undo, h, bc);
-                plan_positions<JMODE>(h, bc, ck, t0 + s0, n, nframes, pl);
-                if (pl.irregular) {
-                    plan_restore(undo, h, bc);
-                    walk_positions<JMODE>(h, bc, ck, t0 + s0, n, nframes, ps, pl);
-                }
-            }
             int cnt = 0;
-            {
+            if (ownsRow) {
                 TileDesc d;
-                d.p0a = pl.p0a; d.Ra = pl.Ra; d.p0b = pl.p0b; d.Rb = pl.Rb; d.cb = pl.cb; d.nrend = 0; d.envConst = 0.0f; d.kind = 0;
+                d.p0a = 0.0; d.Ra = 0.0; d.p0b = 0.0; d.Rb = 0.0; d.e0a = 0.0f; d.Ea = 0.0f; d.e0b = 0.0f; d.Eb = 0.0f;
+                d.cb = n; d.ce = n; d.ct = INT_MAX; d.nrend = 0;
                 if (active) {
-                    bool fromTable, ended;
-                    cnt = plan_envelope<JMODE, Q3>(h, bc, pl, te, d.envConst, fromTable, ended);
-                    d.nrend = cnt;
-                    d.kind = (fromTable ? 1 : 0) | (pl.irregular ? 2 : 0);
+                    const zl_block_clock ck = P.clocks[blk];
+                    VoiceHot h = ws.hot[lane];
+                    VoiceBlockCtl bc = ws.ctl[lane];
+                    float* te = ws.tbl + lane * teStride;
+                    double* ps = reinterpret_cast<double*>(ws.tbl + VPW * 33) + lane * 33;
+                    PosPlan pl;
+                    PlanUndo undo;
+                    plan_save(undo, h, bc);
+                    plan_positions<JMODE>(h, bc, ck, t0 + s0, n, nframes, pl);
+                    if (pl.irregular) {
+                        plan_restore(undo, h, bc);
+                        walk_positions<JMODE>(h, bc, ck, t0 + s0, n, nframes, ps, pl);
+                    }
+                    d.p0a = pl.p0a; d.Ra = pl.Ra; d.p0b = pl.p0b; d.Rb = pl.Rb; d.cb = pl.cb;
+                    EnvPlan ep;
+                    bool ended;
+                    cnt = plan_envelope<JMODE, Q3>(h, bc, pl, te, ep, ended);
+                    d.e0a = ep.e0a; d.Ea = ep.Ea; d.e0b = ep.e0b; d.Eb = ep.Eb; d.ce = ep.ce; d.ct = ep.ct;
+                    d.nrend = cnt | (pl.irregular ? kSlotBit : 0);
                     if (ended && cnt < pl.nPos) {                          // the ADSR ran out before the tile did: p is frame cnt's
                         if (pl.irregular) h.p = ps[cnt];
                         else h.p = cnt >= pl.cb ? __fma_rn((double) (cnt - pl.cb), pl.Rb, pl.p0b) : __fma_rn((double) cnt, pl.Ra, pl.p0a);
                     }
                     if (pl.stopped || ended) { voice_stop(h, false); active = false; }
                     else prefetch_span_l2(ws.vg[lane].data, bc.nch, bc.clipFrames, h.p, h.ratio, kT);
+                    ws.hot[lane] = h; ws.ctl[lane] = bc;
                 }
                 ws.td[lane] = d;
             }
@@ -299,6 +353,8 @@ render_kernel(const RenderParams P) {
             __syncwarp();
 
             // ---- G: lane = frame -----------------------------------------------------------------------------
+            const bool chain = P.master != nullptr;
+            const double* psbase = reinterpret_cast<const double*>(ws.tbl + VPW * 33);
             for (int bl = 0; bl < busesPerWarp; ++bl) {
                 const int wb = warpBus0 + bl;               // bus of the session
                 if (wb >= B) break;
@@ -306,21 +362,37 @@ render_kernel(const RenderParams P) {
                 float accL[kNC], accR[kNC];
 #pragma unroll
                 for (int ch = 0; ch < kNC; ++ch) { accL[ch] = 0.0f; accR[ch] = 0.0f; }
-                for (int vs = 0; vs < V; ++vs) {
-                    const int row = bl * V + vs;
-                    const TileDesc d = ws.td[row];
-                    if (d.nrend <= 0) continue;                                // warp-uniform: voice silent in this tile
-                    const VoiceGather g = ws.vg[row];
-                    const float* terow = ws.tbl + row * teStride;
-                    const double* psrow = reinterpret_cast<const double*>(ws.tbl + 32 * 33) + row * 33;
-                    const float vmax = g.nch > 1 ? gather_tile<JMODE, Q1, true>(d, g, terow, psrow, lane, laneD, accL, accR)
-                                                 : gather_tile<JMODE, Q1, false>(d, g, terow, psrow, lane, laneD, accL, accR);
-                    if (!JMODE) {                                              // block peak of the voice  :213-216
-                        const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));   // vmax >= +0: int order == float order
-                        if (lane == 0) atomicMax(&ws.vpeak[row], pk);
+                for (int vs = 0; vs < V; vs += 2) {
+                    const int row0 = bl * V + vs;
+                    const bool two = vs + 1 < V;
+                    const int row1 = two ? row0 + 1 : row0;
+                    const TileDesc d0 = ws.td[row0], d1 = ws.td[row1];
+#ifdef ZL_EXP_NOG
+                    const bool on0 = false, on1 = false;
+#else
+                    const bool on0 = (d0.nrend & ~kSlotBit) > 0, on1 = two && (d1.nrend & ~kSlotBit) > 0;  // warp-uniform
+#endif
+                    if (!on0 && !on1) continue;
+                    const VoiceGather g0 = ws.vg[row0], g1 = ws.vg[row1];
+                    Taps t0v, t1v;
+                    if (on0) gather_issue<JMODE>(d0, g0, ws.tbl + row0 * teStride, psbase + row0 * 33, lane, laneD, t0v);
+                    if (on1) gather_issue<JMODE>(d1, g1, ws.tbl + row1 * teStride, psbase + row1 * 33, lane, laneD, t1v);
+                    if (on0) {
+                        const float vmax = gather_finish<JMODE, Q1>(g0, t0v, accL, accR);
+                        if (!JMODE) {                                          // block peak of the voice  :213-216
+                            const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));   // vmax >= +0: int order == float order
+                            if (lane == 0) atomicMax(&ws.vpeak[row0], pk);
+                        }
+                    }
+                    if (on1) {
+                        const float vmax = gather_finish<JMODE, Q1>(g1, t1v, accL, accR);
+                        if (!JMODE) {
+                            const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));
+                            if (lane == 0) atomicMax(&ws.vpeak[row1], pk);
+                        }
                     }
                 }
-                // raw SamplerChannel ports, then JackPassthrough, meters, master staging
+                // raw SamplerChannel ports, then JackPassthrough, meters, master running sum
                 const zl_passthrough_params pt = P.buses[gbw].pt;
                 int pkL = 0, pkR = 0;
                 double sqL = 0.0, sqR = 0.0;
@@ -355,9 +427,9 @@ render_kernel(const RenderParams P) {
                         sqL += (double) __fmul_rn(dL, dL);                     // juce_AudioSampleBuffer.h:1087-1095
                         sqR += (double) __fmul_rn(dR, dR);
                     }
-                    if (P.master && c < nn) { stage[((size_t) wb * 2) * kT + s0 + c] = dL; stage[((size_t) wb * 2 + 1) * kT + s0 + c] = dR; }
+                    if (chain && c < n) { own[((size_t) bl * 2) * kT + s0 + c] = dL; own[((size_t) bl * 2 + 1) * kT + s0 + c] = dR; }
                 }
-                if (Q2 && t0 + s0 == 0 && lane == 0) {                              // index 0 is never accumulated into (:218): stays zero
+                if (Q2 && t0 + s0 == 0 && lane == 0) {                         // index 0 is never accumulated into (:218): stays zero
                     for (int w = 0; w < 4; ++w)
                         if (P.out[w]) { P.out[w][((int64_t) gbw * 2) * P.stride + off] = 0.0f; P.out[w][((int64_t) gbw * 2 + 1) * P.stride + off] = 0.0f; }
                 }
@@ -376,26 +448,46 @@ render_kernel(const RenderParams P) {
             }
             __syncwarp();
           }
-            // ---- JACK port mix of the session (sum of the dry outs in bus order) ------------------------------
-            if (P.master) {
-                __syncthreads();
-                for (int t2 = tid; t2 < 2 * kT; t2 += blockDim.x) {
-                    const int ch = t2 / kT, c = t2 - ch * kT;
-                    const float* st = stage + ch * kT + c;
-                    float m = st[0];
-                    for (int b2 = 1; b2 < B; ++b2) m = __fadd_rn(m, st[(size_t) b2 * 2 * kT]);
-                    const int j = t0 + c + QS;
-                    if (c < nT && j < nframes) P.master[((int64_t) s * 2 + ch) * P.stride + off + j] = m;
-                    if (Q2 && t0 == 0 && c == 0) P.master[((int64_t) s * 2 + ch) * P.stride + off] = 0.0f;
+            // ---- JACK port mix of the session: the dry outs summed in bus order (copy the first, add the others) ----
+            // The running sum travels from warp to warp through double-buffered shared rows; a warp joins the chain
+            // only after its own tile is done, so nobody waits on a neighbour in the hot loop.
+            if (P.master != nullptr) {
+                const bool lastWarp = warp == nwarps - 1;
+                const int seq = tileSeq, buf = tileSeq & 1;
+                if (lane == 0) {
+                    if (warp > 0) while (pub[warp - 1] < seq) __nanosleep(32);
+                    if (!lastWarp) while (con[warp + 1] < seq - 2) __nanosleep(32);
                 }
-                __syncthreads();
+                __syncwarp();
+                const float* preIn = pre + ((size_t) (warp > 0 ? warp - 1 : 0) * 2 + buf) * 2 * kT;
+                float* preOut = pre + ((size_t) warp * 2 + buf) * 2 * kT;
+                const int nb = min(busesPerWarp, B - warpBus0);
+                for (int idx = lane; idx < 2 * kT; idx += 32) {
+                    const int ch = idx / kT, c = idx - ch * kT;
+                    float m = own[(size_t) ch * kT + c];
+                    if (warp > 0) m = __fadd_rn(preIn[idx], m);
+                    for (int b2 = 1; b2 < nb; ++b2) m = __fadd_rn(m, own[((size_t) b2 * 2 + ch) * kT + c]);
+                    if (lastWarp) {
+                        const int j = t0 + c + QS;
+                        if (c < nT && j < nframes) P.master[((int64_t) s * 2 + ch) * P.stride + off + j] = m;
+                        if (Q2 && t0 == 0 && c == 0) P.master[((int64_t) s * 2 + ch) * P.stride + off] = 0.0f;
+                    } else preOut[idx] = m;
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    __threadfence_block();
+                    if (!lastWarp) pub[warp] = seq;                            // our running sum of this tile is complete
+                    if (warp > 0) con[warp] = seq;                             // and the previous warp's buffer is drained
+                }
             }
         }
 
         // ---- block epilogue ----------------------------------------------------------------------------------
         if (walked) {
-            nVoiceFrames += (unsigned long long) nrendBlock;
-            if (nrendBlock > 0) nSrcFloats += (unsigned long long) (bc.span + (uint32_t) (bc.lastPos + 2 - bc.spanStart)) * (unsigned) bc.nch;
+            VoiceHot& h = ws.hot[lane];
+            const VoiceBlockCtl& bc = ws.ctl[lane];
+            ws.cntFrames[lane] += (unsigned long long) nrendBlock;
+            if (nrendBlock > 0) ws.cntSrc[lane] += (unsigned long long) (bc.span + (uint32_t) (bc.lastPos + 2 - bc.spanStart)) * (unsigned) bc.nch;
             // positions model update   lib/SamplerSynthVoice.cpp:265-267
             if (h.clip >= 0 && (JMODE || (h.flags & VF_HAS_POSID))) {
                 h.posGain = JMODE ? 0.0f : __fmul_rn(__int_as_float(ws.vpeak[lane]), 0.5f);
@@ -411,9 +503,10 @@ render_kernel(const RenderParams P) {
     }
 
     // ---- write the voice records back, account the launch -------------------------------------------------------
+    unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
     if (hasVoice) {
-        hot_store(h, *rec);
-        if (slot == 0) { BusDev& bus = P.buses[gb]; bus.cmdBegin = cmdCur; bus.cmdCount = cmdEnd - cmdCur; }
+        hot_store(ws.hot[lane], *rec);
+        nVoiceFrames = ws.cntFrames[lane]; nSrcFloats = ws.cntSrc[lane];
     }
     for (int o = 16; o > 0; o >>= 1) {
         nVoiceFrames += __shfl_down_sync(FULL, nVoiceFrames, o);
@@ -426,31 +519,37 @@ render_kernel(const RenderParams P) {
 }
 
 // ---------------------------------------------------------------------------------------------
-static int render_threads(int B, int V) { return ((B * V + 31) / 32) * 32; }
+static int voices_per_warp(int B, int V) { return (ZL_VPW_SMALL == 16 && V <= 16 && B * V <= 512) ? 16 : 32; }
+static int render_threads(int B, int V) { const int w = voices_per_warp(B, V); return ((B * V + w - 1) / w) * 32; }
 
 size_t render_smem_bytes(int B, int V, int nframes) {
     (void) nframes;
     const int nv = B * V;
-    if (nv > 1024) return (size_t) 1 << 30;                 // one thread per voice of the session: reported as "does not fit"
-    return sizeof(WarpSmem) * (size_t) (render_threads(B, V) / 32) + sizeof(float) * (size_t) B * 2 * kT;
+    if (nv > 1024) return (size_t) 1 << 30;                 // reported as "does not fit"
+    const size_t per = voices_per_warp(B, V) == 16 ? sizeof(WarpSmem<16>) : sizeof(WarpSmem<32>);
+    const size_t nw = (size_t) (render_threads(B, V) / 32);
+    return per * nw + sizeof(float) * nw * 4 * kT + sizeof(int) * 2 * nw                      // + master chain buffers and flags
+           + sizeof(float) * nw * (size_t) (voices_per_warp(B, V) / V) * 2 * kT;            // + each warp's own dry stage
 }
 
-template <int CFG, int MAXT>
+template <int CFG, int MAXT, int VPW>
 static cudaError_t launch_cfg_t(const RenderParams& P, cudaStream_t stream) {
     const size_t smem = render_smem_bytes(P.B, P.V, P.nframes);
     static size_t configured = 0;
     if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(render_kernel<CFG, MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        cudaError_t e = cudaFuncSetAttribute(render_kernel<CFG, MAXT, VPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    render_kernel<CFG, MAXT><<<P.nSessions, render_threads(P.B, P.V), smem, stream>>>(P);
+    render_kernel<CFG, MAXT, VPW><<<P.nSessions, render_threads(P.B, P.V), smem, stream>>>(P);
     return cudaGetLastError();
 }
 
 template <int CFG>
 static cudaError_t launch_cfg(const RenderParams& P, cudaStream_t stream) {
-    return render_threads(P.B, P.V) <= 256 ? launch_cfg_t<CFG, 256>(P, stream) : launch_cfg_t<CFG, 1024>(P, stream);
+    const int t = render_threads(P.B, P.V);
+    if (voices_per_warp(P.B, P.V) == 16) return t <= 256 ? launch_cfg_t<CFG, 256, 16>(P, stream) : launch_cfg_t<CFG, 1024, 16>(P, stream);
+    return t <= 256 ? launch_cfg_t<CFG, 256, 32>(P, stream) : launch_cfg_t<CFG, 1024, 32>(P, stream);
 }
 
 cudaError_t launch_render(const RenderParams& P, cudaStream_t stream) {

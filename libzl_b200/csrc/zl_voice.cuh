@@ -277,38 +277,132 @@ __device__ __forceinline__ void walk_positions(VoiceHot& h, VoiceBlockCtl& b, co
     }
 }
 
-// Envelope of tile frames [0, nPos): constant when the ADSR sits in sustain (or, J-mode, idle) and no noteOff lands
-// inside; otherwise stepped frame by frame into te[].  Applies the release logic of :253-261.  Returns the frames
-// rendered (<= nPos) and sets `ended` when the ADSR going idle ends the voice (:258-261).
+// ---------------------------------------------------------------------------------------------
+// Closed-form envelope segments: the same binade argument as for the position, in f32.  While juce::ADSR attacks,
+// decays or (single noteOff) releases, env +- rate is exact-linear as long as env stays in one f32 binade, so a tile
+// is described by up to two (e0, E) segments  env(c) = e0 + (c - cs) * E  (E = 0: sustain / J-mode idle), evaluated
+// exactly by one FFMA; what does not fit (the first frames of an attack from 0, state changes beyond two segments,
+// the per-frame re-armed release of quirk Q3) is stepped frame by frame into the shared-memory row from frame ct on.
+struct EnvPlan {
+    float e0a, Ea, e0b, Eb;
+    int32_t ce;               // first tile frame of segment b
+    int32_t ct;               // first tile frame read from the table row (INT_MAX: none)
+};
+
+// E = rate rounded to the ulp of e0's binade, or false when the closed form does not apply (tiny e0, ties, rate too big).
+__device__ __forceinline__ bool binade_step_f(float e0, float rate, float& E, float& top, float& bottom) {
+    if (!(e0 >= 1.0e-30f) || !(rate > 0.0f)) return false;
+    const int bits = __float_as_int(e0);
+    bottom = __int_as_float(bits & 0x7f800000);
+    top = __fmul_rn(bottom, 2.0f);
+    if (!(rate < __fmul_rn(top, 0.25f))) return false;
+    const float M = __fmul_rn(top, 0.75f);                                  // 1.5 * 2^e: ulp(M) = u
+    E = __fsub_rn(__fadd_rn(M, rate), M);
+    const float u = __fmul_rn(top, 5.9604644775390625e-08f);               // 2^(e+1) * 2^-24
+    if (__fmul_rn(fabsf(__fsub_rn(rate, E)), 2.0f) == u) return false;      // tie: rounding would depend on env's parity
+    return E > 0.0f;
+}
+
+// Largest x in [0, X] with e0 + x*E < lim (up) or e0 - x*E >= lim (down); x = 0 always qualifies by construction.
+__device__ __forceinline__ int env_run_up(float e0, float E, float lim, int X) {
+    if (__fmaf_rn((float) X, E, e0) < lim) return X;
+    int x = (int) __fdiv_rn(__fsub_rn(lim, e0), E);
+    x = max(0, min(X, x));
+    while (x > 0 && !(__fmaf_rn((float) x, E, e0) < lim)) --x;
+    while (x < X && __fmaf_rn((float) (x + 1), E, e0) < lim) ++x;
+    return x;
+}
+__device__ __forceinline__ int env_run_down(float e0, float E, float lim, int X) {
+    if (__fmaf_rn((float) X, -E, e0) >= lim) return X;
+    int x = (int) __fdiv_rn(__fsub_rn(e0, lim), E);
+    x = max(0, min(X, x));
+    while (x > 0 && !(__fmaf_rn((float) x, -E, e0) >= lim)) --x;
+    while (x < X && __fmaf_rn((float) (x + 1), -E, e0) >= lim) ++x;
+    return x;
+}
+
+// juce::ADSR::noteOff with the f64 division replaced by a multiply with 1/relDen, kept bit-exact: the product is
+// within 2 ulp(f64) of the quotient, so the f32 result can differ only when it sits next to an f32 rounding
+// midpoint; those (2^-26 of the cases) take the real division.   juce_ADSR.h:132-146
+__device__ __forceinline__ void adsr_note_off_fast(VoiceHot& v, double relRcp) {
+    if (v.adsrState == kIdle) return;
+    if (!(v.release > 0.0f)) { adsr_reset(v); return; }
+    const double q = __dmul_rn((double) v.env, relRcp);
+    const unsigned lo = (unsigned) __double2loint(q) & 0x1fffffffu;
+    float rr;
+    if (lo - 0x0ffffff8u <= 16u || !(q > 1.0e-30)) rr = __double2float_rn(__ddiv_rn((double) v.env, v.relDen));
+    else rr = __double2float_rn(q);
+    v.rRate = rr;
+    v.adsrState = kRelease;
+}
+
+// Envelope of tile frames [0, nPos).  Applies the release logic of :253-261.  Returns the frames rendered (<= nPos)
+// and sets `ended` when the ADSR going idle ends the voice (:258-261).
 template <bool JMODE, bool Q3>
-__device__ __forceinline__ int plan_envelope(VoiceHot& h, VoiceBlockCtl& b, const PosPlan& pl, float* te, float& envConst,
-                                             bool& fromTable, bool& ended) {
-    ended = false; fromTable = false;
+__device__ __forceinline__ int plan_envelope(VoiceHot& h, VoiceBlockCtl& b, const PosPlan& pl, float* te, EnvPlan& ep, bool& ended) {
+    ended = false;
     const int nPos = pl.nPos;
     const int lastNoteOffInc = pl.stopped ? nPos - 1 : nPos;      // the increment that stops the voice fires no noteOff
-    if (JMODE) {
-        if (h.adsrState == kIdle) { envConst = 0.0f; return nPos; }
-        if (h.adsrState == kSustain) { h.env = h.sustain; envConst = h.sustain; return nPos; }
-        fromTable = true;
-        for (int i = 0; i < nPos; ++i) te[i] = adsr_next(h);
-        return nPos;
-    }
-    if (h.adsrState == kSustain && pl.kRel >= nPos) {
-        h.env = h.sustain; envConst = h.sustain;
-        if (pl.kRel <= lastNoteOffInc) {                           // noteOff right after the tile's last frame
-            if (Q3 || !b.releaseArmed) { adsr_note_off(h); b.releaseArmed = 1; }
-            if (h.adsrState == kIdle) ended = true;
+    ep.e0a = 0.0f; ep.Ea = 0.0f; ep.e0b = 0.0f; ep.Eb = 0.0f; ep.ce = nPos; ep.ct = INT_MAX;
+    int i = 0, nseg = 0;
+    while (i < nPos) {
+        // next increment at which noteOff fires (after frame k0 - 1)
+        int k0 = INT_MAX;
+        if (!JMODE && pl.kRel <= lastNoteOffInc && (Q3 || !b.releaseArmed)) { k0 = max(pl.kRel, i + 1); if (k0 > lastNoteOffInc) k0 = INT_MAX; }
+        const int runEnd = min(nPos, k0);
+        const int st = h.adsrState;
+        if (nseg == 2 || (!JMODE && st == kIdle) || (st == kAttack && h.env == 0.0f)) break;   // the rest goes frame by frame
+#ifdef ZL_EXP_NOENV
+        const int stx = kSustain;
+#else
+        const int stx = st;
+#endif
+        float e0, E = 0.0f;
+        int m;
+        if (stx == kSustain || st == kIdle) {
+            e0 = st == kIdle ? 0.0f : h.sustain;
+            if (st != kIdle) h.env = h.sustain;
+            m = runEnd - i;
+        } else {
+            e0 = adsr_next(h);                                     // exact step; may clamp and change state
+            m = 1;
+            const int X = runEnd - i - 1;
+            float step = st == kAttack ? h.aRate : (st == kDecay ? h.dRate : h.rRate), top, bottom;
+            if (h.adsrState == st && X > 0 && binade_step_f(e0, step, E, top, bottom)) {
+                int x;
+                if (st == kAttack) x = env_run_up(e0, E, fminf(1.0f, top), X);
+                else {
+                    // stay strictly above the binade floor (a result below it would round on the finer grid) and,
+                    // decaying, strictly above sustain (<= sustain ends the decay, juce_ADSR.h:170)
+                    const float floorUp = __int_as_float(__float_as_int(bottom) + 1);
+                    const float lim = st == kDecay ? fmaxf(floorUp, __int_as_float(__float_as_int(h.sustain) + 1)) : floorUp;
+                    x = env_run_down(e0, E, lim, X);
+                    E = -E;
+                }
+                h.env = __fmaf_rn((float) x, E, e0);
+                m = 1 + x;
+                if (x == 0) E = 0.0f;
+            } else E = 0.0f;
         }
-        return nPos;
+        if (nseg == 0) { ep.e0a = e0; ep.Ea = E; } else { ep.e0b = e0; ep.Eb = E; ep.ce = i; }
+        ++nseg;
+        i += m;
+        if (i == k0) { adsr_note_off(h); b.releaseArmed = 1; }
+        if (!JMODE && h.adsrState == kIdle && !(pl.stopped && i == nPos)) { ended = true; return i; }
     }
-    fromTable = true;
-    for (int i = 0; i < nPos; ++i) {
+    if (i >= nPos) return nPos;
+    // ---- frame by frame from frame i on ------------------------------------------------------------------
+    ep.ct = i;
+    if (nseg == 1) ep.ce = i;
+    if (nseg == 0) { ep.ce = 0; }
+    const double relRcp = __ddiv_rn(1.0, h.relDen);
+    for (; i < nPos; ++i) {
         te[i] = adsr_next(h);
         const int k = i + 1;
-        if (k >= pl.kRel && k <= lastNoteOffInc) {
-            if (Q3 || !b.releaseArmed) { adsr_note_off(h); b.releaseArmed = 1; }
+        if (!JMODE && k >= pl.kRel && k <= lastNoteOffInc) {
+            if (Q3 || !b.releaseArmed) { adsr_note_off_fast(h, relRcp); b.releaseArmed = 1; }
         }
-        if (h.adsrState == kIdle && !(pl.stopped && k == nPos)) { ended = true; return k; }
+        if (!JMODE && h.adsrState == kIdle && !(pl.stopped && k == nPos)) { ended = true; return k; }
     }
     return nPos;
 }

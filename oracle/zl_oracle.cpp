@@ -936,6 +936,8 @@ int zlo_read_positions(zl_ctx* ctx, int32_t clip, float* gains, float* progress,
             }
     *count = n; return ZL_OK;
 }
+int zlo_kernel_timing(zl_ctx* ctx, int32_t) { return ctx ? ZL_OK : ZL_ERR_INVALID; }   // no kernels in the oracle
+int zlo_kernel_time(zl_ctx* ctx, double* ms, uint64_t* n) { if (!ctx) return ZL_ERR_INVALID; if (ms) *ms = 0.0; if (n) *n = 0; return ZL_OK; }
 int zlo_last_voice_frames(zl_ctx* ctx, uint64_t* vf) { if (!ctx || !vf) return ZL_ERR_INVALID; *vf = ctx->voiceFrames; return ZL_OK; }
 int zlo_dropped_commands(zl_ctx* ctx, uint64_t* n) { if (!ctx || !n) return ZL_ERR_INVALID; *n = ctx->dropped; return ZL_OK; }
 int zlo_launch_count(zl_ctx*, uint64_t* n) { if (n) *n = 0; return ZL_OK; }
