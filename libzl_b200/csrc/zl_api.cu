@@ -15,6 +15,7 @@
 
 namespace zl {
 cudaError_t launch_render(const RenderParams& P, cudaStream_t stream);
+cudaError_t launch_master_mix(const float* raw, const BusDev* buses, float* master, int nSessions, int B, int64_t stride, int64_t n, cudaStream_t stream);
 size_t render_smem_bytes(int B, int V, int nframes);
 cudaError_t launch_thumb_level0(const float*, int, int, int, int, int8_t*, cudaStream_t);
 cudaError_t launch_thumb_bounds(double, double, double, int, int*, cudaStream_t);
@@ -473,7 +474,8 @@ static int ensure_outputs(zl_ctx* ctx, int nblocks, int nframes) {
         ctx->d_master = nullptr;
         ctx->stride = 0;
         for (int w = 0; w < 4; ++w)
-            if (ctx->cfg.outputs & (ZL_OUT_RAW << w)) CK(cudaMalloc((void**) &ctx->d_out[w], sizeof(float) * NB * 2 * (size_t) n));
+            if ((ctx->cfg.outputs & (ZL_OUT_RAW << w)) || (w == 0 && (ctx->cfg.outputs & ZL_OUT_MASTER)))   // the master mix reads the raw plane
+                CK(cudaMalloc((void**) &ctx->d_out[w], sizeof(float) * NB * 2 * (size_t) n));
         if (ctx->cfg.outputs & ZL_OUT_MASTER) CK(cudaMalloc((void**) &ctx->d_master, sizeof(float) * (size_t) ctx->cfg.n_sessions * 2 * (size_t) n));
         ctx->stride = n;
     }
@@ -571,7 +573,7 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     P.cmds = reinterpret_cast<const CmdDev*>(ds + offCmds); P.clocks = dck; P.pow2 = ctx->d_pow2;
     P.cmdRange = nCmds ? reinterpret_cast<const int32_t*>(ds + offRanges) : nullptr;
     for (int w = 0; w < 4; ++w) P.out[w] = ctx->d_out[w];
-    P.master = ctx->d_master; P.peaks = ctx->d_peaks; P.sumsq = ctx->d_sumsq;
+    P.master = nullptr; P.peaks = ctx->d_peaks; P.sumsq = ctx->d_sumsq;
     P.voiceFrames = ctx->d_counters;
     P.outRate = ctx->cfg.sample_rate; P.stride = ctx->stride;
     P.nSessions = ctx->cfg.n_sessions; P.B = ctx->cfg.buses_per_session; P.V = ctx->cfg.voices_per_bus;
@@ -588,6 +590,11 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         CK(launch_render(P, st));
     }
     ctx->launches++;
+    if (ctx->d_master) {
+        CK(launch_master_mix(ctx->d_out[0], ctx->d_buses, ctx->d_master, ctx->cfg.n_sessions, ctx->cfg.buses_per_session,
+                             ctx->stride, (int64_t) nblocks * nframes, st));
+        ctx->launches++;
+    }
     ctx->nblocks = nblocks; ctx->nframes = nframes;
     ctx->lvlCached = false; ctx->vfCached = false;
     CK(cudaEventRecord(ctx->clkEv[slot], st));

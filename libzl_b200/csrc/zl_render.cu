@@ -20,7 +20,8 @@
 //      gathers both taps from the HBM-resident clip (lanes read consecutive source frames -> coalesced), applies
 //      gain / envelope / M-S pan, keeps the bus accumulators in registers and runs the passthrough + meter
 //      epilogue on them; 128-byte coalesced stores.
-// Only the per-session master mix crosses warps (one shared stage + two barriers per tile).
+// Warps never wait for each other: the per-session master mix (the only cross-bus step) is master_mix_kernel below,
+// a streaming pass over the raw bus planes.
 #include "zl_voice.cuh"
 
 namespace zl {
@@ -214,17 +215,9 @@ render_kernel(const RenderParams P) {
     const int B = P.B, V = P.V, NV = B * V;
     const int nframes = P.nframes;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int nwarps = blockDim.x >> 5;
     const unsigned FULL = 0xffffffffu;
 
     WarpSmem<VPW>& ws = reinterpret_cast<WarpSmem<VPW>*>(smemRaw)[warp];
-    // master chain: pre[warp][buf][ch][kT] running sums handed from warp to warp, pub/con[warp] sequence flags
-    float* pre = reinterpret_cast<float*>(smemRaw + sizeof(WarpSmem<VPW>) * nwarps);
-    volatile int* pub = reinterpret_cast<volatile int*>(pre + (size_t) nwarps * 4 * kT);
-    volatile int* con = pub + nwarps;
-    // this warp's dry outs of the current tile, [bus of the warp][ch][kT], until the chain reaches it
-    float* own = reinterpret_cast<float*>(const_cast<int*>(con + nwarps)) + (size_t) warp * (VPW / P.V) * 2 * kT;
-
     // ownership: this lane's voice / bus; the warp's buses
     const int vIdx = warp * VPW + lane;                   // lanes >= VPW own no voice; they only help in G
     const bool ownsRow = lane < VPW;
@@ -250,9 +243,6 @@ render_kernel(const RenderParams P) {
         ws.hot[lane] = h;
         ws.cntFrames[lane] = 0; ws.cntSrc[lane] = 0;
     }
-    if (tid < nwarps) { pub[tid] = 0; con[tid] = 0; }
-    __syncthreads();
-    int tileSeq = 0;
 
     for (int blk = 0; blk < P.nblocks; ++blk) {
         const int64_t off = (int64_t) blk * nframes;
@@ -297,7 +287,6 @@ render_kernel(const RenderParams P) {
 
         for (int t0 = 0; t0 < nframes; t0 += kT) {
             const int nT = min(kT, nframes - t0);
-            ++tileSeq;
             // ---- W: every owner lane plans its voice's tile (state comes from / returns to shared memory) ---------
             // A lane that cannot express its tile in closed form makes the warp cover it in 32-frame sub-tiles.
             bool irregular = false;
@@ -353,7 +342,6 @@ render_kernel(const RenderParams P) {
             __syncwarp();
 
             // ---- G: lane = frame -----------------------------------------------------------------------------
-            const bool chain = P.master != nullptr;
             const double* psbase = reinterpret_cast<const double*>(ws.tbl + VPW * 33);
             for (int bl = 0; bl < busesPerWarp; ++bl) {
                 const int wb = warpBus0 + bl;               // bus of the session
@@ -427,7 +415,6 @@ render_kernel(const RenderParams P) {
                         sqL += (double) __fmul_rn(dL, dL);                     // juce_AudioSampleBuffer.h:1087-1095
                         sqR += (double) __fmul_rn(dR, dR);
                     }
-                    if (chain && c < n) { own[((size_t) bl * 2) * kT + s0 + c] = dL; own[((size_t) bl * 2 + 1) * kT + s0 + c] = dR; }
                 }
                 if (Q2 && t0 + s0 == 0 && lane == 0) {                         // index 0 is never accumulated into (:218): stays zero
                     for (int w = 0; w < 4; ++w)
@@ -448,38 +435,6 @@ render_kernel(const RenderParams P) {
             }
             __syncwarp();
           }
-            // ---- JACK port mix of the session: the dry outs summed in bus order (copy the first, add the others) ----
-            // The running sum travels from warp to warp through double-buffered shared rows; a warp joins the chain
-            // only after its own tile is done, so nobody waits on a neighbour in the hot loop.
-            if (P.master != nullptr) {
-                const bool lastWarp = warp == nwarps - 1;
-                const int seq = tileSeq, buf = tileSeq & 1;
-                if (lane == 0) {
-                    if (warp > 0) while (pub[warp - 1] < seq) __nanosleep(32);
-                    if (!lastWarp) while (con[warp + 1] < seq - 2) __nanosleep(32);
-                }
-                __syncwarp();
-                const float* preIn = pre + ((size_t) (warp > 0 ? warp - 1 : 0) * 2 + buf) * 2 * kT;
-                float* preOut = pre + ((size_t) warp * 2 + buf) * 2 * kT;
-                const int nb = min(busesPerWarp, B - warpBus0);
-                for (int idx = lane; idx < 2 * kT; idx += 32) {
-                    const int ch = idx / kT, c = idx - ch * kT;
-                    float m = own[(size_t) ch * kT + c];
-                    if (warp > 0) m = __fadd_rn(preIn[idx], m);
-                    for (int b2 = 1; b2 < nb; ++b2) m = __fadd_rn(m, own[((size_t) b2 * 2 + ch) * kT + c]);
-                    if (lastWarp) {
-                        const int j = t0 + c + QS;
-                        if (c < nT && j < nframes) P.master[((int64_t) s * 2 + ch) * P.stride + off + j] = m;
-                        if (Q2 && t0 == 0 && c == 0) P.master[((int64_t) s * 2 + ch) * P.stride + off] = 0.0f;
-                    } else preOut[idx] = m;
-                }
-                __syncwarp();
-                if (lane == 0) {
-                    __threadfence_block();
-                    if (!lastWarp) pub[warp] = seq;                            // our running sum of this tile is complete
-                    if (warp > 0) con[warp] = seq;                             // and the previous warp's buffer is drained
-                }
-            }
         }
 
         // ---- block epilogue ----------------------------------------------------------------------------------
@@ -519,6 +474,37 @@ render_kernel(const RenderParams P) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// JACK port mix of each session: master = dry(bus 0), then += dry(bus b) in bus order, where dry is
+// JackPassthroughPrivate::process applied to the raw SamplerChannel port (lib/JackPassthrough.cpp:94-101) — recomputed
+// here from the raw plane with the same arithmetic the render kernel used, so the dry plane need not exist.
+// One thread per (session, frame); both channels; the raw rows are read fully coalesced.
+__global__ void __launch_bounds__(256)
+master_mix_kernel(const float* __restrict__ raw, const BusDev* __restrict__ buses, float* __restrict__ master,
+                  int nSessions, int B, int64_t stride, int64_t n) {
+    const int64_t j = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = blockIdx.y;
+    if (j >= n) return;
+    float mL = 0.0f, mR = 0.0f;
+    for (int b = 0; b < B; ++b) {
+        const int gb = s * B + b;
+        const zl_passthrough_params pt = buses[gb].pt;
+        const float inL = raw[((int64_t) gb * 2) * stride + j], inR = raw[((int64_t) gb * 2 + 1) * stride + j];
+        float dL, dR;
+        passthrough_pair(pt, pt.dry_amount, inL, inR, dL, dR);
+        if (b == 0) { mL = dL; mR = dR; } else { mL = __fadd_rn(mL, dL); mR = __fadd_rn(mR, dR); }
+    }
+    master[((int64_t) s * 2) * stride + j] = mL;
+    master[((int64_t) s * 2 + 1) * stride + j] = mR;
+}
+
+cudaError_t launch_master_mix(const float* raw, const BusDev* buses, float* master, int nSessions, int B, int64_t stride,
+                              int64_t n, cudaStream_t stream) {
+    const dim3 grid((unsigned) ((n + 255) / 256), (unsigned) nSessions);
+    master_mix_kernel<<<grid, 256, 0, stream>>>(raw, buses, master, nSessions, B, stride, n);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
 static int voices_per_warp(int B, int V) { return (ZL_VPW_SMALL == 16 && V <= 16 && B * V <= 512) ? 16 : 32; }
 static int render_threads(int B, int V) { const int w = voices_per_warp(B, V); return ((B * V + w - 1) / w) * 32; }
 
@@ -527,9 +513,7 @@ size_t render_smem_bytes(int B, int V, int nframes) {
     const int nv = B * V;
     if (nv > 1024) return (size_t) 1 << 30;                 // reported as "does not fit"
     const size_t per = voices_per_warp(B, V) == 16 ? sizeof(WarpSmem<16>) : sizeof(WarpSmem<32>);
-    const size_t nw = (size_t) (render_threads(B, V) / 32);
-    return per * nw + sizeof(float) * nw * 4 * kT + sizeof(int) * 2 * nw                      // + master chain buffers and flags
-           + sizeof(float) * nw * (size_t) (voices_per_warp(B, V) / V) * 2 * kT;            // + each warp's own dry stage
+    return per * (size_t) (render_threads(B, V) / 32);
 }
 
 template <int CFG, int MAXT, int VPW>

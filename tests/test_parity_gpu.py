@@ -139,7 +139,7 @@ def test_native_library_is_what_ran(product):
     e.play(c)
     before = e.launch_count()
     e.render(1, 128)
-    assert e.launch_count() == before + 1 and e.voice_frames() == 128
+    assert e.launch_count() >= before + 1 and e.voice_frames() == 128   # render_kernel (+ master_mix_kernel)
     maps = open("/proc/self/maps").read()
     assert "libzl_b200.so" in maps
     e.close()
