@@ -47,6 +47,8 @@ struct __align__(16) TileDesc {
     int32_t nrend;                   // frames of the tile this voice renders; bit 30: positions from the slot row
 };
 constexpr int kSlotBit = 1 << 30;
+constexpr int kSimpleBit = 1 << 29;   // one position segment, one envelope segment, stereo, every tap inside the sample
+constexpr int kCountMask = (1 << 29) - 1;
 
 // VPW = voices per warp (16 or 32): fewer voices per warp = more warps per session = more latency hiding.
 template <int VPW>
@@ -83,7 +85,7 @@ template <bool JMODE>
 __device__ __forceinline__ void gather_issue(const TileDesc& d, const VoiceGather& g, const float* terow, const double* psrow,
                                              int lane, double laneD, Taps& t) {
     t.ok = 0;
-    const int nrend = d.nrend & ~kSlotBit;
+    const int nrend = d.nrend & kCountMask;
     const bool slotPos = (d.nrend & kSlotBit) != 0;
     const bool single = d.cb >= nrend && !slotPos;
     const bool envConst = d.ce >= nrend && d.ct >= nrend && d.Ea == 0.0f;
@@ -122,6 +124,24 @@ __device__ __forceinline__ void gather_issue(const TileDesc& d, const VoiceGathe
             }
         }
         if (v) t.ok |= 1u << ch;
+    }
+}
+
+// The common case (kSimpleBit): no selects, no range tests; lanes past nrend just do not load.
+__device__ __forceinline__ void gather_issue_simple(const TileDesc& d, const VoiceGather& g, int lane, double laneD, float laneF, Taps& t) {
+    t.ok = 0;
+    const int nrend = d.nrend & kCountMask;
+    const float2* src = reinterpret_cast<const float2*>(g.data);
+#pragma unroll
+    for (int ch = 0; ch < kNC; ++ch) {
+        const bool v = ch * 32 + lane < nrend;
+        const double p = __fma_rn(__dadd_rn(laneD, (double) (ch * 32)), d.Ra, d.p0a);
+        const double fl = __dadd_rd(p, 4503599627370496.0);
+        const int pos = __double2loint(fl);
+        t.alpha[ch] = __double2float_rn(__dsub_rn(p, __dsub_rn(fl, 4503599627370496.0)));
+        t.env[ch] = __fmaf_rn(__fadd_rn(laneF, (float) (ch * 32)), d.Ea, d.e0a);
+        t.a[ch] = make_float2(0.0f, 0.0f); t.b[ch] = t.a[ch];
+        if (v) { t.a[ch] = __ldg(src + pos); t.b[ch] = __ldg(src + pos + 1); t.ok |= 1u << ch; }
     }
 }
 
@@ -228,6 +248,7 @@ render_kernel(const RenderParams P) {
     const int warpBus0 = warp * busesPerWarp;
     VoiceDev* rec = P.voices + (size_t) s * NV + vIdx;
     const double laneD = (double) lane;
+    const float laneF = (float) lane;
 
     int cmdCur = 0, cmdEnd = 0, busEnabled = 0;
     if (ownsRow) {
@@ -328,6 +349,9 @@ render_kernel(const RenderParams P) {
                     cnt = plan_envelope<JMODE, Q3>(h, bc, pl, te, ep, ended);
                     d.e0a = ep.e0a; d.Ea = ep.Ea; d.e0b = ep.e0b; d.Eb = ep.Eb; d.ce = ep.ce; d.ct = ep.ct;
                     d.nrend = cnt | (pl.irregular ? kSlotBit : 0);
+                    if (cnt > 0 && !pl.irregular && pl.cb >= cnt && ep.ce >= cnt && ep.ct >= cnt && bc.nch == 2
+                        && (JMODE || (int) __fma_rn((double) (cnt - 1), pl.Ra, pl.p0a) < ws.vg[lane].sampleDuration))
+                        d.nrend |= kSimpleBit;
                     if (ended && cnt < pl.nPos) {                          // the ADSR ran out before the tile did: p is frame cnt's
                         if (pl.irregular) h.p = ps[cnt];
                         else h.p = cnt >= pl.cb ? __fma_rn((double) (cnt - pl.cb), pl.Rb, pl.p0b) : __fma_rn((double) cnt, pl.Ra, pl.p0a);
@@ -358,13 +382,19 @@ render_kernel(const RenderParams P) {
 #ifdef ZL_EXP_NOG
                     const bool on0 = false, on1 = false;
 #else
-                    const bool on0 = (d0.nrend & ~kSlotBit) > 0, on1 = two && (d1.nrend & ~kSlotBit) > 0;  // warp-uniform
+                    const bool on0 = (d0.nrend & kCountMask) > 0, on1 = two && (d1.nrend & kCountMask) > 0;  // warp-uniform
 #endif
                     if (!on0 && !on1) continue;
                     const VoiceGather g0 = ws.vg[row0], g1 = ws.vg[row1];
                     Taps t0v, t1v;
-                    if (on0) gather_issue<JMODE>(d0, g0, ws.tbl + row0 * teStride, psbase + row0 * 33, lane, laneD, t0v);
-                    if (on1) gather_issue<JMODE>(d1, g1, ws.tbl + row1 * teStride, psbase + row1 * 33, lane, laneD, t1v);
+                    if (on0) {
+                        if (d0.nrend & kSimpleBit) gather_issue_simple(d0, g0, lane, laneD, laneF, t0v);
+                        else gather_issue<JMODE>(d0, g0, ws.tbl + row0 * teStride, psbase + row0 * 33, lane, laneD, t0v);
+                    }
+                    if (on1) {
+                        if (d1.nrend & kSimpleBit) gather_issue_simple(d1, g1, lane, laneD, laneF, t1v);
+                        else gather_issue<JMODE>(d1, g1, ws.tbl + row1 * teStride, psbase + row1 * 33, lane, laneD, t1v);
+                    }
                     if (on0) {
                         const float vmax = gather_finish<JMODE, Q1>(g0, t0v, accL, accR);
                         if (!JMODE) {                                          // block peak of the voice  :213-216
