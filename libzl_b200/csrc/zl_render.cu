@@ -30,7 +30,7 @@ namespace zl {
 #define ZL_MINB 2
 #endif
 #ifndef ZL_KT
-#define ZL_KT 64
+#define ZL_KT 128
 #endif
 #ifndef ZL_VPW_SMALL
 #define ZL_VPW_SMALL 16
@@ -61,7 +61,6 @@ struct __align__(16) WarpSmem {
     VoiceHot hot[VPW];               // the voices' state machines between tiles (registers only while a lane plans)
     VoiceBlockCtl ctl[VPW];
     unsigned long long cntFrames[VPW], cntSrc[VPW];   // voice-frames / algorithmic source floats of the launch
-    int   vpeak[VPW];                // per-voice block peak of l + r (float bits, >= 0)   :213-216
     int   busPk[64];                 // per-bus block peaks [bus][2]
     double busSq[64];                // per-bus block sums of squares [bus][2]
 };
@@ -73,103 +72,111 @@ __device__ __forceinline__ float lerp_gain_z(float a, float b, float ia, float a
     return __fmul_rn(__fmul_rn(__fmul_rn(__fadd_rn(__fmul_rn(a, ia), __fmul_rn(b, alpha)), g), env), vol);
 }
 
-// The gather of one voice x one tile is split in two so the loads of several voice-steps are in flight together:
-// gather_issue computes (pos, alpha, env) per lane-frame and issues both tap loads; gather_finish does the arithmetic.
+// The gather of one voice x one tile is split in two so all of the tile's loads are in flight together:
+// gather_issue computes (pos, alpha, env) per lane-frame and issues both tap loads of every chunk; gather_finish does
+// the arithmetic.  Lanes past the voice's last frame read zeros (from the clip's zero padding or not at all), so they add
+// +0 to the bus and to the voice peak: no validity predicate is needed downstream.
 struct Taps {
     float2 a[kNC], b[kNC];           // taps at pos and pos + 1 (mono: .y duplicates .x, so r == l falls out of the same math)
     float alpha[kNC], env[kNC];
-    unsigned ok;                     // bit ch: this lane's frame of chunk ch is rendered
 };
+
+// (int) p and p - (int) p without int<->f64 conversions: p + 2^52 rounded down is floor(p) + 2^52
+__device__ __forceinline__ int split_pos(double p, float& alpha) {
+    const double fl = __dadd_rd(p, 4503599627370496.0);
+    alpha = __double2float_rn(__dsub_rn(p, __dsub_rn(fl, 4503599627370496.0)));
+    return __double2loint(fl);
+}
 
 template <bool JMODE>
 __device__ __forceinline__ void gather_issue(const TileDesc& d, const VoiceGather& g, const float* terow, const double* psrow,
-                                             int lane, double laneD, Taps& t) {
-    t.ok = 0;
+                                             int lane, int nchunks, Taps& t) {
     const int nrend = d.nrend & kCountMask;
     const bool slotPos = (d.nrend & kSlotBit) != 0;
-    const bool single = d.cb >= nrend && !slotPos;
-    const bool envConst = d.ce >= nrend && d.ct >= nrend && d.Ea == 0.0f;
 #pragma unroll
     for (int ch = 0; ch < kNC; ++ch) {
-        const int c = ch * 32 + lane;
-        const bool v = c < nrend;
-        double p;
-        if (single) p = __fma_rn(__dadd_rn(laneD, (double) (ch * 32)), d.Ra, d.p0a);
-        else if (slotPos) p = v ? psrow[c] : 0.0;
-        else {
-            const bool sb = c >= d.cb;
-            p = __fma_rn((double) (c - (sb ? d.cb : 0)), sb ? d.Rb : d.Ra, sb ? d.p0b : d.p0a);
-        }
-        // (int) p and p - (int) p without int<->f64 conversions: p + 2^52 rounded down is floor(p) + 2^52
-        const double fl = __dadd_rd(p, 4503599627370496.0);
-        const int pos = __double2loint(fl);
-        t.alpha[ch] = __double2float_rn(__dsub_rn(p, __dsub_rn(fl, 4503599627370496.0)));
-        float env;
-        if (envConst) env = d.e0a;
-        else if (c >= d.ct) env = v ? terow[c] : 0.0f;
-        else {
-            const bool sb = c >= d.ce;
-            env = __fmaf_rn((float) (c - (sb ? d.ce : 0)), sb ? d.Eb : d.Ea, sb ? d.e0b : d.e0a);   // exact: see zl_voice.cuh
-        }
-        t.env[ch] = env;
-        const bool inR = v && (JMODE || g.sampleDuration > pos);      // Z: taps outside the sample read as 0  (:204-205)
-        t.a[ch] = make_float2(0.0f, 0.0f); t.b[ch] = t.a[ch];
-        if (inR) {
-            if (g.nch > 1) {
-                t.a[ch] = __ldg(reinterpret_cast<const float2*>(g.data) + pos);
-                t.b[ch] = __ldg(reinterpret_cast<const float2*>(g.data) + pos + 1);
-            } else {
-                const float a = __ldg(g.data + pos), b = __ldg(g.data + pos + 1);
-                t.a[ch] = make_float2(a, a); t.b[ch] = make_float2(b, b);
+        t.a[ch] = make_float2(0.0f, 0.0f); t.b[ch] = t.a[ch]; t.alpha[ch] = 0.0f; t.env[ch] = 0.0f;
+        if (ch < nchunks) {                                           // warp-uniform
+            const int c = ch * 32 + lane;
+            const bool v = c < nrend;
+            double p;
+            if (slotPos) p = v ? psrow[c] : 0.0;
+            else {
+                const bool sb = c >= d.cb;
+                p = __fma_rn((double) (c - (sb ? d.cb : 0)), sb ? d.Rb : d.Ra, sb ? d.p0b : d.p0a);
+            }
+            const int pos = split_pos(p, t.alpha[ch]);
+            float env;
+            if (c >= d.ct) env = v ? terow[c] : 0.0f;
+            else {
+                const bool sb = c >= d.ce;
+                env = __fmaf_rn((float) (c - (sb ? d.ce : 0)), sb ? d.Eb : d.Ea, sb ? d.e0b : d.e0a);   // exact: see zl_voice.cuh
+            }
+            t.env[ch] = env;
+            const bool inR = v && (JMODE || g.sampleDuration > pos);      // Z: taps outside the sample read as 0  (:204-205)
+            if (inR) {
+                if (g.nch > 1) {
+                    t.a[ch] = __ldg(reinterpret_cast<const float2*>(g.data) + pos);
+                    t.b[ch] = __ldg(reinterpret_cast<const float2*>(g.data) + pos + 1);
+                } else {
+                    const float a = __ldg(g.data + pos), b = __ldg(g.data + pos + 1);
+                    t.a[ch] = make_float2(a, a); t.b[ch] = make_float2(b, b);
+                }
             }
         }
-        if (v) t.ok |= 1u << ch;
     }
 }
 
-// The common case (kSimpleBit): no selects, no range tests; lanes past nrend just do not load.
+// The common case (kSimpleBit): one position segment, one envelope segment, stereo, every tap inside the sample.
+// FULL: all kT frames are rendered -> no range test at all.  Otherwise lanes past nrend are pointed at the clip's zero
+// padding (frames length .. length + 7 are zero), so the loads stay unpredicated.
+template <bool FULL>
 __device__ __forceinline__ void gather_issue_simple(const TileDesc& d, const VoiceGather& g, int lane, double laneD, float laneF, Taps& t) {
-    t.ok = 0;
     const int nrend = d.nrend & kCountMask;
     const float2* src = reinterpret_cast<const float2*>(g.data);
+    const int zeroPos = g.sampleDuration + 2;                         // length + 1 (and + 2): inside the padding
+    const bool envConst = d.Ea == 0.0f;                               // warp-uniform (sustain, J-mode idle)
 #pragma unroll
     for (int ch = 0; ch < kNC; ++ch) {
-        const bool v = ch * 32 + lane < nrend;
         const double p = __fma_rn(__dadd_rn(laneD, (double) (ch * 32)), d.Ra, d.p0a);
-        const double fl = __dadd_rd(p, 4503599627370496.0);
-        const int pos = __double2loint(fl);
-        t.alpha[ch] = __double2float_rn(__dsub_rn(p, __dsub_rn(fl, 4503599627370496.0)));
-        t.env[ch] = __fmaf_rn(__fadd_rn(laneF, (float) (ch * 32)), d.Ea, d.e0a);
-        t.a[ch] = make_float2(0.0f, 0.0f); t.b[ch] = t.a[ch];
-        if (v) { t.a[ch] = __ldg(src + pos); t.b[ch] = __ldg(src + pos + 1); t.ok |= 1u << ch; }
+        int pos = split_pos(p, t.alpha[ch]);
+        if (!FULL) pos = (ch * 32 + lane < nrend) ? pos : zeroPos;
+        t.a[ch] = __ldg(src + pos); t.b[ch] = __ldg(src + pos + 1);
+    }
+    if (envConst) {
+#pragma unroll
+        for (int ch = 0; ch < kNC; ++ch) t.env[ch] = d.e0a;
+    } else {
+#pragma unroll
+        for (int ch = 0; ch < kNC; ++ch) t.env[ch] = __fmaf_rn(__fadd_rn(laneF, (float) (ch * 32)), d.Ea, d.e0a);
     }
 }
 
 // Interpolation, gains, (Z) M/S pan, bus accumulate.  J: juce_Sampler.cpp:128-152, Z: lib/SamplerSynthVoice.cpp:198-221
 template <bool JMODE, bool Q1>
-__device__ __forceinline__ float gather_finish(const VoiceGather& g, const Taps& t, float (&accL)[kNC], float (&accR)[kNC]) {
+__device__ __forceinline__ float gather_finish(const VoiceGather& g, const Taps& t, int nchunks, float (&accL)[kNC], float (&accR)[kNC]) {
     float vmax = 0.0f;
 #pragma unroll
     for (int ch = 0; ch < kNC; ++ch) {
-        const float alpha = t.alpha[ch], env = t.env[ch];
-        const float ia = __fsub_rn(1.0f, alpha);
-        float l, r;
-        if (JMODE) {
-            l = __fadd_rn(__fmul_rn(t.a[ch].x, ia), __fmul_rn(t.b[ch].x, alpha));
-            r = __fadd_rn(__fmul_rn(t.a[ch].y, ia), __fmul_rn(t.b[ch].y, alpha));
-            const float ge = __fmul_rn(g.gain, env);
-            l = __fmul_rn(l, ge);
-            r = __fmul_rn(r, ge);
-        } else {
-            l = lerp_gain_z<Q1>(t.a[ch].x, t.b[ch].x, ia, alpha, g.gain, env, g.vol);
-            r = lerp_gain_z<Q1>(t.a[ch].y, t.b[ch].y, ia, alpha, g.gain, env, g.vol);
-            const float m = __fmul_rn(0.5f, __fadd_rn(l, r));   // :208 (0.5*(l+r) in f64 is exact)
-            const float sd = __fsub_rn(l, r);
-            l = __fadd_rn(__fmul_rn(g.lPan, m), sd);
-            r = __fsub_rn(__fmul_rn(g.rPan, m), sd);
-        }
-        if (t.ok & (1u << ch)) {
-            accL[ch] = __fadd_rn(accL[ch], l);
+        if (ch < nchunks) {                                           // warp-uniform
+            const float alpha = t.alpha[ch], env = t.env[ch];
+            const float ia = __fsub_rn(1.0f, alpha);
+            float l, r;
+            if (JMODE) {
+                l = __fadd_rn(__fmul_rn(t.a[ch].x, ia), __fmul_rn(t.b[ch].x, alpha));
+                r = __fadd_rn(__fmul_rn(t.a[ch].y, ia), __fmul_rn(t.b[ch].y, alpha));
+                const float ge = __fmul_rn(g.gain, env);
+                l = __fmul_rn(l, ge);
+                r = __fmul_rn(r, ge);
+            } else {
+                l = lerp_gain_z<Q1>(t.a[ch].x, t.b[ch].x, ia, alpha, g.gain, env, g.vol);
+                r = lerp_gain_z<Q1>(t.a[ch].y, t.b[ch].y, ia, alpha, g.gain, env, g.vol);
+                const float m = __fmul_rn(0.5f, __fadd_rn(l, r));   // :208 (0.5*(l+r) in f64 is exact)
+                const float sd = __fsub_rn(l, r);
+                l = __fadd_rn(__fmul_rn(g.lPan, m), sd);
+                r = __fsub_rn(__fmul_rn(g.rPan, m), sd);
+            }
+            accL[ch] = __fadd_rn(accL[ch], l);                      // lanes past the voice's end add +0
             accR[ch] = __fadd_rn(accR[ch], r);
             vmax = fmaxf(vmax, __fadd_rn(l, r));
         }
@@ -298,24 +305,27 @@ render_kernel(const RenderParams P) {
             if (hasVoice && busEnabled && (h.flags & VF_PLAYING))                       // :136-140
                 active = voice_block_begin<JMODE>(h, P, ck, nframes, bc, g);
             ws.hot[lane] = h; ws.ctl[lane] = bc;
-            ws.vg[lane] = g; ws.vpeak[lane] = 0;
+            ws.vg[lane] = g;
         }
         ws.busPk[lane] = 0; ws.busPk[lane + 32] = 0;
         ws.busSq[lane] = 0.0; ws.busSq[lane + 32] = 0.0;
         const bool walked = active;
         int nrendBlock = 0;
+        int vpk = 0;                                          // block peak of this lane's voice, l + r as float bits (>= +0)   :213-216
         __syncwarp();
 
         for (int t0 = 0; t0 < nframes; t0 += kT) {
             const int nT = min(kT, nframes - t0);
             // ---- W: every owner lane plans its voice's tile (state comes from / returns to shared memory) ---------
-            // A lane that cannot express its tile in closed form makes the warp cover it in 32-frame sub-tiles.
+            // One O(1) plan per lane per tile.  A lane that cannot express its tile in closed form makes the warp cover
+            // the tile in 32-frame sub-tiles instead (every lane re-plans from its saved state).
+            VoiceHot h;
+            VoiceBlockCtl bc;
+            PosPlan pl;
             bool irregular = false;
             if (active) {
                 const zl_block_clock ck = P.clocks[blk];
-                VoiceHot h = ws.hot[lane];
-                VoiceBlockCtl bc = ws.ctl[lane];
-                PosPlan pl;
+                h = ws.hot[lane]; bc = ws.ctl[lane];
                 plan_positions<JMODE>(h, bc, ck, t0, nT, nframes, pl);
                 irregular = pl.irregular != 0;
             }
@@ -324,24 +334,25 @@ render_kernel(const RenderParams P) {
             const int teStride = shortTile ? 33 : kT + 1;
           for (int s0 = 0; s0 < nT; s0 += nn) {
             const int n = min(nn, nT - s0);
+            const int nchunks = (n + 31) >> 5;
             int cnt = 0;
             if (ownsRow) {
                 TileDesc d;
                 d.p0a = 0.0; d.Ra = 0.0; d.p0b = 0.0; d.Rb = 0.0; d.e0a = 0.0f; d.Ea = 0.0f; d.e0b = 0.0f; d.Eb = 0.0f;
                 d.cb = n; d.ce = n; d.ct = INT_MAX; d.nrend = 0;
                 if (active) {
-                    const zl_block_clock ck = P.clocks[blk];
-                    VoiceHot h = ws.hot[lane];
-                    VoiceBlockCtl bc = ws.ctl[lane];
                     float* te = ws.tbl + lane * teStride;
                     double* ps = reinterpret_cast<double*>(ws.tbl + VPW * 33) + lane * 33;
-                    PosPlan pl;
-                    PlanUndo undo;
-                    plan_save(undo, h, bc);
-                    plan_positions<JMODE>(h, bc, ck, t0 + s0, n, nframes, pl);
-                    if (pl.irregular) {
-                        plan_restore(undo, h, bc);
-                        walk_positions<JMODE>(h, bc, ck, t0 + s0, n, nframes, ps, pl);
+                    if (shortTile) {
+                        const zl_block_clock ck = P.clocks[blk];
+                        h = ws.hot[lane]; bc = ws.ctl[lane];
+                        PlanUndo undo;
+                        plan_save(undo, h, bc);
+                        plan_positions<JMODE>(h, bc, ck, t0 + s0, n, nframes, pl);
+                        if (pl.irregular) {
+                            plan_restore(undo, h, bc);
+                            walk_positions<JMODE>(h, bc, ck, t0 + s0, n, nframes, ps, pl);
+                        }
                     }
                     d.p0a = pl.p0a; d.Ra = pl.Ra; d.p0b = pl.p0b; d.Rb = pl.Rb; d.cb = pl.cb;
                     EnvPlan ep;
@@ -365,7 +376,7 @@ render_kernel(const RenderParams P) {
             nrendBlock += cnt;
             __syncwarp();
 
-            // ---- G: lane = frame -----------------------------------------------------------------------------
+            // ---- G: lane = frame; one voice at a time, all chunks of the tile in flight ------------------------------
             const double* psbase = reinterpret_cast<const double*>(ws.tbl + VPW * 33);
             for (int bl = 0; bl < busesPerWarp; ++bl) {
                 const int wb = warpBus0 + bl;               // bus of the session
@@ -374,81 +385,67 @@ render_kernel(const RenderParams P) {
                 float accL[kNC], accR[kNC];
 #pragma unroll
                 for (int ch = 0; ch < kNC; ++ch) { accL[ch] = 0.0f; accR[ch] = 0.0f; }
-                for (int vs = 0; vs < V; vs += 2) {
-                    const int row0 = bl * V + vs;
-                    const bool two = vs + 1 < V;
-                    const int row1 = two ? row0 + 1 : row0;
-                    const TileDesc d0 = ws.td[row0], d1 = ws.td[row1];
+                for (int vs = 0; vs < V; ++vs) {
+                    const int row = bl * V + vs;
+                    const TileDesc d = ws.td[row];
+                    const int nr = d.nrend & kCountMask;              // warp-uniform
 #ifdef ZL_EXP_NOG
-                    const bool on0 = false, on1 = false;
-#else
-                    const bool on0 = (d0.nrend & kCountMask) > 0, on1 = two && (d1.nrend & kCountMask) > 0;  // warp-uniform
+                    continue;
 #endif
-                    if (!on0 && !on1) continue;
-                    const VoiceGather g0 = ws.vg[row0], g1 = ws.vg[row1];
-                    Taps t0v, t1v;
-                    if (on0) {
-                        if (d0.nrend & kSimpleBit) gather_issue_simple(d0, g0, lane, laneD, laneF, t0v);
-                        else gather_issue<JMODE>(d0, g0, ws.tbl + row0 * teStride, psbase + row0 * 33, lane, laneD, t0v);
-                    }
-                    if (on1) {
-                        if (d1.nrend & kSimpleBit) gather_issue_simple(d1, g1, lane, laneD, laneF, t1v);
-                        else gather_issue<JMODE>(d1, g1, ws.tbl + row1 * teStride, psbase + row1 * 33, lane, laneD, t1v);
-                    }
-                    if (on0) {
-                        const float vmax = gather_finish<JMODE, Q1>(g0, t0v, accL, accR);
-                        if (!JMODE) {                                          // block peak of the voice  :213-216
-                            const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));   // vmax >= +0: int order == float order
-                            if (lane == 0) atomicMax(&ws.vpeak[row0], pk);
+                    if (nr == 0) continue;
+                    const VoiceGather g = ws.vg[row];
+                    Taps tp;
+                    float vmax;
+                    if (d.nrend & kSimpleBit) {
+                        if (nr == kT) {
+                            gather_issue_simple<true>(d, g, lane, laneD, laneF, tp);
+                            vmax = gather_finish<JMODE, Q1>(g, tp, kNC, accL, accR);
+                        } else {
+                            gather_issue_simple<false>(d, g, lane, laneD, laneF, tp);
+                            vmax = gather_finish<JMODE, Q1>(g, tp, nchunks, accL, accR);
                         }
+                    } else {
+                        gather_issue<JMODE>(d, g, ws.tbl + row * teStride, psbase + row * 33, lane, nchunks, tp);
+                        vmax = gather_finish<JMODE, Q1>(g, tp, nchunks, accL, accR);
                     }
-                    if (on1) {
-                        const float vmax = gather_finish<JMODE, Q1>(g1, t1v, accL, accR);
-                        if (!JMODE) {
-                            const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));
-                            if (lane == 0) atomicMax(&ws.vpeak[row1], pk);
-                        }
+                    if (!JMODE) {                                              // block peak of the voice  :213-216
+                        const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));   // vmax >= +0: int order == float order
+                        if (lane == row) vpk = max(vpk, pk);
                     }
                 }
-                // raw SamplerChannel ports, then JackPassthrough, meters, master running sum
+                // raw SamplerChannel ports, then JackPassthrough and the meters on the register accumulators
                 const zl_passthrough_params pt = P.buses[gbw].pt;
+                const int64_t rowL = ((int64_t) gbw * 2) * P.stride + off, rowR = rowL + P.stride;
                 int pkL = 0, pkR = 0;
                 double sqL = 0.0, sqR = 0.0;
 #pragma unroll
                 for (int ch = 0; ch < kNC; ++ch) {
                     const int c = ch * 32 + lane;
                     const int j = t0 + s0 + c + QS;                            // output index in the block
-                    float dL = 0.0f, dR = 0.0f;
                     if (c < n && j < nframes) {
-                        const int64_t o = off + j;
-                        if (P.out[0]) {
-                            P.out[0][((int64_t) gbw * 2) * P.stride + o] = accL[ch];
-                            P.out[0][((int64_t) gbw * 2 + 1) * P.stride + o] = accR[ch];
-                        }
+                        float dL, dR;
+                        if (P.out[0]) { P.out[0][rowL + j] = accL[ch]; P.out[0][rowR + j] = accR[ch]; }
                         passthrough_pair(pt, pt.dry_amount, accL[ch], accR[ch], dL, dR);
-                        if (P.out[1]) {
-                            P.out[1][((int64_t) gbw * 2) * P.stride + o] = dL;
-                            P.out[1][((int64_t) gbw * 2 + 1) * P.stride + o] = dR;
-                        }
+                        if (P.out[1]) { P.out[1][rowL + j] = dL; P.out[1][rowR + j] = dR; }
                         float xL, xR;
                         if (P.out[2]) {
                             passthrough_pair(pt, pt.wet_fx1_amount, accL[ch], accR[ch], xL, xR);
-                            P.out[2][((int64_t) gbw * 2) * P.stride + o] = xL;
-                            P.out[2][((int64_t) gbw * 2 + 1) * P.stride + o] = xR;
+                            P.out[2][rowL + j] = xL; P.out[2][rowR + j] = xR;
                         }
                         if (P.out[3]) {
                             passthrough_pair(pt, pt.wet_fx2_amount, accL[ch], accR[ch], xL, xR);
-                            P.out[3][((int64_t) gbw * 2) * P.stride + o] = xL;
-                            P.out[3][((int64_t) gbw * 2 + 1) * P.stride + o] = xR;
+                            P.out[3][rowL + j] = xL; P.out[3][rowR + j] = xR;
                         }
                         pkL = max(pkL, peak_int(dL)); pkR = max(pkR, peak_int(dR));
-                        sqL += (double) __fmul_rn(dL, dL);                     // juce_AudioSampleBuffer.h:1087-1095
-                        sqR += (double) __fmul_rn(dR, dR);
+                        if (P.sumsq) {
+                            sqL += (double) __fmul_rn(dL, dL);                 // juce_AudioSampleBuffer.h:1087-1095
+                            sqR += (double) __fmul_rn(dR, dR);
+                        }
                     }
                 }
                 if (Q2 && t0 + s0 == 0 && lane == 0) {                         // index 0 is never accumulated into (:218): stays zero
                     for (int w = 0; w < 4; ++w)
-                        if (P.out[w]) { P.out[w][((int64_t) gbw * 2) * P.stride + off] = 0.0f; P.out[w][((int64_t) gbw * 2 + 1) * P.stride + off] = 0.0f; }
+                        if (P.out[w]) { P.out[w][rowL] = 0.0f; P.out[w][rowR] = 0.0f; }
                 }
                 if (P.peaks) {
                     pkL = __reduce_max_sync(FULL, pkL);
@@ -475,7 +472,7 @@ render_kernel(const RenderParams P) {
             if (nrendBlock > 0) ws.cntSrc[lane] += (unsigned long long) (bc.span + (uint32_t) (bc.lastPos + 2 - bc.spanStart)) * (unsigned) bc.nch;
             // positions model update   lib/SamplerSynthVoice.cpp:265-267
             if (h.clip >= 0 && (JMODE || (h.flags & VF_HAS_POSID))) {
-                h.posGain = JMODE ? 0.0f : __fmul_rn(__int_as_float(ws.vpeak[lane]), 0.5f);
+                h.posGain = JMODE ? 0.0f : __fmul_rn(__int_as_float(vpk), 0.5f);
                 h.posProgress = __double2float_rn(__ddiv_rn(h.p, h.srcLen));
             }
         }

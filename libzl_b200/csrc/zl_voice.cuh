@@ -396,6 +396,23 @@ __device__ __forceinline__ int plan_envelope(VoiceHot& h, VoiceBlockCtl& b, cons
     if (nseg == 1) ep.ce = i;
     if (nseg == 0) { ep.ce = 0; }
     const double relRcp = __ddiv_rn(1.0, h.relDen);
+    if (!JMODE && Q3 && h.adsrState == kRelease && h.release > 0.0f && pl.kRel <= i + 1) {
+        // Quirk Q3 inside the release window: every frame is  env -= releaseRate  (juce_ADSR.h:178-184) followed by a
+        // noteOff that re-derives releaseRate = env / (release * sr)  (:132-146) - a serial recurrence with no closed
+        // form.  Same arithmetic as the generic loop below, without its state tests; the frame that takes the
+        // envelope to <= 0 (and everything after it) is left to the generic loop.
+        const int iEnd = min(nPos, lastNoteOffInc);              // frames i < iEnd are followed by a noteOff
+        float env = h.env, rr = h.rRate;
+        while (i < iEnd) {
+            const float e = __fsub_rn(env, rr);
+            if (!(e > 0.0f)) break;
+            te[i] = e; env = e; ++i;
+            const double q = __dmul_rn((double) e, relRcp);
+            const unsigned lo = (unsigned) __double2loint(q) & 0x1fffffffu;
+            rr = (lo - 0x0ffffff8u <= 16u || !(q > 1.0e-30)) ? __double2float_rn(__ddiv_rn((double) e, h.relDen)) : __double2float_rn(q);
+        }
+        h.env = env; h.rRate = rr; b.releaseArmed = 1;
+    }
     for (; i < nPos; ++i) {
         te[i] = adsr_next(h);
         const int k = i + 1;
