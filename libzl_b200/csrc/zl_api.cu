@@ -14,9 +14,10 @@
 #include "zl_device.cuh"
 
 namespace zl {
-cudaError_t launch_render(const RenderParams& P, cudaStream_t stream);
+cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream);
+size_t render_scratch_bytes(int nVoices, int nframes, size_t off[4]);
+void render_bind_scratch(RenderParams& P, void* scratch, int nVoices, int nframes);
 cudaError_t launch_master_mix(const float* raw, const BusDev* buses, float* master, int nSessions, int B, int64_t stride, int64_t n, cudaStream_t stream);
-size_t render_smem_bytes(int B, int V, int nframes);
 cudaError_t launch_thumb_level0(const float*, int, int, int, int, int8_t*, cudaStream_t);
 cudaError_t launch_thumb_bounds(double, double, double, int, int*, cudaStream_t);
 cudaError_t launch_thumb_pixels(const int8_t*, int, int, const int*, int, int8_t*, cudaStream_t);
@@ -127,6 +128,7 @@ struct zl_ctx {
     float* d_out[4] = {nullptr, nullptr, nullptr, nullptr};
     float* d_master = nullptr;
     int32_t* d_peaks = nullptr; double* d_sumsq = nullptr;
+    void* d_scratch = nullptr; size_t scratchCap = 0;   // plan -> gather hand-over of one block
     int64_t stride = 0; size_t lvlCap = 0;
     int nblocks = 0, nframes = 0;
     std::vector<int32_t> h_peaks; std::vector<double> h_sumsq; bool lvlCached = false;
@@ -301,6 +303,7 @@ int zl_ctx_destroy(zl_ctx* ctx) {
                      ctx->d_counters, ctx->d_bnd, ctx->d_px, ctx->d_mask, ctx->d_tmp, ctx->d_out[0], ctx->d_out[1],
                      ctx->d_out[2], ctx->d_out[3], ctx->d_master, ctx->d_peaks, ctx->d_sumsq};
     for (void* p : frees) if (p) cudaFree(p);
+    if (ctx->d_scratch) cudaFree(ctx->d_scratch);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     if (ctx->h_clocks) cudaFreeHost(ctx->h_clocks);
     for (int k = 0; k < 2; ++k) { if (ctx->h_slot[k]) cudaFreeHost(ctx->h_slot[k]); if (ctx->d_slot[k]) cudaFree(ctx->d_slot[k]); }
@@ -479,6 +482,16 @@ static int ensure_outputs(zl_ctx* ctx, int nblocks, int nframes) {
         if (ctx->cfg.outputs & ZL_OUT_MASTER) CK(cudaMalloc((void**) &ctx->d_master, sizeof(float) * (size_t) ctx->cfg.n_sessions * 2 * (size_t) n));
         ctx->stride = n;
     }
+    {
+        size_t off[4];
+        const size_t need = render_scratch_bytes((int) (NB * ctx->cfg.voices_per_bus), nframes, off);
+        if (need > ctx->scratchCap) {
+            if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+            ctx->d_scratch = nullptr; ctx->scratchCap = 0;
+            CK(cudaMalloc(&ctx->d_scratch, need));
+            ctx->scratchCap = need;
+        }
+    }
     const size_t lv = (size_t) nblocks * NB * 2;
     if (lv > ctx->lvlCap) {
         if (ctx->d_peaks) cudaFree(ctx->d_peaks);
@@ -495,8 +508,7 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     BIND();
     if (nblocks < 1 || nframes < 1 || !clocks || nblocks > ctx->cfg.max_blocks || nframes > ctx->cfg.max_frames)
         return invalid(ctx, "render: nblocks/nframes out of range or null clocks");
-    if (render_smem_bytes(ctx->cfg.buses_per_session, ctx->cfg.voices_per_bus, nframes) > 227 * 1024)
-        return invalid(ctx, "render: buses x voices x nframes does not fit the 227 KB shared memory of one CTA");
+    if (ctx->cfg.voices_per_bus > 1024) return invalid(ctx, "render: more than 1024 voices per bus");
     int rc = ensure_outputs(ctx, nblocks, nframes);
     if (rc != ZL_OK) return rc;
     cudaStream_t st = ctx->stream;
@@ -579,17 +591,21 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     P.nSessions = ctx->cfg.n_sessions; P.B = ctx->cfg.buses_per_session; P.V = ctx->cfg.voices_per_bus;
     P.nClips = (int) ctx->clips.size();
     P.nblocks = nblocks; P.nframes = nframes; P.mode = ctx->cfg.mode; P.quirks = ctx->cfg.quirks;
+    render_bind_scratch(P, ctx->d_scratch, (int) (NB * ctx->cfg.voices_per_bus), nframes);
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->timing) {
-        cudaEvent_t e0, e1;
         CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
         CK(cudaEventRecord(e0, st));
-        CK(launch_render(P, st));
+    }
+    for (int blk = 0; blk < nblocks; ++blk) {      // one JACK period = plan_kernel + gather_kernel
+        P.blk = blk;
+        CK(launch_render_block(P, st));
+        ctx->launches += 2;
+    }
+    if (ctx->timing) {
         CK(cudaEventRecord(e1, st));
         ctx->tev.push_back(e0); ctx->tev.push_back(e1);
-    } else {
-        CK(launch_render(P, st));
     }
-    ctx->launches++;
     if (ctx->d_master) {
         CK(launch_master_mix(ctx->d_out[0], ctx->d_buses, ctx->d_master, ctx->cfg.n_sessions, ctx->cfg.buses_per_session,
                              ctx->stride, (int64_t) nblocks * nframes, st));

@@ -76,6 +76,9 @@ struct CmdDev {
     uint64_t tick;
 };
 
+struct TileDesc;
+struct VoiceGather;
+
 struct RenderParams {
     VoiceDev* voices;        // [nbus][V]
     const ClipDev* clips;
@@ -95,6 +98,12 @@ struct RenderParams {
     int32_t nSessions, B, V, nClips;
     int32_t nblocks, nframes;
     int32_t mode, quirks;
+    // per-block hand-over between plan_kernel and gather_kernel (scratch, overwritten every block)
+    TileDesc* descs;         // [tilesPerBlock][nVoices]
+    VoiceGather* vgs;        // [nVoices]
+    float* te;               // [tilesPerBlock][nVoices][kT] envelope rows (only frames >= TileDesc.ct are used)
+    double* ps;              // [tilesPerBlock][nVoices][kT] position rows (only kSlotBit voice-tiles)
+    int32_t nVoices, tilesPerBlock, blk, planBusesPerCta;
 };
 
 // ---------------------------------------------------------------------------------------------

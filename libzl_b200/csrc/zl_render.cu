@@ -1,69 +1,46 @@
-// zl_render.cu — the batched sampler render kernel (sm_100a).
+// zl_render.cu — the batched sampler render kernels (sm_100a).
 //
-// One CTA renders one session (an independent JACK graph: B SamplerChannels x V voices) for all blocks of
-// the launch:  SamplerChannel::process (lib/SamplerSynth.cpp:116-148) -> SamplerSynthVoice::process
-// (lib/SamplerSynthVoice.cpp:174-270) or juce::SamplerVoice::renderNextBlock (juce_Sampler.cpp:117-163)
-// -> JackPassthroughPrivate::process (lib/JackPassthrough.cpp:45-115) -> AudioLevels peak scan
-// (lib/AudioLevels.cpp:357-385) -> JACK port mix of the dry outputs (master).
+// One JACK period (block) of every session = two kernels on one stream:
 //
-// Work decomposition (stage 3).  Thread t of the CTA owns voice t of the session for the whole launch
-// (bus = t / V, slot = t % V); its state machine lives in registers.  A warp therefore owns 32 voices =
-// 32/V whole buses, and everything up to the bus outputs is warp-local:
-//   W  each lane PLANS its voice's next tile of kT frames in O(1): the f64 position recurrence p += ratio is
-//      exact-linear inside a binade (zl_voice.cuh), so a tile is at most two (p0, R) segments broken at binade
-//      crossings / loop wraps / the stop position; the envelope is a constant while the ADSR sits in sustain and
-//      is stepped frame by frame into a shared-memory row only while it attacks, decays or releases.  Tiles a
-//      voice cannot express that way (p < 1, rounding ties, tiny loops) make the warp drop to 32-frame tiles in
-//      which that lane walks its positions frame by frame into a shared-memory slot;
-//   G  the warp turns 90 degrees: lane = frame.  For each of its buses it walks the voices in slot order (the
-//      serial += order of the reference), evaluates p = p0 + k*R with one DFMA, splits it into (pos, alpha),
-//      gathers both taps from the HBM-resident clip (lanes read consecutive source frames -> coalesced), applies
-//      gain / envelope / M-S pan, keeps the bus accumulators in registers and runs the passthrough + meter
-//      epilogue on them; 128-byte coalesced stores.
-// Warps never wait for each other: the per-session master mix (the only cross-bus step) is master_mix_kernel below,
-// a streaming pass over the raw bus planes.
+//   plan_kernel    thread = voice.  SamplerChannel::process's ring drain + handleCommand (lib/SamplerSynth.cpp:118-122,
+//                  187-230), the per-block prelude of SamplerSynthVoice::process (lib/SamplerSynthVoice.cpp:176-196) and
+//                  the voice's state machine for the whole block, advanced tile by tile (kT = 128 frames) in O(1) per
+//                  tile: the f64 position recurrence p += ratio is exact-linear inside a binade (zl_voice.cuh), so a tile
+//                  is at most two (p0, R) segments broken at binade crossings / loop wraps / the stop position; the
+//                  juce::ADSR envelope is up to two exact-linear f32 segments and is stepped frame by frame into a table
+//                  row only where no closed form exists (attack from 0, quirk Q3's re-armed release); positions that
+//                  have no closed form (p < 1, rounding ties, tiny loops) are walked into a position row.  Output: one
+//                  64-byte TileDesc per voice-tile + one 32-byte VoiceGather per voice-block (L2-resident hand-over).
+//   gather_kernel  warp = bus (SamplerChannel), lane = frame.  Pure streaming: for each tile it walks the bus's voices in
+//                  slot order (the serial += order of the reference), evaluates p = p0 + k*R with one DFMA, splits it
+//                  into (pos, alpha), gathers both taps of four 32-frame chunks from the HBM-resident interleaved clip
+//                  (lanes read consecutive source frames: coalesced, 8 x LDG.64 in flight per lane), applies gain /
+//                  envelope / M-S pan (lib/SamplerSynthVoice.cpp:198-221, J: juce_Sampler.cpp:128-152), keeps the bus
+//                  accumulators in registers and runs JackPassthroughPrivate::process (lib/JackPassthrough.cpp:45-115)
+//                  and the AudioLevels integer peak scan (lib/AudioLevels.cpp:357-385) on them; 128-byte coalesced
+//                  stores.  No shared memory, no barriers; small enough to stay in the instruction cache and to run at
+//                  high occupancy, which is what hides the HBM latency of the gather.
+//   master_mix_kernel  the JACK port mix of each session's dry outputs (the only cross-bus step), once per launch.
 #include "zl_voice.cuh"
 
 namespace zl {
 
-#ifndef ZL_MINB
-#define ZL_MINB 2
-#endif
 #ifndef ZL_KT
 #define ZL_KT 128
 #endif
-#ifndef ZL_VPW_SMALL
-#define ZL_VPW_SMALL 16
+#ifndef ZL_GATHER_THREADS
+#define ZL_GATHER_THREADS 128
 #endif
-constexpr int kT = ZL_KT;            // frames per tile in the regular mode (multiple of 32)
+#ifndef ZL_GATHER_MINB
+#define ZL_GATHER_MINB 6
+#endif
+constexpr int kT = ZL_KT;            // frames per tile (multiple of 32)
 constexpr int kNC = kT / 32;         // 32-frame chunks per tile
-constexpr int kShort = 32;           // frames per tile when some lane of the warp needs the per-frame position walk
 
-// What G needs to know about one voice for one tile (shared memory, 64 bytes = 4 x LDS.128).
-struct __align__(16) TileDesc {
-    double p0a, Ra, p0b, Rb;         // position segments a: frames [0, cb), b: frames [cb, nrend)
-    float e0a, Ea, e0b, Eb;          // envelope segments a: frames [0, ce), b: frames [ce, ct); frames >= ct: table row
-    int32_t cb, ce, ct;
-    int32_t nrend;                   // frames of the tile this voice renders; bit 30: positions from the slot row
-};
-constexpr int kSlotBit = 1 << 30;
+constexpr int kSlotBit = 1 << 30;     // positions come from the voice-tile's position row
 constexpr int kSimpleBit = 1 << 29;   // one position segment, one envelope segment, stereo, every tap inside the sample
-constexpr int kCountMask = (1 << 29) - 1;
-
-// VPW = voices per warp (16 or 32): fewer voices per warp = more warps per session = more latency hiding.
-template <int VPW>
-struct __align__(16) WarpSmem {
-    // regular tiles: te[VPW][kT + 1] envelope rows.  short tiles: te[VPW][33] followed by ps[VPW][33] f64 position slots.
-    static constexpr int kTblFloats = (VPW * (kT + 1) > VPW * 33 * 3) ? VPW * (kT + 1) : VPW * 33 * 3;
-    float tbl[kTblFloats];
-    TileDesc td[VPW];
-    VoiceGather vg[VPW];
-    VoiceHot hot[VPW];               // the voices' state machines between tiles (registers only while a lane plans)
-    VoiceBlockCtl ctl[VPW];
-    unsigned long long cntFrames[VPW], cntSrc[VPW];   // voice-frames / algorithmic source floats of the launch
-    int   busPk[64];                 // per-bus block peaks [bus][2]
-    double busSq[64];                // per-bus block sums of squares [bus][2]
-};
+constexpr int kCountMask = (1 << 20) - 1;
+constexpr int kWantPeak = 1 << 8;     // VoiceGather.nch flag: the positions model takes this block's peak  :265-267
 
 template <bool Q1>
 __device__ __forceinline__ float lerp_gain_z(float a, float b, float ia, float alpha, float g, float env, float vol) {
@@ -89,10 +66,11 @@ __device__ __forceinline__ int split_pos(double p, float& alpha) {
 }
 
 template <bool JMODE>
-__device__ __forceinline__ void gather_issue(const TileDesc& d, const VoiceGather& g, const float* terow, const double* psrow,
-                                             int lane, int nchunks, Taps& t) {
+__device__ __forceinline__ void gather_issue(const TileDesc& d, const VoiceGather& g, const float* __restrict__ terow,
+                                             const double* __restrict__ psrow, int lane, int nchunks, Taps& t) {
     const int nrend = d.nrend & kCountMask;
     const bool slotPos = (d.nrend & kSlotBit) != 0;
+    const int nch = g.nch & 0xff;
 #pragma unroll
     for (int ch = 0; ch < kNC; ++ch) {
         t.a[ch] = make_float2(0.0f, 0.0f); t.b[ch] = t.a[ch]; t.alpha[ch] = 0.0f; t.env[ch] = 0.0f;
@@ -115,7 +93,7 @@ __device__ __forceinline__ void gather_issue(const TileDesc& d, const VoiceGathe
             t.env[ch] = env;
             const bool inR = v && (JMODE || g.sampleDuration > pos);      // Z: taps outside the sample read as 0  (:204-205)
             if (inR) {
-                if (g.nch > 1) {
+                if (nch > 1) {
                     t.a[ch] = __ldg(reinterpret_cast<const float2*>(g.data) + pos);
                     t.b[ch] = __ldg(reinterpret_cast<const float2*>(g.data) + pos + 1);
                 } else {
@@ -133,9 +111,8 @@ __device__ __forceinline__ void gather_issue(const TileDesc& d, const VoiceGathe
 template <bool FULL>
 __device__ __forceinline__ void gather_issue_simple(const TileDesc& d, const VoiceGather& g, int lane, double laneD, float laneF, Taps& t) {
     const int nrend = d.nrend & kCountMask;
-    const float2* src = reinterpret_cast<const float2*>(g.data);
+    const float2* __restrict__ src = reinterpret_cast<const float2*>(g.data);
     const int zeroPos = g.sampleDuration + 2;                         // length + 1 (and + 2): inside the padding
-    const bool envConst = d.Ea == 0.0f;                               // warp-uniform (sustain, J-mode idle)
 #pragma unroll
     for (int ch = 0; ch < kNC; ++ch) {
         const double p = __fma_rn(__dadd_rn(laneD, (double) (ch * 32)), d.Ra, d.p0a);
@@ -143,7 +120,7 @@ __device__ __forceinline__ void gather_issue_simple(const TileDesc& d, const Voi
         if (!FULL) pos = (ch * 32 + lane < nrend) ? pos : zeroPos;
         t.a[ch] = __ldg(src + pos); t.b[ch] = __ldg(src + pos + 1);
     }
-    if (envConst) {
+    if (d.Ea == 0.0f) {                                               // warp-uniform (sustain, J-mode idle)
 #pragma unroll
         for (int ch = 0; ch < kNC; ++ch) t.env[ch] = d.e0a;
     } else {
@@ -184,23 +161,6 @@ __device__ __forceinline__ float gather_finish(const VoiceGather& g, const Taps&
     return vmax;
 }
 
-// Fire-and-forget L2 prefetch of the source span the voice will read in its NEXT tile (one bulk request per voice:
-// UBLKPF).  The gather's loads then hit L2 instead of waiting on HBM; the HBM requests of 32 voices x all resident
-// warps are in flight while the current tile is being computed.
-__device__ __forceinline__ void prefetch_span_l2(const float* data, int nch, int clipFrames, double p, double ratio, int frames) {
-    const int first = (int) p;
-    int last = first + (int) (ratio * (double) frames) + 2;
-    last = min(last, clipFrames + 7);
-    if (last <= first) return;
-    const size_t fb = (size_t) nch * sizeof(float);
-    uintptr_t a = reinterpret_cast<uintptr_t>(data) + (size_t) first * fb;
-    uintptr_t e = reinterpret_cast<uintptr_t>(data) + (size_t) (last + 1) * fb;
-    a &= ~uintptr_t(15);
-    const unsigned bytes = (unsigned) ((e - a) & ~uintptr_t(15));
-    if (bytes == 0) return;
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(a), "r"(bytes) : "memory");
-}
-
 // JackPassthroughPrivate::process for one output pair   lib/JackPassthrough.cpp:58-111
 __device__ __forceinline__ void passthrough_pair(const zl_passthrough_params& p, float amt, float inL, float inR,
                                                  float& oL, float& oR) {
@@ -215,7 +175,6 @@ __device__ __forceinline__ int peak_int(float x) {   // lib/AudioLevels.cpp:365-
     return __float2int_rz(fabsf(__fmul_rn(131072.0f, x)));
 }
 
-
 // What a position plan may change before it is accepted.
 struct PlanUndo {
     double p; uint64_t nextLoopTick, nextLoopUsecs; int32_t fWrap, spanStart, lastPos; uint32_t span;
@@ -229,281 +188,228 @@ __device__ __forceinline__ void plan_restore(const PlanUndo& u, VoiceHot& h, Voi
     b.fWrap = u.fWrap; b.spanStart = u.spanStart; b.lastPos = u.lastPos; b.span = u.span;
 }
 
-// CFG = mode << 3 | quirks (quirks forced to 0 in J-mode): compile-time so the frame loops carry no mode tests.
-// MAXT: 256 threads (3 CTAs per SM, <= 85 registers) or 1024.
-template <int CFG, int MAXT, int VPW>
-__global__ void __launch_bounds__(MAXT, MAXT == 256 ? ZL_MINB : 1)
-render_kernel(const RenderParams P) {
-    constexpr bool JMODE = (CFG >> 3) == ZL_MODE_J;
-    constexpr bool Q1 = (CFG & ZL_Q1_TAP_GAIN) != 0, Q2 = (CFG & ZL_Q2_PREINC) != 0, Q3 = (CFG & ZL_Q3_RENOTEOFF) != 0;
-    constexpr int QS = Q2 ? 1 : 0;                        // frame f lands at output index f + QS   :218-221
-    extern __shared__ __align__(16) unsigned char smemRaw[];
-    const int s = blockIdx.x;
-    const int B = P.B, V = P.V, NV = B * V;
-    const int nframes = P.nframes;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+// ---------------------------------------------------------------------------------------------------------------------
+// plan_kernel: thread = voice, CTA = whole buses (planBusesPerCta x V threads, rounded up to a warp).
+template <bool JMODE, bool Q3, int MAXT>
+__global__ void __launch_bounds__(MAXT) plan_kernel(const RenderParams P) {
+    const int V = P.V, B = P.B;
+    const int tid = threadIdx.x;
+    const int lb = tid / V, slot = tid - lb * V;              // bus within the CTA, voice slot within the bus
+    const int gb = blockIdx.x * P.planBusesPerCta + lb;        // global bus = session * B + bus
+    const bool hasVoice = lb < P.planBusesPerCta && gb < P.nSessions * B;
+    const int vIdx = gb * V + slot;                            // global voice
+    const int blk = P.blk, nframes = P.nframes;
     const unsigned FULL = 0xffffffffu;
 
-    WarpSmem<VPW>& ws = reinterpret_cast<WarpSmem<VPW>*>(smemRaw)[warp];
-    // ownership: this lane's voice / bus; the warp's buses
-    const int vIdx = warp * VPW + lane;                   // lanes >= VPW own no voice; they only help in G
-    const bool ownsRow = lane < VPW;
-    const bool hasVoice = ownsRow && vIdx < NV;
-    const int bi = vIdx / V, slot = vIdx - bi * V;        // bus within the session, voice slot within the bus
-    const int gb = s * B + bi;
-    const int busesPerWarp = VPW / V;
-    const int warpBus0 = warp * busesPerWarp;
-    VoiceDev* rec = P.voices + (size_t) s * NV + vIdx;
-    const double laneD = (double) lane;
-    const float laneF = (float) lane;
-
-    int cmdCur = 0, cmdEnd = 0, busEnabled = 0;
-    if (ownsRow) {
-        VoiceHot h;
-        h.p = 0.0; h.ratio = 0.0; h.relDen = 1.0; h.srcLen = 1.0; h.nextLoopTick = 0; h.nextLoopUsecs = 0;
-        h.env = 0.f; h.rRate = 0.f; h.aRate = 0.f; h.dRate = 0.f; h.sustain = 0.f; h.release = 0.f; h.gain = 0.f;
-        h.posGain = 0.f; h.posProgress = 0.f; h.adsrState = kIdle; h.flags = 0; h.sound = -1; h.clip = -1; h.slice = -1; h.looping = 0;
-        if (hasVoice) {
-            hot_load(h, *rec);
-            if (P.cmdRange) { cmdCur = P.cmdRange[2 * gb]; cmdEnd = cmdCur + P.cmdRange[2 * gb + 1]; }
-            busEnabled = P.buses[gb].enabled;
+    // ---- commands of this block: SamplerChannel::process ring drain   lib/SamplerSynth.cpp:118-122 ------------------
+    // The bus's slot-0 thread applies them serially on the HBM voice records before anybody loads its state.
+    if (P.cmdRange) {
+        if (hasVoice && slot == 0) {
+            const int c0 = P.cmdRange[2 * gb], c1 = c0 + P.cmdRange[2 * gb + 1];
+            for (int c = c0; c < c1; ++c)
+                if (P.cmds[c].block == blk) bus_handle_command(P.voices + (size_t) gb * V, V, gb % B - 2, P.cmds[c], P);
         }
-        ws.hot[lane] = h;
-        ws.cntFrames[lane] = 0; ws.cntSrc[lane] = 0;
+        __syncthreads();
     }
-
-    for (int blk = 0; blk < P.nblocks; ++blk) {
-        const int64_t off = (int64_t) blk * nframes;
-
-        // ---- commands of this block: SamplerChannel::process ring drain   lib/SamplerSynth.cpp:118-122 ----------
-        const bool hasCmd = hasVoice && cmdCur < cmdEnd && P.cmds[cmdCur].block == blk;
-        if (__any_sync(FULL, hasCmd)) {
-            if (hasCmd) hot_store(ws.hot[lane], *rec);
-            __syncwarp();
-            if (hasCmd) {
-                int cur = cmdCur;
-                while (cur < cmdEnd && P.cmds[cur].block == blk) {
-                    if (slot == 0) bus_handle_command(rec, V, bi - 2, P.cmds[cur], P);   // the bus's V records start at slot 0
-                    ++cur;
-                }
-                cmdCur = cur;
-            }
-            __syncwarp();
-            if (hasCmd) hot_load(ws.hot[lane], *rec);
-        }
-
-        // ---- block prelude -------------------------------------------------------------------------------
+    unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
+    if (hasVoice) {
+        VoiceDev* rec = P.voices + vIdx;
+        VoiceHot h;
+        hot_load(h, *rec);
+        const zl_block_clock ck = P.clocks[blk];
+        // ---- block prelude ---------------------------------------------------------------------------------------
+        VoiceBlockCtl bc;
+        bc.stopD = 0.0; bc.startD = 0.0; bc.relStart = 0.0; bc.usPerFrame = 0.0; bc.lengthInTicks = 0; bc.fWrap = nframes;
+        bc.beatAligned = 0; bc.spanStart = 0; bc.lastPos = 0; bc.span = 0; bc.nch = 0; bc.clipFrames = 0; bc.releaseArmed = 0;
+        VoiceGather g;
+        g.data = nullptr; g.sampleDuration = 0; g.nch = 0; g.gain = g.vol = g.lPan = g.rPan = 0.0f;
         bool active = false;
-        if (ownsRow) {
-            const zl_block_clock ck = P.clocks[blk];
-            VoiceHot h = ws.hot[lane];
-            VoiceBlockCtl bc;
-            bc.stopD = 0.0; bc.startD = 0.0; bc.relStart = 0.0; bc.usPerFrame = 0.0; bc.lengthInTicks = 0; bc.fWrap = nframes;
-            bc.beatAligned = 0; bc.spanStart = 0; bc.lastPos = 0; bc.span = 0; bc.nch = 0; bc.clipFrames = 0; bc.releaseArmed = 0;
-            VoiceGather g;
-            g.data = nullptr; g.sampleDuration = 0; g.nch = 0; g.gain = g.vol = g.lPan = g.rPan = 0.0f;
-            if (hasVoice && busEnabled && (h.flags & VF_PLAYING))                       // :136-140
-                active = voice_block_begin<JMODE>(h, P, ck, nframes, bc, g);
-            ws.hot[lane] = h; ws.ctl[lane] = bc;
-            ws.vg[lane] = g;
-        }
-        ws.busPk[lane] = 0; ws.busPk[lane + 32] = 0;
-        ws.busSq[lane] = 0.0; ws.busSq[lane + 32] = 0.0;
+        if (P.buses[gb].enabled && (h.flags & VF_PLAYING))                              // :136-140
+            active = voice_block_begin<JMODE>(h, P, ck, nframes, bc, g);
         const bool walked = active;
+        const int sampleDuration = g.sampleDuration;
         int nrendBlock = 0;
-        int vpk = 0;                                          // block peak of this lane's voice, l + r as float bits (>= +0)   :213-216
-        __syncwarp();
 
-        for (int t0 = 0; t0 < nframes; t0 += kT) {
-            const int nT = min(kT, nframes - t0);
-            // ---- W: every owner lane plans its voice's tile (state comes from / returns to shared memory) ---------
-            // One O(1) plan per lane per tile.  A lane that cannot express its tile in closed form makes the warp cover
-            // the tile in 32-frame sub-tiles instead (every lane re-plans from its saved state).
-            VoiceHot h;
-            VoiceBlockCtl bc;
-            PosPlan pl;
-            bool irregular = false;
+        for (int t = 0; t < P.tilesPerBlock; ++t) {
+            const int t0 = t * kT;
+            const int n = min(kT, nframes - t0);
+            const size_t vt = (size_t) t * P.nVoices + vIdx;    // voice-tile
+            TileDesc d;
+            d.p0a = 0.0; d.Ra = 0.0; d.p0b = 0.0; d.Rb = 0.0; d.e0a = 0.0f; d.Ea = 0.0f; d.e0b = 0.0f; d.Eb = 0.0f;
+            d.cb = n; d.ce = n; d.ct = INT_MAX; d.nrend = 0;
             if (active) {
-                const zl_block_clock ck = P.clocks[blk];
-                h = ws.hot[lane]; bc = ws.ctl[lane];
-                plan_positions<JMODE>(h, bc, ck, t0, nT, nframes, pl);
-                irregular = pl.irregular != 0;
+                double* ps = P.ps + vt * kT;
+                PosPlan pl;
+                PlanUndo undo;
+                plan_save(undo, h, bc);
+                plan_positions<JMODE>(h, bc, ck, t0, n, nframes, pl);
+                if (pl.irregular) {
+                    plan_restore(undo, h, bc);
+                    walk_positions<JMODE>(h, bc, ck, t0, n, nframes, ps, pl);
+                }
+                EnvPlan ep;
+                bool ended;
+                int resume;
+                int cnt = plan_envelope_closed<JMODE, Q3>(h, bc, pl, ep, ended, resume);
+                if (resume >= 0) cnt = plan_envelope_walk<JMODE, Q3>(h, bc, pl, P.te + vt * kT, resume, ended);
+                d.p0a = pl.p0a; d.Ra = pl.Ra; d.p0b = pl.p0b; d.Rb = pl.Rb; d.cb = pl.cb;
+                d.e0a = ep.e0a; d.Ea = ep.Ea; d.e0b = ep.e0b; d.Eb = ep.Eb; d.ce = ep.ce; d.ct = ep.ct;
+                d.nrend = cnt | (pl.irregular ? kSlotBit : 0);
+                if (cnt > 0 && !pl.irregular && pl.cb >= cnt && ep.ce >= cnt && ep.ct >= cnt && bc.nch == 2
+                    && (JMODE || (int) __fma_rn((double) (cnt - 1), pl.Ra, pl.p0a) < sampleDuration))
+                    d.nrend |= kSimpleBit;
+                if (ended && cnt < pl.nPos) {                          // the ADSR ran out before the tile did: p is frame cnt's
+                    if (pl.irregular) h.p = ps[cnt];
+                    else h.p = cnt >= pl.cb ? __fma_rn((double) (cnt - pl.cb), pl.Rb, pl.p0b) : __fma_rn((double) cnt, pl.Ra, pl.p0a);
+                }
+                if (pl.stopped || ended) { voice_stop(h, false); active = false; }
+                nrendBlock += cnt;
             }
-            const bool shortTile = __any_sync(FULL, irregular);
-            const int nn = shortTile ? kShort : nT;
-            const int teStride = shortTile ? 33 : kT + 1;
-          for (int s0 = 0; s0 < nT; s0 += nn) {
-            const int n = min(nn, nT - s0);
-            const int nchunks = (n + 31) >> 5;
-            int cnt = 0;
-            if (ownsRow) {
-                TileDesc d;
-                d.p0a = 0.0; d.Ra = 0.0; d.p0b = 0.0; d.Rb = 0.0; d.e0a = 0.0f; d.Ea = 0.0f; d.e0b = 0.0f; d.Eb = 0.0f;
-                d.cb = n; d.ce = n; d.ct = INT_MAX; d.nrend = 0;
-                if (active) {
-                    float* te = ws.tbl + lane * teStride;
-                    double* ps = reinterpret_cast<double*>(ws.tbl + VPW * 33) + lane * 33;
-                    if (shortTile) {
-                        const zl_block_clock ck = P.clocks[blk];
-                        h = ws.hot[lane]; bc = ws.ctl[lane];
-                        PlanUndo undo;
-                        plan_save(undo, h, bc);
-                        plan_positions<JMODE>(h, bc, ck, t0 + s0, n, nframes, pl);
-                        if (pl.irregular) {
-                            plan_restore(undo, h, bc);
-                            walk_positions<JMODE>(h, bc, ck, t0 + s0, n, nframes, ps, pl);
-                        }
-                    }
-                    d.p0a = pl.p0a; d.Ra = pl.Ra; d.p0b = pl.p0b; d.Rb = pl.Rb; d.cb = pl.cb;
-                    EnvPlan ep;
-                    bool ended;
-                    cnt = plan_envelope<JMODE, Q3>(h, bc, pl, te, ep, ended);
-                    d.e0a = ep.e0a; d.Ea = ep.Ea; d.e0b = ep.e0b; d.Eb = ep.Eb; d.ce = ep.ce; d.ct = ep.ct;
-                    d.nrend = cnt | (pl.irregular ? kSlotBit : 0);
-                    if (cnt > 0 && !pl.irregular && pl.cb >= cnt && ep.ce >= cnt && ep.ct >= cnt && bc.nch == 2
-                        && (JMODE || (int) __fma_rn((double) (cnt - 1), pl.Ra, pl.p0a) < ws.vg[lane].sampleDuration))
-                        d.nrend |= kSimpleBit;
-                    if (ended && cnt < pl.nPos) {                          // the ADSR ran out before the tile did: p is frame cnt's
-                        if (pl.irregular) h.p = ps[cnt];
-                        else h.p = cnt >= pl.cb ? __fma_rn((double) (cnt - pl.cb), pl.Rb, pl.p0b) : __fma_rn((double) cnt, pl.Ra, pl.p0a);
-                    }
-                    if (pl.stopped || ended) { voice_stop(h, false); active = false; }
-                    else prefetch_span_l2(ws.vg[lane].data, bc.nch, bc.clipFrames, h.p, h.ratio, kT);
-                    ws.hot[lane] = h; ws.ctl[lane] = bc;
-                }
-                ws.td[lane] = d;
-            }
-            nrendBlock += cnt;
-            __syncwarp();
-
-            // ---- G: lane = frame; one voice at a time, all chunks of the tile in flight ------------------------------
-            const double* psbase = reinterpret_cast<const double*>(ws.tbl + VPW * 33);
-            for (int bl = 0; bl < busesPerWarp; ++bl) {
-                const int wb = warpBus0 + bl;               // bus of the session
-                if (wb >= B) break;
-                const int gbw = s * B + wb;
-                float accL[kNC], accR[kNC];
-#pragma unroll
-                for (int ch = 0; ch < kNC; ++ch) { accL[ch] = 0.0f; accR[ch] = 0.0f; }
-                for (int vs = 0; vs < V; ++vs) {
-                    const int row = bl * V + vs;
-                    const TileDesc d = ws.td[row];
-                    const int nr = d.nrend & kCountMask;              // warp-uniform
-#ifdef ZL_EXP_NOG
-                    continue;
-#endif
-                    if (nr == 0) continue;
-                    const VoiceGather g = ws.vg[row];
-                    Taps tp;
-                    float vmax;
-                    if (d.nrend & kSimpleBit) {
-                        if (nr == kT) {
-                            gather_issue_simple<true>(d, g, lane, laneD, laneF, tp);
-                            vmax = gather_finish<JMODE, Q1>(g, tp, kNC, accL, accR);
-                        } else {
-                            gather_issue_simple<false>(d, g, lane, laneD, laneF, tp);
-                            vmax = gather_finish<JMODE, Q1>(g, tp, nchunks, accL, accR);
-                        }
-                    } else {
-                        gather_issue<JMODE>(d, g, ws.tbl + row * teStride, psbase + row * 33, lane, nchunks, tp);
-                        vmax = gather_finish<JMODE, Q1>(g, tp, nchunks, accL, accR);
-                    }
-                    if (!JMODE) {                                              // block peak of the voice  :213-216
-                        const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));   // vmax >= +0: int order == float order
-                        if (lane == row) vpk = max(vpk, pk);
-                    }
-                }
-                // raw SamplerChannel ports, then JackPassthrough and the meters on the register accumulators
-                const zl_passthrough_params pt = P.buses[gbw].pt;
-                const int64_t rowL = ((int64_t) gbw * 2) * P.stride + off, rowR = rowL + P.stride;
-                int pkL = 0, pkR = 0;
-                double sqL = 0.0, sqR = 0.0;
-#pragma unroll
-                for (int ch = 0; ch < kNC; ++ch) {
-                    const int c = ch * 32 + lane;
-                    const int j = t0 + s0 + c + QS;                            // output index in the block
-                    if (c < n && j < nframes) {
-                        float dL, dR;
-                        if (P.out[0]) { P.out[0][rowL + j] = accL[ch]; P.out[0][rowR + j] = accR[ch]; }
-                        passthrough_pair(pt, pt.dry_amount, accL[ch], accR[ch], dL, dR);
-                        if (P.out[1]) { P.out[1][rowL + j] = dL; P.out[1][rowR + j] = dR; }
-                        float xL, xR;
-                        if (P.out[2]) {
-                            passthrough_pair(pt, pt.wet_fx1_amount, accL[ch], accR[ch], xL, xR);
-                            P.out[2][rowL + j] = xL; P.out[2][rowR + j] = xR;
-                        }
-                        if (P.out[3]) {
-                            passthrough_pair(pt, pt.wet_fx2_amount, accL[ch], accR[ch], xL, xR);
-                            P.out[3][rowL + j] = xL; P.out[3][rowR + j] = xR;
-                        }
-                        pkL = max(pkL, peak_int(dL)); pkR = max(pkR, peak_int(dR));
-                        if (P.sumsq) {
-                            sqL += (double) __fmul_rn(dL, dL);                 // juce_AudioSampleBuffer.h:1087-1095
-                            sqR += (double) __fmul_rn(dR, dR);
-                        }
-                    }
-                }
-                if (Q2 && t0 + s0 == 0 && lane == 0) {                         // index 0 is never accumulated into (:218): stays zero
-                    for (int w = 0; w < 4; ++w)
-                        if (P.out[w]) { P.out[w][rowL] = 0.0f; P.out[w][rowR] = 0.0f; }
-                }
-                if (P.peaks) {
-                    pkL = __reduce_max_sync(FULL, pkL);
-                    pkR = __reduce_max_sync(FULL, pkR);
-                    if (lane == 0) { ws.busPk[bl * 2] = max(ws.busPk[bl * 2], pkL); ws.busPk[bl * 2 + 1] = max(ws.busPk[bl * 2 + 1], pkR); }
-                }
-                if (P.sumsq) {                                                 // fixed order: lane tree, then tiles in order
-                    for (int o = 16; o > 0; o >>= 1) {
-                        sqL += __shfl_down_sync(FULL, sqL, o);
-                        sqR += __shfl_down_sync(FULL, sqR, o);
-                    }
-                    if (lane == 0) { ws.busSq[bl * 2] += sqL; ws.busSq[bl * 2 + 1] += sqR; }
-                }
-            }
-            __syncwarp();
-          }
+            P.descs[vt] = d;
         }
 
         // ---- block epilogue ----------------------------------------------------------------------------------
         if (walked) {
-            VoiceHot& h = ws.hot[lane];
-            const VoiceBlockCtl& bc = ws.ctl[lane];
-            ws.cntFrames[lane] += (unsigned long long) nrendBlock;
-            if (nrendBlock > 0) ws.cntSrc[lane] += (unsigned long long) (bc.span + (uint32_t) (bc.lastPos + 2 - bc.spanStart)) * (unsigned) bc.nch;
-            // positions model update   lib/SamplerSynthVoice.cpp:265-267
+            nVoiceFrames = (unsigned long long) nrendBlock;
+            if (nrendBlock > 0) nSrcFloats = (unsigned long long) (bc.span + (uint32_t) (bc.lastPos + 2 - bc.spanStart)) * (unsigned) bc.nch;
+            // positions model update   lib/SamplerSynthVoice.cpp:265-267.  Z: the gain is this block's peak of l + r, which only
+            // the gather knows: it is reset here and max-ed in by gather_kernel (kWantPeak).
             if (h.clip >= 0 && (JMODE || (h.flags & VF_HAS_POSID))) {
-                h.posGain = JMODE ? 0.0f : __fmul_rn(__int_as_float(vpk), 0.5f);
+                h.posGain = 0.0f;
+                if (!JMODE) g.nch |= kWantPeak;
                 h.posProgress = __double2float_rn(__ddiv_rn(h.p, h.srcLen));
             }
         }
-        if (lane < busesPerWarp && warpBus0 + lane < B) {
-            const size_t idx = ((size_t) blk * P.nSessions * B + (size_t) s * B + warpBus0 + lane) * 2;
-            if (P.peaks) { P.peaks[idx] = ws.busPk[lane * 2]; P.peaks[idx + 1] = ws.busPk[lane * 2 + 1]; }
-            if (P.sumsq) { P.sumsq[idx] = ws.busSq[lane * 2]; P.sumsq[idx + 1] = ws.busSq[lane * 2 + 1]; }
-        }
-        __syncwarp();
-    }
-
-    // ---- write the voice records back, account the launch -------------------------------------------------------
-    unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
-    if (hasVoice) {
-        hot_store(ws.hot[lane], *rec);
-        nVoiceFrames = ws.cntFrames[lane]; nSrcFloats = ws.cntSrc[lane];
+        P.vgs[vIdx] = g;
+        hot_store(h, *rec);
     }
     for (int o = 16; o > 0; o >>= 1) {
         nVoiceFrames += __shfl_down_sync(FULL, nVoiceFrames, o);
         nSrcFloats += __shfl_down_sync(FULL, nSrcFloats, o);
     }
-    if (lane == 0 && nVoiceFrames) {
+    if ((tid & 31) == 0 && nVoiceFrames) {
         atomicAdd(P.voiceFrames, nVoiceFrames); atomicAdd(P.voiceFrames + 1, nSrcFloats);
         atomicAdd(P.voiceFrames + 2, nVoiceFrames); atomicAdd(P.voiceFrames + 3, nSrcFloats);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// gather_kernel: warp = bus, lane = frame; all tiles of one block.
+__device__ __forceinline__ TileDesc load_desc(const TileDesc* p) {
+    TileDesc d;
+    const int4* q = reinterpret_cast<const int4*>(p);
+    int4* o = reinterpret_cast<int4*>(&d);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) o[i] = __ldg(q + i);
+    return d;
+}
+__device__ __forceinline__ VoiceGather load_vg(const VoiceGather* p) {
+    VoiceGather g;
+    const int4* q = reinterpret_cast<const int4*>(p);
+    int4* o = reinterpret_cast<int4*>(&g);
+    o[0] = __ldg(q); o[1] = __ldg(q + 1);
+    return g;
+}
+
+template <bool JMODE, bool Q1, bool Q2>
+__global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kernel(const RenderParams P) {
+    constexpr int QS = Q2 ? 1 : 0;                            // frame f lands at output index f + QS   :218-221
+    const int lane = threadIdx.x & 31;
+    const int gbw = blockIdx.x * (ZL_GATHER_THREADS / 32) + (threadIdx.x >> 5);   // global bus
+    if (gbw >= P.nSessions * P.B) return;
+    const unsigned FULL = 0xffffffffu;
+    const int V = P.V, nframes = P.nframes, blk = P.blk;
+    const double laneD = (double) lane;
+    const float laneF = (float) lane;
+    const zl_passthrough_params pt = P.buses[gbw].pt;
+    const int64_t off = (int64_t) blk * nframes;
+    const int64_t rowL = ((int64_t) gbw * 2) * P.stride + off, rowR = rowL + P.stride;
+    const size_t v0 = (size_t) gbw * V;
+    int pkL = 0, pkR = 0;
+    double sqL = 0.0, sqR = 0.0;
+
+    for (int t = 0; t < P.tilesPerBlock; ++t) {
+        const int t0 = t * kT;
+        const int n = min(kT, nframes - t0);
+        const int nchunks = (n + 31) >> 5;
+        const TileDesc* __restrict__ dp = P.descs + (size_t) t * P.nVoices + v0;
+        float accL[kNC], accR[kNC];
+#pragma unroll
+        for (int ch = 0; ch < kNC; ++ch) { accL[ch] = 0.0f; accR[ch] = 0.0f; }
+        for (int vs = 0; vs < V; ++vs) {
+            const TileDesc d = load_desc(dp + vs);
+            const int nr = d.nrend & kCountMask;              // warp-uniform
+            if (nr == 0) continue;
+            const VoiceGather g = load_vg(P.vgs + v0 + vs);
+            Taps tp;
+            int nc = nchunks;
+            if (d.nrend & kSimpleBit) {
+                if (nr == kT) { gather_issue_simple<true>(d, g, lane, laneD, laneF, tp); nc = kNC; }
+                else gather_issue_simple<false>(d, g, lane, laneD, laneF, tp);
+            } else {
+                const size_t vt = (size_t) t * P.nVoices + v0 + vs;
+                gather_issue<JMODE>(d, g, P.te + vt * kT, P.ps + vt * kT, lane, nchunks, tp);
+            }
+            const float vmax = gather_finish<JMODE, Q1>(g, tp, nc, accL, accR);
+            if (!JMODE && (g.nch & kWantPeak)) {               // block peak of the voice -> positions model gain  :213-216, :265
+                const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));   // vmax >= +0: int order == float order
+                if (lane == 0 && pk > 0)
+                    atomicMax(reinterpret_cast<int*>(&P.voices[v0 + vs].posGain), __float_as_int(__fmul_rn(__int_as_float(pk), 0.5f)));
+            }
+        }
+        // raw SamplerChannel ports, then JackPassthrough and the meters on the register accumulators
+#pragma unroll
+        for (int ch = 0; ch < kNC; ++ch) {
+            const int c = ch * 32 + lane;
+            const int j = t0 + c + QS;                            // output index in the block
+            if (c < n && j < nframes) {
+                float dL, dR;
+                if (P.out[0]) { P.out[0][rowL + j] = accL[ch]; P.out[0][rowR + j] = accR[ch]; }
+                passthrough_pair(pt, pt.dry_amount, accL[ch], accR[ch], dL, dR);
+                if (P.out[1]) { P.out[1][rowL + j] = dL; P.out[1][rowR + j] = dR; }
+                if (P.out[2]) {
+                    float xL, xR;
+                    passthrough_pair(pt, pt.wet_fx1_amount, accL[ch], accR[ch], xL, xR);
+                    P.out[2][rowL + j] = xL; P.out[2][rowR + j] = xR;
+                }
+                if (P.out[3]) {
+                    float xL, xR;
+                    passthrough_pair(pt, pt.wet_fx2_amount, accL[ch], accR[ch], xL, xR);
+                    P.out[3][rowL + j] = xL; P.out[3][rowR + j] = xR;
+                }
+                pkL = max(pkL, peak_int(dL)); pkR = max(pkR, peak_int(dR));
+                if (P.sumsq) {
+                    sqL += (double) __fmul_rn(dL, dL);                 // juce_AudioSampleBuffer.h:1087-1095
+                    sqR += (double) __fmul_rn(dR, dR);
+                }
+            }
+        }
+    }
+    if (Q2 && lane == 0) {                                         // index 0 is never accumulated into (:218): stays zero
+#pragma unroll 1
+        for (int w = 0; w < 4; ++w)
+            if (P.out[w]) { P.out[w][rowL] = 0.0f; P.out[w][rowR] = 0.0f; }
+    }
+    const size_t idx = ((size_t) blk * P.nSessions * P.B + gbw) * 2;
+    if (P.peaks) {
+        pkL = __reduce_max_sync(FULL, pkL);
+        pkR = __reduce_max_sync(FULL, pkR);
+        if (lane == 0) { P.peaks[idx] = pkL; P.peaks[idx + 1] = pkR; }
+    }
+    if (P.sumsq) {                                                 // fixed order: per-lane partial sums over the block, then the lane tree
+#pragma unroll 1
+        for (int o = 16; o > 0; o >>= 1) {
+            sqL += __shfl_down_sync(FULL, sqL, o);
+            sqR += __shfl_down_sync(FULL, sqR, o);
+        }
+        if (lane == 0) { P.sumsq[idx] = sqL; P.sumsq[idx + 1] = sqR; }
     }
 }
 
 // ---------------------------------------------------------------------------------------------
 // JACK port mix of each session: master = dry(bus 0), then += dry(bus b) in bus order, where dry is
 // JackPassthroughPrivate::process applied to the raw SamplerChannel port (lib/JackPassthrough.cpp:94-101) — recomputed
-// here from the raw plane with the same arithmetic the render kernel used, so the dry plane need not exist.
+// here from the raw plane with the same arithmetic the gather used, so the dry plane need not exist.
 // One thread per (session, frame); both channels; the raw rows are read fully coalesced.
 __global__ void __launch_bounds__(256)
 master_mix_kernel(const float* __restrict__ raw, const BusDev* __restrict__ buses, float* __restrict__ master,
@@ -532,49 +438,56 @@ cudaError_t launch_master_mix(const float* raw, const BusDev* buses, float* mast
 }
 
 // ---------------------------------------------------------------------------------------------
-static int voices_per_warp(int B, int V) { return (ZL_VPW_SMALL == 16 && V <= 16 && B * V <= 512) ? 16 : 32; }
-static int render_threads(int B, int V) { const int w = voices_per_warp(B, V); return ((B * V + w - 1) / w) * 32; }
-
-size_t render_smem_bytes(int B, int V, int nframes) {
-    (void) nframes;
-    const int nv = B * V;
-    if (nv > 1024) return (size_t) 1 << 30;                 // reported as "does not fit"
-    const size_t per = voices_per_warp(B, V) == 16 ? sizeof(WarpSmem<16>) : sizeof(WarpSmem<32>);
-    return per * (size_t) (render_threads(B, V) / 32);
+// Scratch of one block: descs | vgs | te rows | ps rows (offsets through `off`, 256-byte aligned).
+size_t render_scratch_bytes(int nVoices, int nframes, size_t off[4]) {
+    const size_t tiles = (size_t) (nframes + kT - 1) / kT;
+    auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+    off[0] = 0;
+    off[1] = up(off[0] + tiles * nVoices * sizeof(TileDesc));
+    off[2] = up(off[1] + (size_t) nVoices * sizeof(VoiceGather));
+    off[3] = up(off[2] + tiles * nVoices * kT * sizeof(float));
+    return up(off[3] + tiles * nVoices * kT * sizeof(double));
 }
 
-template <int CFG, int MAXT, int VPW>
-static cudaError_t launch_cfg_t(const RenderParams& P, cudaStream_t stream) {
-    const size_t smem = render_smem_bytes(P.B, P.V, P.nframes);
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(render_kernel<CFG, MAXT, VPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
+void render_bind_scratch(RenderParams& P, void* scratch, int nVoices, int nframes) {
+    size_t off[4];
+    render_scratch_bytes(nVoices, nframes, off);
+    unsigned char* b = static_cast<unsigned char*>(scratch);
+    P.descs = reinterpret_cast<TileDesc*>(b + off[0]);
+    P.vgs = reinterpret_cast<VoiceGather*>(b + off[1]);
+    P.te = reinterpret_cast<float*>(b + off[2]);
+    P.ps = reinterpret_cast<double*>(b + off[3]);
+    P.nVoices = nVoices;
+    P.tilesPerBlock = (nframes + kT - 1) / kT;
+}
+
+// One block (P.blk) of every session: plan, then gather, stream-ordered.
+cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream) {
+    const int V = P.V, nBuses = P.nSessions * P.B;
+    if (V < 1 || V > 1024) return cudaErrorInvalidValue;
+    P.planBusesPerCta = V >= 128 ? 1 : 128 / V;
+    const int planThreads = ((P.planBusesPerCta * V + 31) / 32) * 32;
+    const int planGrid = (nBuses + P.planBusesPerCta - 1) / P.planBusesPerCta;
+    const bool q3 = (P.quirks & ZL_Q3_RENOTEOFF) != 0;
+    if (planThreads <= 128) {
+        if (P.mode == ZL_MODE_J) plan_kernel<true, false, 128><<<planGrid, planThreads, 0, stream>>>(P);
+        else if (q3) plan_kernel<false, true, 128><<<planGrid, planThreads, 0, stream>>>(P);
+        else plan_kernel<false, false, 128><<<planGrid, planThreads, 0, stream>>>(P);
+    } else {
+        if (P.mode == ZL_MODE_J) plan_kernel<true, false, 1024><<<planGrid, planThreads, 0, stream>>>(P);
+        else if (q3) plan_kernel<false, true, 1024><<<planGrid, planThreads, 0, stream>>>(P);
+        else plan_kernel<false, false, 1024><<<planGrid, planThreads, 0, stream>>>(P);
     }
-    render_kernel<CFG, MAXT, VPW><<<P.nSessions, render_threads(P.B, P.V), smem, stream>>>(P);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    const int gGrid = (nBuses + ZL_GATHER_THREADS / 32 - 1) / (ZL_GATHER_THREADS / 32);
+    const bool q1 = (P.quirks & ZL_Q1_TAP_GAIN) != 0, q2 = (P.quirks & ZL_Q2_PREINC) != 0;
+    if (P.mode == ZL_MODE_J) gather_kernel<true, false, false><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
+    else if (q1 && q2) gather_kernel<false, true, true><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
+    else if (q1) gather_kernel<false, true, false><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
+    else if (q2) gather_kernel<false, false, true><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
+    else gather_kernel<false, false, false><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
     return cudaGetLastError();
-}
-
-template <int CFG>
-static cudaError_t launch_cfg(const RenderParams& P, cudaStream_t stream) {
-    const int t = render_threads(P.B, P.V);
-    if (voices_per_warp(P.B, P.V) == 16) return t <= 256 ? launch_cfg_t<CFG, 256, 16>(P, stream) : launch_cfg_t<CFG, 1024, 16>(P, stream);
-    return t <= 256 ? launch_cfg_t<CFG, 256, 32>(P, stream) : launch_cfg_t<CFG, 1024, 32>(P, stream);
-}
-
-cudaError_t launch_render(const RenderParams& P, cudaStream_t stream) {
-    if (P.mode == ZL_MODE_J) return launch_cfg<(ZL_MODE_J << 3)>(P, stream);
-    switch (P.quirks & 7) {
-        case 0: return launch_cfg<0>(P, stream);
-        case 1: return launch_cfg<1>(P, stream);
-        case 2: return launch_cfg<2>(P, stream);
-        case 3: return launch_cfg<3>(P, stream);
-        case 4: return launch_cfg<4>(P, stream);
-        case 5: return launch_cfg<5>(P, stream);
-        case 6: return launch_cfg<6>(P, stream);
-        default: return launch_cfg<7>(P, stream);
-    }
 }
 
 }  // namespace zl

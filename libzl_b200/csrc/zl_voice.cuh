@@ -84,6 +84,16 @@ struct __align__(16) VoiceGather {
     float gain, vol, lPan, rPan;
 };
 
+// What the gather needs to know about one voice for one tile (64 bytes = 4 x LDG.128), written by plan_kernel.
+struct __align__(16) TileDesc {
+    double p0a, Ra, p0b, Rb;         // position segments a: frames [0, cb), b: frames [cb, nrend)
+    float e0a, Ea, e0b, Eb;          // envelope segments a: frames [0, ce), b: frames [ce, ct); frames >= ct: table row
+    int32_t cb, ce, ct;
+    int32_t nrend;                   // frames of the tile this voice renders | flag bits (zl_render.cu)
+};
+static_assert(sizeof(TileDesc) == 64, "TileDesc is 64 bytes");
+static_assert(sizeof(VoiceGather) == 32, "VoiceGather is 32 bytes");
+
 // Per-block constants of the owner lane's walk (registers).
 struct VoiceBlockCtl {
     double stopD, startD, relStart, usPerFrame;
@@ -336,11 +346,15 @@ __device__ __forceinline__ void adsr_note_off_fast(VoiceHot& v, double relRcp) {
     v.adsrState = kRelease;
 }
 
-// Envelope of tile frames [0, nPos).  Applies the release logic of :253-261.  Returns the frames rendered (<= nPos)
-// and sets `ended` when the ADSR going idle ends the voice (:258-261).
+// Envelope of tile frames [0, nPos), with the release logic of :253-261, in two parts so the warp can hand out the few
+// shared-memory table rows only to the voices that need one.
+//
+// Part 1 - closed-form segments.  Returns the frames rendered (<= nPos) when the tile's envelope is complete
+// (resume = -1; `ended` is set when the ADSR going idle ends the voice, :258-261).  Otherwise resume = the first tile
+// frame that has to be stepped frame by frame (plan_envelope_walk) and the return value is meaningless.
 template <bool JMODE, bool Q3>
-__device__ __forceinline__ int plan_envelope(VoiceHot& h, VoiceBlockCtl& b, const PosPlan& pl, float* te, EnvPlan& ep, bool& ended) {
-    ended = false;
+__device__ __forceinline__ int plan_envelope_closed(VoiceHot& h, VoiceBlockCtl& b, const PosPlan& pl, EnvPlan& ep, bool& ended, int& resume) {
+    ended = false; resume = -1;
     const int nPos = pl.nPos;
     const int lastNoteOffInc = pl.stopped ? nPos - 1 : nPos;      // the increment that stops the voice fires no noteOff
     ep.e0a = 0.0f; ep.Ea = 0.0f; ep.e0b = 0.0f; ep.Eb = 0.0f; ep.ce = nPos; ep.ct = INT_MAX;
@@ -352,14 +366,10 @@ __device__ __forceinline__ int plan_envelope(VoiceHot& h, VoiceBlockCtl& b, cons
         const int runEnd = min(nPos, k0);
         const int st = h.adsrState;
         if (nseg == 2 || (!JMODE && st == kIdle) || (st == kAttack && h.env == 0.0f)) break;   // the rest goes frame by frame
-#ifdef ZL_EXP_NOENV
-        const int stx = kSustain;
-#else
-        const int stx = st;
-#endif
+        if (!JMODE && Q3 && st == kRelease && k0 == i + 1) break;  // Q3 release window: one-frame runs, straight to the walk
         float e0, E = 0.0f;
         int m;
-        if (stx == kSustain || st == kIdle) {
+        if (st == kSustain || st == kIdle) {
             e0 = st == kIdle ? 0.0f : h.sustain;
             if (st != kIdle) h.env = h.sustain;
             m = runEnd - i;
@@ -391,10 +401,19 @@ __device__ __forceinline__ int plan_envelope(VoiceHot& h, VoiceBlockCtl& b, cons
         if (!JMODE && h.adsrState == kIdle && !(pl.stopped && i == nPos)) { ended = true; return i; }
     }
     if (i >= nPos) return nPos;
-    // ---- frame by frame from frame i on ------------------------------------------------------------------
     ep.ct = i;
     if (nseg == 1) ep.ce = i;
-    if (nseg == 0) { ep.ce = 0; }
+    if (nseg == 0) ep.ce = 0;
+    resume = i;
+    return -1;
+}
+
+// Part 2 - frame by frame from tile frame i on, into the table row te (indexed by tile frame).
+template <bool JMODE, bool Q3>
+__device__ __forceinline__ int plan_envelope_walk(VoiceHot& h, VoiceBlockCtl& b, const PosPlan& pl, float* te, int i, bool& ended) {
+    ended = false;
+    const int nPos = pl.nPos;
+    const int lastNoteOffInc = pl.stopped ? nPos - 1 : nPos;
     const double relRcp = __ddiv_rn(1.0, h.relDen);
     if (!JMODE && Q3 && h.adsrState == kRelease && h.release > 0.0f && pl.kRel <= i + 1) {
         // Quirk Q3 inside the release window: every frame is  env -= releaseRate  (juce_ADSR.h:178-184) followed by a
