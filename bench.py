@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--no-latency", action="store_true")
     ap.add_argument("--span-mix", type=int, default=0, help="G>1: groups of G GPUs share one mix -> NCCL reduce of the masters")
     ap.add_argument("--seed", type=int, default=5)
+    ap.add_argument("--quirks", type=int, default=7, help="ZL_Q* bits of the Z-mode voice (7 = faithful to libzl, the default)")
     return ap.parse_args()
 
 
@@ -184,7 +185,8 @@ def run_cuda(args, rank, world, local_rank):
     wl = Workload(S, NB, total_steps * 2 + 2, args.seed, rank)
     outputs = K.ZL_OUT_RAW | K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS
     e = Engine(lib=libzl_b200.load(), n_sessions=S, buses_per_session=BUSES, voices_per_bus=VOICES,
-               max_clips=S * CLIPS_PER_SESSION, max_frames=FRAMES, max_blocks=NB, outputs=outputs, device=local_rank)
+               max_clips=S * CLIPS_PER_SESSION, max_frames=FRAMES, max_blocks=NB, outputs=outputs, device=local_rank,
+               quirks=args.quirks)
     stream = torch.cuda.Stream(device=dev)          # a real (non-default) stream: the context launches on exactly this one
     e.set_stream(stream.cuda_stream)
     # clips: generated on the device (synthetic noise / sweep), adopted zero-copy by the clip table
@@ -283,7 +285,7 @@ def run_cpu(args, sessions, steps, warmup, threads=None):
     wl = Workload(sessions, NB, warmup + steps + 1, args.seed, rank=0)
     outputs = K.ZL_OUT_RAW | K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS
     e = Engine(lib=lib, n_sessions=sessions, buses_per_session=BUSES, voices_per_bus=VOICES,
-               max_clips=sessions * CLIPS_PER_SESSION, max_frames=FRAMES, max_blocks=NB, outputs=outputs)
+               max_clips=sessions * CLIPS_PER_SESSION, max_frames=FRAMES, max_blocks=NB, outputs=outputs, quirks=args.quirks)
     lib.dll.zlo_set_threads(e.ctx, threads)
     nclips = sessions * CLIPS_PER_SESSION
     for c0 in range(0, nclips, 64):

@@ -15,7 +15,7 @@
 
 namespace zl {
 cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream);
-size_t render_scratch_bytes(int nVoices, int nframes, size_t off[4]);
+size_t render_scratch_bytes(int nVoices, int nframes, size_t off[5]);
 void render_bind_scratch(RenderParams& P, void* scratch, int nVoices, int nframes);
 cudaError_t launch_master_mix(const float* raw, const BusDev* buses, float* master, int nSessions, int B, int64_t stride, int64_t n, cudaStream_t stream);
 cudaError_t launch_thumb_level0(const float*, int, int, int, int, int8_t*, cudaStream_t);
@@ -129,6 +129,7 @@ struct zl_ctx {
     float* d_master = nullptr;
     int32_t* d_peaks = nullptr; double* d_sumsq = nullptr;
     void* d_scratch = nullptr; size_t scratchCap = 0;   // plan -> gather hand-over of one block
+    int32_t* d_walkCount = nullptr; int walkCountCap = 0;
     int64_t stride = 0; size_t lvlCap = 0;
     int nblocks = 0, nframes = 0;
     std::vector<int32_t> h_peaks; std::vector<double> h_sumsq; bool lvlCached = false;
@@ -304,6 +305,7 @@ int zl_ctx_destroy(zl_ctx* ctx) {
                      ctx->d_out[2], ctx->d_out[3], ctx->d_master, ctx->d_peaks, ctx->d_sumsq};
     for (void* p : frees) if (p) cudaFree(p);
     if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+    if (ctx->d_walkCount) cudaFree(ctx->d_walkCount);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     if (ctx->h_clocks) cudaFreeHost(ctx->h_clocks);
     for (int k = 0; k < 2; ++k) { if (ctx->h_slot[k]) cudaFreeHost(ctx->h_slot[k]); if (ctx->d_slot[k]) cudaFree(ctx->d_slot[k]); }
@@ -483,10 +485,11 @@ static int ensure_outputs(zl_ctx* ctx, int nblocks, int nframes) {
         ctx->stride = n;
     }
     {
-        size_t off[4];
+        size_t off[5];
         const size_t need = render_scratch_bytes((int) (NB * ctx->cfg.voices_per_bus), nframes, off);
         if (need > ctx->scratchCap) {
             if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+    if (ctx->d_walkCount) cudaFree(ctx->d_walkCount);
             ctx->d_scratch = nullptr; ctx->scratchCap = 0;
             CK(cudaMalloc(&ctx->d_scratch, need));
             ctx->scratchCap = need;
@@ -592,6 +595,14 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     P.nClips = (int) ctx->clips.size();
     P.nblocks = nblocks; P.nframes = nframes; P.mode = ctx->cfg.mode; P.quirks = ctx->cfg.quirks;
     render_bind_scratch(P, ctx->d_scratch, (int) (NB * ctx->cfg.voices_per_bus), nframes);
+    if (nblocks > ctx->walkCountCap) {
+        if (ctx->d_walkCount) cudaFree(ctx->d_walkCount);
+        ctx->d_walkCount = nullptr; ctx->walkCountCap = 0;
+        CK(cudaMalloc((void**) &ctx->d_walkCount, sizeof(int32_t) * (size_t) nblocks));
+        ctx->walkCountCap = nblocks;
+    }
+    CK(cudaMemsetAsync(ctx->d_walkCount, 0, sizeof(int32_t) * (size_t) nblocks, st));
+    P.walkCount = ctx->d_walkCount;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->timing) {
         CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
@@ -600,7 +611,7 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     for (int blk = 0; blk < nblocks; ++blk) {      // one JACK period = plan_kernel + gather_kernel
         P.blk = blk;
         CK(launch_render_block(P, st));
-        ctx->launches += 2;
+        ctx->launches += 3;
     }
     if (ctx->timing) {
         CK(cudaEventRecord(e1, st));

@@ -32,7 +32,7 @@ namespace zl {
 #define ZL_GATHER_THREADS 128
 #endif
 #ifndef ZL_GATHER_MINB
-#define ZL_GATHER_MINB 6
+#define ZL_GATHER_MINB 5
 #endif
 constexpr int kT = ZL_KT;            // frames per tile (multiple of 32)
 constexpr int kNC = kT / 32;         // 32-frame chunks per tile
@@ -130,12 +130,12 @@ __device__ __forceinline__ void gather_issue_simple(const TileDesc& d, const Voi
 }
 
 // Interpolation, gains, (Z) M/S pan, bus accumulate.  J: juce_Sampler.cpp:128-152, Z: lib/SamplerSynthVoice.cpp:198-221
-template <bool JMODE, bool Q1>
+template <bool JMODE, bool Q1, bool FULL>
 __device__ __forceinline__ float gather_finish(const VoiceGather& g, const Taps& t, int nchunks, float (&accL)[kNC], float (&accR)[kNC]) {
     float vmax = 0.0f;
 #pragma unroll
     for (int ch = 0; ch < kNC; ++ch) {
-        if (ch < nchunks) {                                           // warp-uniform
+        if (FULL || ch < nchunks) {                                   // warp-uniform
             const float alpha = t.alpha[ch], env = t.env[ch];
             const float ia = __fsub_rn(1.0f, alpha);
             float l, r;
@@ -189,6 +189,124 @@ __device__ __forceinline__ void plan_restore(const PlanUndo& u, VoiceHot& h, Voi
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// One voice, one block: prelude, tiles, epilogue.  Returns false (and changes nothing) when DEFER is set and the voice
+// will need a frame-by-frame envelope walk in this block; such voices are queued and planned by walk_kernel, packed
+// 32 to a warp, instead of holding a whole warp of plan_kernel hostage with one busy lane.
+template <bool JMODE, bool Q3, bool DEFER>
+__device__ __forceinline__ bool plan_voice_block(const RenderParams& P, int vIdx, int gb, unsigned long long& nVoiceFrames,
+                                                 unsigned long long& nSrcFloats) {
+    const int blk = P.blk, nframes = P.nframes;
+    VoiceDev* rec = P.voices + vIdx;
+    VoiceHot h;
+    hot_load(h, *rec);
+    const zl_block_clock ck = P.clocks[blk];
+    // ---- block prelude ---------------------------------------------------------------------------------------
+    VoiceBlockCtl bc;
+    bc.stopD = 0.0; bc.startD = 0.0; bc.relStart = 0.0; bc.usPerFrame = 0.0; bc.lengthInTicks = 0; bc.fWrap = nframes;
+    bc.beatAligned = 0; bc.spanStart = 0; bc.lastPos = 0; bc.span = 0; bc.nch = 0; bc.clipFrames = 0; bc.releaseArmed = 0;
+    VoiceGather g;
+    g.data = nullptr; g.sampleDuration = 0; g.nch = 0; g.gain = g.vol = g.lPan = g.rPan = 0.0f;
+    bool active = false;
+    if (P.buses[gb].enabled && (h.flags & VF_PLAYING))                              // :136-140
+        active = voice_block_begin<JMODE>(h, P, ck, nframes, bc, g);
+    if (DEFER && active) {
+        // attack from 0 is stepped frame by frame (zl_voice.cuh); so is quirk Q3's release window, which a one-shot voice
+        // enters once p reaches relStart (:253) - a conservative test: a deferred voice is planned all the same
+        bool slow = h.adsrState == kAttack && h.env == 0.0f;
+        if (!JMODE && Q3 && !h.looping)
+            slow = slow || __fma_rn((double) nframes * 1.0000001, h.ratio, h.p) >= bc.relStart;
+        if (slow) return false;
+    }
+    const bool walked = active;
+    const int sampleDuration = g.sampleDuration;
+    int nrendBlock = 0;
+
+    // ---- fast path: the whole block is one event-free run --------------------------------------------------
+    // Sustaining voice whose positions stay inside one binade and below every event of :223-261 (loop wrap, stop
+    // position, release window) until the end of the block: every tile is one (p0, R) segment with a constant
+    // envelope, exactly what the generic planner below would produce tile by tile.
+    bool fast = false;
+    if (active && h.adsrState == kSustain) {
+        double R, top;
+        if (binade_step(h.p, h.ratio, R, top)) {
+            const double q = __fma_rn((double) nframes, R, h.p);   // position after the block's last increment
+            if (!JMODE && h.looping) fast = bc.beatAligned ? (bc.fWrap >= nframes && q < top) : (q < fmin(top, bc.stopD));
+            else fast = q < fmin(top, bc.stopD) && (JMODE || q < bc.relStart);
+            if (fast) {
+                for (int t = 0; t < P.tilesPerBlock; ++t) {
+                    const int t0 = t * kT;
+                    const int n = min(kT, nframes - t0);
+                    TileDesc d;
+                    d.p0a = __fma_rn((double) t0, R, h.p); d.Ra = R; d.p0b = 0.0; d.Rb = 0.0;
+                    d.e0a = h.sustain; d.Ea = 0.0f; d.e0b = 0.0f; d.Eb = 0.0f;
+                    d.cb = n; d.ce = n; d.ct = INT_MAX;
+                    const int lastPos = (int) __fma_rn((double) (t0 + n - 1), R, h.p);
+                    d.nrend = n | ((bc.nch == 2 && (JMODE || lastPos < sampleDuration)) ? kSimpleBit : 0);
+                    P.descs[(size_t) t * P.nVoices + vIdx] = d;
+                    bc.lastPos = lastPos;
+                }
+                h.p = q; h.env = h.sustain;
+                nrendBlock = nframes;
+            }
+        }
+    }
+
+    for (int t = 0; t < (fast ? 0 : P.tilesPerBlock); ++t) {
+        const int t0 = t * kT;
+        const int n = min(kT, nframes - t0);
+        const size_t vt = (size_t) t * P.nVoices + vIdx;    // voice-tile
+        TileDesc d;
+        d.p0a = 0.0; d.Ra = 0.0; d.p0b = 0.0; d.Rb = 0.0; d.e0a = 0.0f; d.Ea = 0.0f; d.e0b = 0.0f; d.Eb = 0.0f;
+        d.cb = n; d.ce = n; d.ct = INT_MAX; d.nrend = 0;
+        if (active) {
+            double* ps = P.ps + vt * kT;
+            PosPlan pl;
+            PlanUndo undo;
+            plan_save(undo, h, bc);
+            plan_positions<JMODE>(h, bc, ck, t0, n, nframes, pl);
+            if (pl.irregular) {
+                plan_restore(undo, h, bc);
+                walk_positions<JMODE>(h, bc, ck, t0, n, nframes, ps, pl);
+            }
+            EnvPlan ep;
+            bool ended;
+            int resume;
+            int cnt = plan_envelope_closed<JMODE, Q3>(h, bc, pl, ep, ended, resume);
+            if (resume >= 0) cnt = plan_envelope_walk<JMODE, Q3>(h, bc, pl, P.te + vt * kT, resume, ended);
+            d.p0a = pl.p0a; d.Ra = pl.Ra; d.p0b = pl.p0b; d.Rb = pl.Rb; d.cb = pl.cb;
+            d.e0a = ep.e0a; d.Ea = ep.Ea; d.e0b = ep.e0b; d.Eb = ep.Eb; d.ce = ep.ce; d.ct = ep.ct;
+            d.nrend = cnt | (pl.irregular ? kSlotBit : 0);
+            if (cnt > 0 && !pl.irregular && pl.cb >= cnt && ep.ce >= cnt && ep.ct >= cnt && bc.nch == 2
+                && (JMODE || (int) __fma_rn((double) (cnt - 1), pl.Ra, pl.p0a) < sampleDuration))
+                d.nrend |= kSimpleBit;
+            if (ended && cnt < pl.nPos) {                          // the ADSR ran out before the tile did: p is frame cnt's
+                if (pl.irregular) h.p = ps[cnt];
+                else h.p = cnt >= pl.cb ? __fma_rn((double) (cnt - pl.cb), pl.Rb, pl.p0b) : __fma_rn((double) cnt, pl.Ra, pl.p0a);
+            }
+            if (pl.stopped || ended) { voice_stop(h, false); active = false; }
+            nrendBlock += cnt;
+        }
+        P.descs[vt] = d;
+    }
+
+    // ---- block epilogue ----------------------------------------------------------------------------------
+    if (walked) {
+        nVoiceFrames = (unsigned long long) nrendBlock;
+        if (nrendBlock > 0) nSrcFloats = (unsigned long long) (bc.span + (uint32_t) (bc.lastPos + 2 - bc.spanStart)) * (unsigned) bc.nch;
+        // positions model update   lib/SamplerSynthVoice.cpp:265-267.  Z: the gain is this block's peak of l + r, which only
+        // the gather knows: it is reset here and max-ed in by gather_kernel (kWantPeak).
+        if (h.clip >= 0 && (JMODE || (h.flags & VF_HAS_POSID))) {
+            h.posGain = 0.0f;
+            if (!JMODE) g.nch |= kWantPeak;
+            h.posProgress = __double2float_rn(__ddiv_rn(h.p, h.srcLen));
+        }
+    }
+    P.vgs[vIdx] = g;
+    hot_store(h, *rec);
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // plan_kernel: thread = voice, CTA = whole buses (planBusesPerCta x V threads, rounded up to a warp).
 template <bool JMODE, bool Q3, int MAXT>
 __global__ void __launch_bounds__(MAXT) plan_kernel(const RenderParams P) {
@@ -212,76 +330,39 @@ __global__ void __launch_bounds__(MAXT) plan_kernel(const RenderParams P) {
         __syncthreads();
     }
     unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
-    if (hasVoice) {
-        VoiceDev* rec = P.voices + vIdx;
-        VoiceHot h;
-        hot_load(h, *rec);
-        const zl_block_clock ck = P.clocks[blk];
-        // ---- block prelude ---------------------------------------------------------------------------------------
-        VoiceBlockCtl bc;
-        bc.stopD = 0.0; bc.startD = 0.0; bc.relStart = 0.0; bc.usPerFrame = 0.0; bc.lengthInTicks = 0; bc.fWrap = nframes;
-        bc.beatAligned = 0; bc.spanStart = 0; bc.lastPos = 0; bc.span = 0; bc.nch = 0; bc.clipFrames = 0; bc.releaseArmed = 0;
-        VoiceGather g;
-        g.data = nullptr; g.sampleDuration = 0; g.nch = 0; g.gain = g.vol = g.lPan = g.rPan = 0.0f;
-        bool active = false;
-        if (P.buses[gb].enabled && (h.flags & VF_PLAYING))                              // :136-140
-            active = voice_block_begin<JMODE>(h, P, ck, nframes, bc, g);
-        const bool walked = active;
-        const int sampleDuration = g.sampleDuration;
-        int nrendBlock = 0;
+    bool deferred = false;
+    if (hasVoice) deferred = !plan_voice_block<JMODE, Q3, true>(P, vIdx, gb, nVoiceFrames, nSrcFloats);
+    // queue the deferred voices of this warp with one atomic
+    const unsigned dm = __ballot_sync(FULL, deferred);
+    if (dm) {
+        int base = 0;
+        if ((tid & 31) == 0) base = atomicAdd(P.walkCount + blk, __popc(dm));
+        base = __shfl_sync(FULL, base, 0);
+        if (deferred) P.walkQueue[base + __popc(dm & ((1u << (tid & 31)) - 1u))] = vIdx;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        nVoiceFrames += __shfl_down_sync(FULL, nVoiceFrames, o);
+        nSrcFloats += __shfl_down_sync(FULL, nSrcFloats, o);
+    }
+    if ((tid & 31) == 0 && nVoiceFrames) {
+        atomicAdd(P.voiceFrames, nVoiceFrames); atomicAdd(P.voiceFrames + 1, nSrcFloats);
+        atomicAdd(P.voiceFrames + 2, nVoiceFrames); atomicAdd(P.voiceFrames + 3, nSrcFloats);
+    }
+}
 
-        for (int t = 0; t < P.tilesPerBlock; ++t) {
-            const int t0 = t * kT;
-            const int n = min(kT, nframes - t0);
-            const size_t vt = (size_t) t * P.nVoices + vIdx;    // voice-tile
-            TileDesc d;
-            d.p0a = 0.0; d.Ra = 0.0; d.p0b = 0.0; d.Rb = 0.0; d.e0a = 0.0f; d.Ea = 0.0f; d.e0b = 0.0f; d.Eb = 0.0f;
-            d.cb = n; d.ce = n; d.ct = INT_MAX; d.nrend = 0;
-            if (active) {
-                double* ps = P.ps + vt * kT;
-                PosPlan pl;
-                PlanUndo undo;
-                plan_save(undo, h, bc);
-                plan_positions<JMODE>(h, bc, ck, t0, n, nframes, pl);
-                if (pl.irregular) {
-                    plan_restore(undo, h, bc);
-                    walk_positions<JMODE>(h, bc, ck, t0, n, nframes, ps, pl);
-                }
-                EnvPlan ep;
-                bool ended;
-                int resume;
-                int cnt = plan_envelope_closed<JMODE, Q3>(h, bc, pl, ep, ended, resume);
-                if (resume >= 0) cnt = plan_envelope_walk<JMODE, Q3>(h, bc, pl, P.te + vt * kT, resume, ended);
-                d.p0a = pl.p0a; d.Ra = pl.Ra; d.p0b = pl.p0b; d.Rb = pl.Rb; d.cb = pl.cb;
-                d.e0a = ep.e0a; d.Ea = ep.Ea; d.e0b = ep.e0b; d.Eb = ep.Eb; d.ce = ep.ce; d.ct = ep.ct;
-                d.nrend = cnt | (pl.irregular ? kSlotBit : 0);
-                if (cnt > 0 && !pl.irregular && pl.cb >= cnt && ep.ce >= cnt && ep.ct >= cnt && bc.nch == 2
-                    && (JMODE || (int) __fma_rn((double) (cnt - 1), pl.Ra, pl.p0a) < sampleDuration))
-                    d.nrend |= kSimpleBit;
-                if (ended && cnt < pl.nPos) {                          // the ADSR ran out before the tile did: p is frame cnt's
-                    if (pl.irregular) h.p = ps[cnt];
-                    else h.p = cnt >= pl.cb ? __fma_rn((double) (cnt - pl.cb), pl.Rb, pl.p0b) : __fma_rn((double) cnt, pl.Ra, pl.p0a);
-                }
-                if (pl.stopped || ended) { voice_stop(h, false); active = false; }
-                nrendBlock += cnt;
-            }
-            P.descs[vt] = d;
-        }
 
-        // ---- block epilogue ----------------------------------------------------------------------------------
-        if (walked) {
-            nVoiceFrames = (unsigned long long) nrendBlock;
-            if (nrendBlock > 0) nSrcFloats = (unsigned long long) (bc.span + (uint32_t) (bc.lastPos + 2 - bc.spanStart)) * (unsigned) bc.nch;
-            // positions model update   lib/SamplerSynthVoice.cpp:265-267.  Z: the gain is this block's peak of l + r, which only
-            // the gather knows: it is reset here and max-ed in by gather_kernel (kWantPeak).
-            if (h.clip >= 0 && (JMODE || (h.flags & VF_HAS_POSID))) {
-                h.posGain = 0.0f;
-                if (!JMODE) g.nch |= kWantPeak;
-                h.posProgress = __double2float_rn(__ddiv_rn(h.p, h.srcLen));
-            }
-        }
-        P.vgs[vIdx] = g;
-        hot_store(h, *rec);
+// walk_kernel: thread = queued voice (the ones plan_kernel deferred), grid-stride over the queue.
+template <bool JMODE, bool Q3>
+__global__ void __launch_bounds__(128) walk_kernel(const RenderParams P) {
+    const unsigned FULL = 0xffffffffu;
+    const int tid = threadIdx.x;
+    const int count = P.walkCount[P.blk];
+    unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
+    for (int i = blockIdx.x * blockDim.x + tid; i < count; i += gridDim.x * blockDim.x) {
+        const int vIdx = P.walkQueue[i];
+        unsigned long long a = 0, b = 0;
+        plan_voice_block<JMODE, Q3, false>(P, vIdx, vIdx / P.V, a, b);
+        nVoiceFrames += a; nSrcFloats += b;
     }
     for (int o = 16; o > 0; o >>= 1) {
         nVoiceFrames += __shfl_down_sync(FULL, nVoiceFrames, o);
@@ -311,14 +392,20 @@ __device__ __forceinline__ VoiceGather load_vg(const VoiceGather* p) {
     return g;
 }
 
+constexpr int kStageV = 16;          // voices per bus whose descriptors are staged through shared memory (else: straight from L2)
+
 template <bool JMODE, bool Q1, bool Q2>
 __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kernel(const RenderParams P) {
     constexpr int QS = Q2 ? 1 : 0;                            // frame f lands at output index f + QS   :218-221
-    const int lane = threadIdx.x & 31;
-    const int gbw = blockIdx.x * (ZL_GATHER_THREADS / 32) + (threadIdx.x >> 5);   // global bus
+    // per warp: this tile's V descriptors and the block's V gather records (V <= kStageV)
+    __shared__ TileDesc sDesc[ZL_GATHER_THREADS / 32][kStageV];
+    __shared__ VoiceGather sVg[ZL_GATHER_THREADS / 32][kStageV];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int gbw = blockIdx.x * (ZL_GATHER_THREADS / 32) + warp;   // global bus
     if (gbw >= P.nSessions * P.B) return;
     const unsigned FULL = 0xffffffffu;
     const int V = P.V, nframes = P.nframes, blk = P.blk;
+    const bool staged = V <= kStageV;                         // then V * 4 <= 64 int4: two per lane at most
     const double laneD = (double) lane;
     const float laneF = (float) lane;
     const zl_passthrough_params pt = P.buses[gbw].pt;
@@ -327,33 +414,58 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
     const size_t v0 = (size_t) gbw * V;
     int pkL = 0, pkR = 0;
     double sqL = 0.0, sqR = 0.0;
+    int vpk = 0;                                              // V <= 32: lane vs keeps voice vs's block peak (float bits, >= +0)
+
+    // descriptor pipeline: tile t + 1's descriptors travel in two registers per lane while tile t is gathered
+    int4 nx0 = make_int4(0, 0, 0, 0), nx1 = nx0;
+    if (staged) {
+        const int4* q = reinterpret_cast<const int4*>(P.descs + v0);
+        if (lane < V * 4) nx0 = __ldg(q + lane);
+        if (lane + 32 < V * 4) nx1 = __ldg(q + lane + 32);
+        if (lane < V * 2) reinterpret_cast<int4*>(sVg[warp])[lane] = __ldg(reinterpret_cast<const int4*>(P.vgs + v0) + lane);
+    }
 
     for (int t = 0; t < P.tilesPerBlock; ++t) {
         const int t0 = t * kT;
         const int n = min(kT, nframes - t0);
         const int nchunks = (n + 31) >> 5;
         const TileDesc* __restrict__ dp = P.descs + (size_t) t * P.nVoices + v0;
+        if (staged) {
+            __syncwarp();                                     // the previous tile's descriptors are no longer read
+            if (lane < V * 4) reinterpret_cast<int4*>(sDesc[warp])[lane] = nx0;
+            if (lane + 32 < V * 4) reinterpret_cast<int4*>(sDesc[warp])[lane + 32] = nx1;
+            __syncwarp();
+            if (t + 1 < P.tilesPerBlock) {
+                const int4* q = reinterpret_cast<const int4*>(dp + P.nVoices);
+                if (lane < V * 4) nx0 = __ldg(q + lane);
+                if (lane + 32 < V * 4) nx1 = __ldg(q + lane + 32);
+            }
+        }
         float accL[kNC], accR[kNC];
 #pragma unroll
         for (int ch = 0; ch < kNC; ++ch) { accL[ch] = 0.0f; accR[ch] = 0.0f; }
         for (int vs = 0; vs < V; ++vs) {
-            const TileDesc d = load_desc(dp + vs);
+            const TileDesc d = staged ? sDesc[warp][vs] : load_desc(dp + vs);
             const int nr = d.nrend & kCountMask;              // warp-uniform
             if (nr == 0) continue;
-            const VoiceGather g = load_vg(P.vgs + v0 + vs);
+            const VoiceGather g = staged ? sVg[warp][vs] : load_vg(P.vgs + v0 + vs);
             Taps tp;
-            int nc = nchunks;
-            if (d.nrend & kSimpleBit) {
-                if (nr == kT) { gather_issue_simple<true>(d, g, lane, laneD, laneF, tp); nc = kNC; }
-                else gather_issue_simple<false>(d, g, lane, laneD, laneF, tp);
+            float vmax;
+            if ((d.nrend & kSimpleBit) && nr == kT) {
+                gather_issue_simple<true>(d, g, lane, laneD, laneF, tp);
+                vmax = gather_finish<JMODE, Q1, true>(g, tp, kNC, accL, accR);
             } else {
-                const size_t vt = (size_t) t * P.nVoices + v0 + vs;
-                gather_issue<JMODE>(d, g, P.te + vt * kT, P.ps + vt * kT, lane, nchunks, tp);
+                if (d.nrend & kSimpleBit) gather_issue_simple<false>(d, g, lane, laneD, laneF, tp);
+                else {
+                    const size_t vt = (size_t) t * P.nVoices + v0 + vs;
+                    gather_issue<JMODE>(d, g, P.te + vt * kT, P.ps + vt * kT, lane, nchunks, tp);
+                }
+                vmax = gather_finish<JMODE, Q1, false>(g, tp, nchunks, accL, accR);
             }
-            const float vmax = gather_finish<JMODE, Q1>(g, tp, nc, accL, accR);
             if (!JMODE && (g.nch & kWantPeak)) {               // block peak of the voice -> positions model gain  :213-216, :265
                 const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));   // vmax >= +0: int order == float order
-                if (lane == 0 && pk > 0)
+                if (V <= 32) { if (lane == vs) vpk = max(vpk, pk); }
+                else if (lane == 0 && pk > 0)
                     atomicMax(reinterpret_cast<int*>(&P.voices[v0 + vs].posGain), __float_as_int(__fmul_rn(__int_as_float(pk), 0.5f)));
             }
         }
@@ -385,6 +497,8 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
             }
         }
     }
+    if (!JMODE && V <= 32 && vpk > 0)                              // plan_kernel reset posGain to 0 where the peak is wanted
+        P.voices[v0 + lane].posGain = __fmul_rn(__int_as_float(vpk), 0.5f);
     if (Q2 && lane == 0) {                                         // index 0 is never accumulated into (:218): stays zero
 #pragma unroll 1
         for (int w = 0; w < 4; ++w)
@@ -439,24 +553,26 @@ cudaError_t launch_master_mix(const float* raw, const BusDev* buses, float* mast
 
 // ---------------------------------------------------------------------------------------------
 // Scratch of one block: descs | vgs | te rows | ps rows (offsets through `off`, 256-byte aligned).
-size_t render_scratch_bytes(int nVoices, int nframes, size_t off[4]) {
+size_t render_scratch_bytes(int nVoices, int nframes, size_t off[5]) {
     const size_t tiles = (size_t) (nframes + kT - 1) / kT;
     auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
     off[0] = 0;
     off[1] = up(off[0] + tiles * nVoices * sizeof(TileDesc));
     off[2] = up(off[1] + (size_t) nVoices * sizeof(VoiceGather));
     off[3] = up(off[2] + tiles * nVoices * kT * sizeof(float));
-    return up(off[3] + tiles * nVoices * kT * sizeof(double));
+    off[4] = up(off[3] + tiles * nVoices * kT * sizeof(double));
+    return up(off[4] + (size_t) nVoices * sizeof(int32_t));
 }
 
 void render_bind_scratch(RenderParams& P, void* scratch, int nVoices, int nframes) {
-    size_t off[4];
+    size_t off[5];
     render_scratch_bytes(nVoices, nframes, off);
     unsigned char* b = static_cast<unsigned char*>(scratch);
     P.descs = reinterpret_cast<TileDesc*>(b + off[0]);
     P.vgs = reinterpret_cast<VoiceGather*>(b + off[1]);
     P.te = reinterpret_cast<float*>(b + off[2]);
     P.ps = reinterpret_cast<double*>(b + off[3]);
+    P.walkQueue = reinterpret_cast<int32_t*>(b + off[4]);
     P.nVoices = nVoices;
     P.tilesPerBlock = (nframes + kT - 1) / kT;
 }
@@ -479,6 +595,12 @@ cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream) {
         else plan_kernel<false, false, 1024><<<planGrid, planThreads, 0, stream>>>(P);
     }
     cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    const int wGrid = min((P.nVoices + 127) / 128, 148 * 4);
+    if (P.mode == ZL_MODE_J) walk_kernel<true, false><<<wGrid, 128, 0, stream>>>(P);
+    else if (q3) walk_kernel<false, true><<<wGrid, 128, 0, stream>>>(P);
+    else walk_kernel<false, false><<<wGrid, 128, 0, stream>>>(P);
+    e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     const int gGrid = (nBuses + ZL_GATHER_THREADS / 32 - 1) / (ZL_GATHER_THREADS / 32);
     const bool q1 = (P.quirks & ZL_Q1_TAP_GAIN) != 0, q2 = (P.quirks & ZL_Q2_PREINC) != 0;

@@ -1,4 +1,5 @@
-for v in a; do
+# usage: bash libzl_b200/variants/runv.sh a b c ...   (on the GPU box; each variant = one .so built with different -D)
+for v in "$@"; do
   ZL_B200_LIB=$PWD/libzl_b200/variants/v_$v.so timeout 200 python bench.py --steps 3 --warmup 3 --no-latency --no-cpu-baseline > gpurun_out/v_$v.log 2>&1
   python -c "
 import json,sys
