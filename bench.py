@@ -161,6 +161,10 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def S_BUS_BYTES(args):
+    return args.sessions * BUSES * 2 * args.blocks * FRAMES * 4      # raw bus planes of one step on one GPU
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -217,9 +221,26 @@ def run_cuda(args, rank, world, local_rank):
     out_bytes = (S * BUSES * 2 * n_per_step * 4) + (S * 2 * n_per_step * 4) + NB * S * BUSES * 2 * 4
     state_bytes = 2 * S * BUSES * VOICES * 224
 
+    # --span-mix G: groups of G ranks share one stereo mix per session index -> NCCL sum of the master planes, in place on
+    # the library's own device buffer, inside the timed region (the only collective on the path)
+    mix_group, master_t = None, None
+    if args.span_mix > 1 and dist is not None:
+        from libzl_b200 import shard
+        for ranks in shard.mix_groups(world, args.span_mix):
+            gobj = dist.new_group(ranks=ranks)
+            if rank in ranks:
+                mix_group = gobj
+        e.render(NB, FRAMES, clocks_for(e, 0, NB))          # allocates the output planes
+        mp_, ms_ = C.c_void_p(), C.c_int64()
+        e._chk(e.lib.device_master_ptr(e.ctx, C.byref(mp_), C.byref(ms_)), "device_master_ptr")
+        master_t = torch.as_tensor(shard.DeviceArray(mp_.value, (S, 2, ms_.value)), device=dev)
+
     def step(i, read_back=None):
         e.command_batch(*wl.steps[i])
         e.render(NB, FRAMES, clocks_for(e, i, NB))
+        if master_t is not None:
+            with torch.cuda.stream(stream):
+                shard.reduce_mix(master_t, group=mix_group)
         if read_back is not None:
             e._chk(e.lib.read_master_all(e.ctx, read_back, n_per_step), "read_master_all")
 
@@ -236,7 +257,7 @@ def run_cuda(args, rank, world, local_rank):
     sampler = ClockSampler(local_rank) if rank == 0 else None
     launches0 = e.launch_count()
     vf0, src0 = e.total_counters()
-    e._chk(e.lib.kernel_timing(e.ctx, 1), "kernel_timing")    # CUDA events around each render_kernel launch, same stream
+    e._chk(e.lib.kernel_timing(e.ctx, 2), "kernel_timing")    # CUDA events around each gather_kernel launch, same stream
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     ev[0].record(stream)
     for k in range(args.steps):
@@ -248,7 +269,8 @@ def run_cuda(args, rank, world, local_rank):
     kms, kn = C.c_double(), C.c_uint64()
     e._chk(e.lib.kernel_time(e.ctx, C.byref(kms), C.byref(kn)), "kernel_time")
     e._chk(e.lib.kernel_timing(e.ctx, 0), "kernel_timing")
-    kernel_ms = kms.value / max(1, kn.value)
+    kernel_ms = kms.value / max(1, kn.value)                  # mean duration of one gather_kernel launch (one period)
+    gather_ms_per_step = kms.value / args.steps
     clocks = sampler.stop() if sampler else None
     step_ms = [ev[k].elapsed_time(ev[k + 1]) for k in range(args.steps)]
     vf1, src1 = e.total_counters()
@@ -267,7 +289,7 @@ def run_cuda(args, rank, world, local_rank):
     h2d = wl.steps[0][3].nbytes + wl.steps[0][0].nbytes * 2 + wl.steps[0][2].nbytes + NB * 40
     d2h = S * 2 * n_per_step * 4
     e.lib.host_free(hostp)
-    return dict(e=e, kernel_ms=kernel_ms, elapsed_ms=elapsed_ms, step_ms=step_ms, timed_vf=timed_vf, timed_src=timed_src, launches=kernel_launches,
+    return dict(e=e, kernel_ms=kernel_ms, gather_ms_per_step=gather_ms_per_step, elapsed_ms=elapsed_ms, step_ms=step_ms, timed_vf=timed_vf, timed_src=timed_src, launches=kernel_launches,
                 clocks=clocks, e2e_s=e2e_s, e2e_vf=e2e_vf, h2d=h2d, d2h=d2h, out_bytes=out_bytes, state_bytes=state_bytes,
                 dist=dist, dev=dev, wl=wl, keep=pcm)
 
@@ -357,7 +379,9 @@ def main():
                 f"shape = 16 buses x 8 voices, batched as configs[4] offline render), {args.blocks} periods x {FRAMES} frames per step")
     config = {"workload": workload, "sessions_per_gpu": args.sessions, "buses": BUSES, "voices_per_bus": VOICES,
               "frames": FRAMES, "blocks_per_step": args.blocks, "mode": "Z (libzl process(), quirks faithful)",
-              "outputs": "raw bus + master + peak meters", "parallelism": f"sessions sharded over {args.gpus} GPU(s), no collective",
+              "outputs": "raw bus + master + peak meters", "quirks": args.quirks,
+              "kernels_per_period": "plan_kernel + walk_kernel + gather_kernel (+ one master_mix_kernel per step)", "parallelism": (f"sessions sharded over {args.gpus} GPU(s), no collective" if args.span_mix <= 1 else
+                              f"sessions sharded over {args.gpus} GPU(s); groups of {args.span_mix} GPUs share one mix: NCCL all-reduce of the master planes per step"),
               "l2": "inputs (clip PCM 3 MB/session) larger than L2; no flush needed"}
 
     if args.impl == "reference":
@@ -387,9 +411,13 @@ def main():
     vf, e2e_vf, src = counts.tolist()
     if rank == 0:
         peak, peak_src = peaks()
-        # roofline of the dominant kernel (render_kernel): algorithmic bytes per launch / mean launch duration
-        alg_bytes = (4.0 * r["timed_src"] / args.steps) + r["out_bytes"] + r["state_bytes"]
-        mean_ms = r["kernel_ms"]     # render_kernel alone: events recorded by the library right around its launch
+        # roofline of the dominant kernel (gather_kernel, one launch = one 512-frame period of every session on this GPU):
+        # algorithmic bytes per launch = unique source samples spanned by the voices (counted by the planner) + the raw
+        # bus planes + the integer peaks, all per period; duration = mean of the CUDA-event pairs around each launch
+        step_alg_bytes = (4.0 * r["timed_src"] / args.steps) + r["out_bytes"] + r["state_bytes"]
+        gather_bytes = (4.0 * r["timed_src"] / args.steps + S_BUS_BYTES(args) + args.blocks * args.sessions * BUSES * 2 * 4) / args.blocks
+        alg_bytes = gather_bytes
+        mean_ms = r["kernel_ms"]
         ach = alg_bytes / (mean_ms * 1e-3) / 1e9
         line = {"metric": "voice_frames_per_s", "value": vf / (el_ms * 1e-3), "unit": "voice-frames/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": el_ms / args.steps, "higher_is_better": True,
@@ -399,8 +427,12 @@ def main():
                         "d2h_bytes_per_step": r["d2h"], "what": "zl_command_batch + zl_render + zl_read_master_all (master of every session to pinned host)"},
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
                              "peak_source": peak_src, "frac_of_nominal_8TBs": ach / 8000.0,
-                             "algorithmic_bytes_per_launch": alg_bytes, "bytes_per_voice_frame": alg_bytes / (r["timed_vf"] / args.steps),
-                             "kernel": "zl::render_kernel", "kernel_ms": mean_ms},
+                             "algorithmic_bytes_per_launch": alg_bytes,
+                             "bytes_per_voice_frame": step_alg_bytes / (r["timed_vf"] / args.steps),
+                             "kernel": "zl::gather_kernel", "kernel_ms": mean_ms, "launches_per_step": args.blocks,
+                             "gather_ms_per_step": r["gather_ms_per_step"],
+                             "whole_step_frac": step_alg_bytes / (el_ms / args.steps * 1e-3) / 1e9 / peak,
+                             "whole_step_note": "all algorithmic bytes of a step (source + voice state + raw planes + master + peaks) / ms_per_step: plan, walk, gather and master mix together"},
                 "voice_frames_per_step": vf / args.steps / world}
         if world == 1 and not args.no_latency:
             try:

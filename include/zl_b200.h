@@ -185,7 +185,9 @@ ZL_EXPORT int ZL_FN(sync)(zl_ctx* ctx);
 ZL_EXPORT int ZL_FN(clip_create_from_pcm)(zl_ctx* ctx, const float* const* planar, int32_t nch,
                                           int64_t length, double sample_rate, int32_t* clip_id);
 /* Same, but the PCM is already on the device as interleaved frames (float for mono, float2 for
- * stereo); the buffer is adopted, not copied, and must outlive the clip. */
+ * stereo); the buffer is adopted, not copied, and must outlive the clip.  It must hold length + 8 frames
+ * with frames length .. length + 7 zero (the gather reads its interpolation halo and the frames of
+ * lanes past a voice's end from that padding instead of predicating the loads). */
 ZL_EXPORT int ZL_FN(clip_create_from_device)(zl_ctx* ctx, const void* d_interleaved, int32_t nch,
                                              int64_t length, double sample_rate, int32_t* clip_id);
 ZL_EXPORT int ZL_FN(clip_destroy)(zl_ctx* ctx, int32_t clip_id);
@@ -260,9 +262,10 @@ ZL_EXPORT int ZL_FN(total_counters)(zl_ctx* ctx, uint64_t* voice_frames, uint64_
 ZL_EXPORT int ZL_FN(last_voice_frames)(zl_ctx* ctx, uint64_t* voice_frames);
 /* Number of commands dropped (ring overflow lib/SamplerSynth.cpp:332-334 / unknown clip :330). */
 ZL_EXPORT int ZL_FN(dropped_commands)(zl_ctx* ctx, uint64_t* n);
-/* Optional device timing of the render kernel alone (bench.py roofline): while enabled, every zl_render brackets its
- * kernel launch with CUDA events on the context stream; zl_kernel_time returns and clears the sum (ms) and count. */
-ZL_EXPORT int ZL_FN(kernel_timing)(zl_ctx* ctx, int32_t enable);
+/* Optional device timing (bench.py roofline) with CUDA events on the context stream.  mode 1: every zl_render brackets
+ * its whole plan/walk/gather launch sequence with one event pair; mode 2: one pair around each gather_kernel launch
+ * (the dominant kernel); 0: off.  zl_kernel_time returns and clears the sum (ms) and the number of pairs. */
+ZL_EXPORT int ZL_FN(kernel_timing)(zl_ctx* ctx, int32_t mode);
 ZL_EXPORT int ZL_FN(kernel_time)(zl_ctx* ctx, double* total_ms, uint64_t* launches);
 /* Kernel launches issued by this context so far (bench `gpu_launches`). */
 ZL_EXPORT int ZL_FN(launch_count)(zl_ctx* ctx, uint64_t* n);

@@ -14,7 +14,7 @@
 #include "zl_device.cuh"
 
 namespace zl {
-cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream);
+cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream, cudaEvent_t gatherBegin, cudaEvent_t gatherEnd);
 size_t render_scratch_bytes(int nVoices, int nframes, size_t off[5]);
 void render_bind_scratch(RenderParams& P, void* scratch, int nVoices, int nframes);
 cudaError_t launch_master_mix(const float* raw, const BusDev* buses, float* master, int nSessions, int B, int64_t stride, int64_t n, cudaStream_t stream);
@@ -123,7 +123,7 @@ struct zl_ctx {
     // never waits for the device: slot k is rewritten only after the render that used it two calls ago finished
     void* h_slot[2] = {nullptr, nullptr}; void* d_slot[2] = {nullptr, nullptr}; size_t slotCap[2] = {0, 0};
     // optional kernel timing (bench roofline): event pairs around each render_kernel launch
-    bool timing = false; std::vector<cudaEvent_t> tev; double timedMs = 0.0; uint64_t timedLaunches = 0;
+    int timing = 0; std::vector<cudaEvent_t> tev; double timedMs = 0.0; uint64_t timedLaunches = 0;
     // outputs of the last render
     float* d_out[4] = {nullptr, nullptr, nullptr, nullptr};
     float* d_master = nullptr;
@@ -603,17 +603,23 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     }
     CK(cudaMemsetAsync(ctx->d_walkCount, 0, sizeof(int32_t) * (size_t) nblocks, st));
     P.walkCount = ctx->d_walkCount;
+    // timing 1: one event pair around the whole plan/walk/gather sequence of this call; 2: one pair per gather_kernel launch
     cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (ctx->timing) {
+    if (ctx->timing == 1) {
         CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
         CK(cudaEventRecord(e0, st));
     }
-    for (int blk = 0; blk < nblocks; ++blk) {      // one JACK period = plan_kernel + gather_kernel
+    for (int blk = 0; blk < nblocks; ++blk) {      // one JACK period = plan_kernel + walk_kernel + gather_kernel
         P.blk = blk;
-        CK(launch_render_block(P, st));
+        cudaEvent_t g0 = nullptr, g1 = nullptr;
+        if (ctx->timing == 2) {
+            CK(cudaEventCreate(&g0)); CK(cudaEventCreate(&g1));
+            ctx->tev.push_back(g0); ctx->tev.push_back(g1);
+        }
+        CK(launch_render_block(P, st, g0, g1));
         ctx->launches += 3;
     }
-    if (ctx->timing) {
+    if (ctx->timing == 1) {
         CK(cudaEventRecord(e1, st));
         ctx->tev.push_back(e0); ctx->tev.push_back(e1);
     }
@@ -833,7 +839,7 @@ int zl_last_source_floats(zl_ctx* ctx, uint64_t* n) {
 int zl_dropped_commands(zl_ctx* ctx, uint64_t* n) { if (!ctx || !n) return ZL_ERR_INVALID; *n = ctx->dropped; return ZL_OK; }
 int zl_kernel_timing(zl_ctx* ctx, int32_t enable) {
     if (!ctx) return ZL_ERR_INVALID;
-    ctx->timing = enable != 0;
+    ctx->timing = enable;
     return ZL_OK;
 }
 int zl_kernel_time(zl_ctx* ctx, double* total_ms, uint64_t* launches) {

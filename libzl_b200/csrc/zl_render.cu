@@ -308,15 +308,18 @@ __device__ __forceinline__ bool plan_voice_block(const RenderParams& P, int vIdx
 
 // ---------------------------------------------------------------------------------------------------------------------
 // plan_kernel: thread = voice, CTA = whole buses (planBusesPerCta x V threads, rounded up to a warp).
+#ifndef ZL_PLAN_MINB
+#define ZL_PLAN_MINB 4
+#endif
 template <bool JMODE, bool Q3, int MAXT>
-__global__ void __launch_bounds__(MAXT) plan_kernel(const RenderParams P) {
+__global__ void __launch_bounds__(MAXT, MAXT == 128 ? ZL_PLAN_MINB : 1) plan_kernel(const RenderParams P) {
     const int V = P.V, B = P.B;
     const int tid = threadIdx.x;
     const int lb = tid / V, slot = tid - lb * V;              // bus within the CTA, voice slot within the bus
     const int gb = blockIdx.x * P.planBusesPerCta + lb;        // global bus = session * B + bus
     const bool hasVoice = lb < P.planBusesPerCta && gb < P.nSessions * B;
     const int vIdx = gb * V + slot;                            // global voice
-    const int blk = P.blk, nframes = P.nframes;
+    const int blk = P.blk;
     const unsigned FULL = 0xffffffffu;
 
     // ---- commands of this block: SamplerChannel::process ring drain   lib/SamplerSynth.cpp:118-122 ------------------
@@ -578,7 +581,7 @@ void render_bind_scratch(RenderParams& P, void* scratch, int nVoices, int nframe
 }
 
 // One block (P.blk) of every session: plan, then gather, stream-ordered.
-cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream) {
+cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream, cudaEvent_t gatherBegin, cudaEvent_t gatherEnd) {
     const int V = P.V, nBuses = P.nSessions * P.B;
     if (V < 1 || V > 1024) return cudaErrorInvalidValue;
     P.planBusesPerCta = V >= 128 ? 1 : 128 / V;
@@ -602,6 +605,7 @@ cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream) {
     else walk_kernel<false, false><<<wGrid, 128, 0, stream>>>(P);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
+    if (gatherBegin && (e = cudaEventRecord(gatherBegin, stream)) != cudaSuccess) return e;
     const int gGrid = (nBuses + ZL_GATHER_THREADS / 32 - 1) / (ZL_GATHER_THREADS / 32);
     const bool q1 = (P.quirks & ZL_Q1_TAP_GAIN) != 0, q2 = (P.quirks & ZL_Q2_PREINC) != 0;
     if (P.mode == ZL_MODE_J) gather_kernel<true, false, false><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
@@ -609,7 +613,9 @@ cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream) {
     else if (q1) gather_kernel<false, true, false><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
     else if (q2) gather_kernel<false, false, true><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
     else gather_kernel<false, false, false><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
-    return cudaGetLastError();
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (gatherEnd) return cudaEventRecord(gatherEnd, stream);
+    return cudaSuccess;
 }
 
 }  // namespace zl
