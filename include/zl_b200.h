@@ -234,6 +234,11 @@ ZL_EXPORT int ZL_FN(read_bus)(zl_ctx* ctx, int32_t session, int32_t bus, int32_t
 ZL_EXPORT int ZL_FN(read_master)(zl_ctx* ctx, int32_t session, float* left, float* right, int64_t n);
 /* All sessions' masters at once: out is [n_sessions][2][n]. */
 ZL_EXPORT int ZL_FN(read_master_all)(zl_ctx* ctx, float* out, int64_t n);
+/* Pipelined variant for offline batch renders: enqueues the same copy on a second stream and returns; the next
+ * zl_render computes into the other of two master buffers meanwhile.  out must be pinned (zl_host_alloc) and is
+ * valid after zl_read_wait.  (The reference has no equivalent: JACK hands the period over synchronously.) */
+ZL_EXPORT int ZL_FN(read_master_all_async)(zl_ctx* ctx, float* out, int64_t n);
+ZL_EXPORT int ZL_FN(read_wait)(zl_ctx* ctx);
 /* Device pointers of the output planes, for zero-copy consumers (torch / NCCL):
  * bus planes are [n_buses_total][2][stride], master [n_sessions][2][stride]. */
 ZL_EXPORT int ZL_FN(device_bus_ptr)(zl_ctx* ctx, int32_t which, float** d_ptr, int64_t* stride);

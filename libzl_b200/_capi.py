@@ -91,6 +91,8 @@ SIGNATURES = {
     "read_bus": (C.c_int, [_ctx, C.c_int32, C.c_int32, C.c_int32, _f32p, _f32p, C.c_int64]),
     "read_master": (C.c_int, [_ctx, C.c_int32, _f32p, _f32p, C.c_int64]),
     "read_master_all": (C.c_int, [_ctx, _f32p, C.c_int64]),
+    "read_master_all_async": (C.c_int, [_ctx, _f32p, C.c_int64]),
+    "read_wait": (C.c_int, [_ctx]),
     "device_bus_ptr": (C.c_int, [_ctx, C.c_int32, _P(C.c_void_p), _P(C.c_int64)]),
     "device_master_ptr": (C.c_int, [_ctx, _P(C.c_void_p), _P(C.c_int64)]),
     "read_block_levels": (C.c_int, [_ctx, _P(C.c_int32), _P(C.c_double)]),

@@ -126,7 +126,11 @@ struct zl_ctx {
     int timing = 0; std::vector<cudaEvent_t> tev; double timedMs = 0.0; uint64_t timedLaunches = 0;
     // outputs of the last render
     float* d_out[4] = {nullptr, nullptr, nullptr, nullptr};
-    float* d_master = nullptr;
+    float* d_master = nullptr;            // the master planes of the last render (= d_masterBuf[masterCur])
+    float* d_masterBuf[2] = {nullptr, nullptr};
+    int masterCur = 0; bool pipelined = false;   // pipelined: renders alternate between two master buffers (zl_read_master_all_async)
+    cudaStream_t copyStream = nullptr; cudaEvent_t renderDone = nullptr; cudaEvent_t copyDone[2] = {nullptr, nullptr};
+    bool copyPending[2] = {false, false};
     int32_t* d_peaks = nullptr; double* d_sumsq = nullptr;
     void* d_scratch = nullptr; size_t scratchCap = 0;   // plan -> gather hand-over of one block
     int32_t* d_walkCount = nullptr; int walkCountCap = 0;
@@ -302,9 +306,12 @@ int zl_ctx_destroy(zl_ctx* ctx) {
     for (ClipHost& c : ctx->clips) { if (c.owned && c.d_data) cudaFree(c.d_data); if (c.d_thumb) cudaFree(c.d_thumb); }
     void* frees[] = {ctx->d_clips, ctx->d_slice, ctx->d_voices, ctx->d_buses, ctx->d_cmds, ctx->d_clocks, ctx->d_pow2,
                      ctx->d_counters, ctx->d_bnd, ctx->d_px, ctx->d_mask, ctx->d_tmp, ctx->d_out[0], ctx->d_out[1],
-                     ctx->d_out[2], ctx->d_out[3], ctx->d_master, ctx->d_peaks, ctx->d_sumsq};
+                     ctx->d_out[2], ctx->d_out[3], ctx->d_masterBuf[0], ctx->d_masterBuf[1], ctx->d_peaks, ctx->d_sumsq};
     for (void* p : frees) if (p) cudaFree(p);
     if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+    if (ctx->copyStream) { cudaStreamSynchronize(ctx->copyStream); cudaStreamDestroy(ctx->copyStream); }
+    if (ctx->renderDone) cudaEventDestroy(ctx->renderDone);
+    for (int k = 0; k < 2; ++k) if (ctx->copyDone[k]) cudaEventDestroy(ctx->copyDone[k]);
     if (ctx->d_walkCount) cudaFree(ctx->d_walkCount);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     if (ctx->h_clocks) cudaFreeHost(ctx->h_clocks);
@@ -475,14 +482,24 @@ static int ensure_outputs(zl_ctx* ctx, int nblocks, int nframes) {
     const size_t NB = (size_t) ctx->nbus();
     if (n > ctx->stride) {
         for (int w = 0; w < 4; ++w) { if (ctx->d_out[w]) cudaFree(ctx->d_out[w]); ctx->d_out[w] = nullptr; }
-        if (ctx->d_master) cudaFree(ctx->d_master);
+        if (ctx->copyStream) CK(cudaStreamSynchronize(ctx->copyStream));
+        for (int k = 0; k < 2; ++k) { if (ctx->d_masterBuf[k]) cudaFree(ctx->d_masterBuf[k]); ctx->d_masterBuf[k] = nullptr; ctx->copyPending[k] = false; }
         ctx->d_master = nullptr;
         ctx->stride = 0;
         for (int w = 0; w < 4; ++w)
             if ((ctx->cfg.outputs & (ZL_OUT_RAW << w)) || (w == 0 && (ctx->cfg.outputs & ZL_OUT_MASTER)))   // the master mix reads the raw plane
                 CK(cudaMalloc((void**) &ctx->d_out[w], sizeof(float) * NB * 2 * (size_t) n));
-        if (ctx->cfg.outputs & ZL_OUT_MASTER) CK(cudaMalloc((void**) &ctx->d_master, sizeof(float) * (size_t) ctx->cfg.n_sessions * 2 * (size_t) n));
         ctx->stride = n;
+    }
+    if (ctx->cfg.outputs & ZL_OUT_MASTER) {
+        if (ctx->pipelined) ctx->masterCur ^= 1;          // the previous render's master may still be on its way to the host
+        float*& buf = ctx->d_masterBuf[ctx->masterCur];
+        if (!buf) CK(cudaMalloc((void**) &buf, sizeof(float) * (size_t) ctx->cfg.n_sessions * 2 * (size_t) ctx->stride));
+        ctx->d_master = buf;
+        if (ctx->copyPending[ctx->masterCur]) {           // the copy that read this buffer two renders ago must be done
+            CK(cudaStreamWaitEvent(ctx->stream, ctx->copyDone[ctx->masterCur], 0));
+            ctx->copyPending[ctx->masterCur] = false;
+        }
     }
     {
         size_t off[5];
@@ -676,6 +693,36 @@ int zl_read_master_all(zl_ctx* ctx, float* out, int64_t n) {
     CK(cudaMemcpy2DAsync(out, sizeof(float) * (size_t) N, ctx->d_master, sizeof(float) * (size_t) ctx->stride,
                          sizeof(float) * (size_t) N, rows, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    return ZL_OK;
+}
+
+// Pipelined read-back: the D2H copy of every session's master runs on a second stream while the next zl_render
+// (which from now on alternates between two master buffers) is already computing.  out must be pinned (zl_host_alloc)
+// and stay untouched until zl_read_wait returns.
+int zl_read_master_all_async(zl_ctx* ctx, float* out, int64_t n) {
+    BIND();
+    if (!out) return invalid(ctx, "read_master_all_async: null");
+    const int64_t N = (int64_t) ctx->nblocks * ctx->nframes;
+    if (n != N || !ctx->d_master) { ctx->err = "read_master_all_async: size mismatch or master not enabled"; return ZL_ERR_STATE; }
+    if (!ctx->copyStream) {
+        CK(cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->renderDone, cudaEventDisableTiming));
+        for (int k = 0; k < 2; ++k) CK(cudaEventCreateWithFlags(&ctx->copyDone[k], cudaEventDisableTiming));
+    }
+    ctx->pipelined = true;
+    CK(cudaEventRecord(ctx->renderDone, ctx->stream));
+    CK(cudaStreamWaitEvent(ctx->copyStream, ctx->renderDone, 0));
+    const size_t rows = (size_t) ctx->cfg.n_sessions * 2;
+    CK(cudaMemcpy2DAsync(out, sizeof(float) * (size_t) N, ctx->d_master, sizeof(float) * (size_t) ctx->stride,
+                         sizeof(float) * (size_t) N, rows, cudaMemcpyDeviceToHost, ctx->copyStream));
+    CK(cudaEventRecord(ctx->copyDone[ctx->masterCur], ctx->copyStream));
+    ctx->copyPending[ctx->masterCur] = true;
+    return ZL_OK;
+}
+
+int zl_read_wait(zl_ctx* ctx) {
+    BIND();
+    if (ctx->copyStream) CK(cudaStreamSynchronize(ctx->copyStream));
     return ZL_OK;
 }
 

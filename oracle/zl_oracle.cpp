@@ -873,6 +873,8 @@ int zlo_read_master_all(zl_ctx* ctx, float* out, int64_t n) {
     if ((size_t) n != N || !(ctx->cfg.outputs & ZL_OUT_MASTER)) return ZL_ERR_STATE;
     memcpy(out, ctx->master.data(), ctx->master.size() * 4); return ZL_OK;
 }
+int zlo_read_master_all_async(zl_ctx* ctx, float* out, int64_t n) { return zlo_read_master_all(ctx, out, n); }   // nothing to overlap on the CPU
+int zlo_read_wait(zl_ctx* ctx) { return ctx ? ZL_OK : ZL_ERR_INVALID; }
 int zlo_device_bus_ptr(zl_ctx*, int32_t, float**, int64_t*) { return ZL_ERR_INVALID; }
 int zlo_device_master_ptr(zl_ctx*, float**, int64_t*) { return ZL_ERR_INVALID; }
 int zlo_read_block_levels(zl_ctx* ctx, int32_t* peaks, double* sumsq) {

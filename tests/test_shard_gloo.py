@@ -30,7 +30,7 @@ def _render_sessions(ids):
         c = e.add_clip(pcm)
         e.set_clip_params(c, attack=0.001, decay=0.01, sustain=0.8, release=0.02, pan=float(rng.uniform(-1, 1)), length_beats=1.5)
         for k in range(3):
-            e.play(c, loop=bool(k & 1), midi_channel=k % 2, note=int(60 + rng.integers(-5, 6)), volume=float(rng.uniform(0.3, 1)), session=local)
+            e.play(c, loop=bool(k & 1), midi_channel=k % 2 - 2, note=int(60 + rng.integers(-5, 6)), volume=float(rng.uniform(0.3, 1)), session=local)
     e.render(BLOCKS, FRAMES)
     m = e.master_all().copy()
     e.close()
@@ -81,6 +81,7 @@ def test_two_rank_sharded_render_and_mix_reduce(tmp_path):
         got = np.load(f"{out}.r{r}.npy")
         ids = shard.units_for_rank(N_SESS, r, world)
         assert np.array_equal(got, serial[ids]), f"rank {r}: session masters differ from the single-process render"
+    assert np.abs(serial).max() > 0.05, "the scenario must actually sound"
     mix = np.load(out + ".mix.npy")
     ref = np.zeros_like(mix)
     for s in range(N_SESS):                                          # the reference's serial += order over tracks
