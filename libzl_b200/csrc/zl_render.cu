@@ -396,19 +396,61 @@ __device__ __forceinline__ VoiceGather load_vg(const VoiceGather* p) {
 }
 
 constexpr int kStageV = 16;          // voices per bus whose descriptors are staged through shared memory (else: straight from L2)
+constexpr int kTapStage = kNC * 32 * (8 + 8 + 4);   // one voice-tile in flight: taps a, taps b (float2 per lane-frame), alpha
 
-template <bool JMODE, bool Q1, bool Q2>
+// Asynchronous gather (Ampere-style cp.async, SASS LDGSTS): every lane copies its own two 8-byte taps of each chunk
+// straight into the warp's shared-memory stage, so the loads of voice v + 1 are in flight - at no register cost - while the
+// arithmetic of voice v runs.  A lane only ever reads what it copied itself: cp.async.wait_group is all the
+// synchronisation there is.
+__device__ __forceinline__ void cp_async8(uint32_t saddr, const void* gptr) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(saddr), "l"(gptr) : "memory");
+}
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+// full simple voice-tile: positions -> alpha to the stage, taps by cp.async
+__device__ __forceinline__ void gather_issue_async(const TileDesc& d, const VoiceGather& g, int lane, double laneD, unsigned char* stage) {
+    const float2* __restrict__ src = reinterpret_cast<const float2*>(g.data);
+    const uint32_t sa = (uint32_t) __cvta_generic_to_shared(stage) + lane * 8;
+    float* al = reinterpret_cast<float*>(stage + kNC * 512) + lane;
+#pragma unroll
+    for (int ch = 0; ch < kNC; ++ch) {
+        const double p = __fma_rn(__dadd_rn(laneD, (double) (ch * 32)), d.Ra, d.p0a);
+        float alpha;
+        const int pos = split_pos(p, alpha);
+        cp_async8(sa + ch * 256, src + pos);
+        cp_async8(sa + kNC * 256 + ch * 256, src + pos + 1);
+        al[ch * 32] = alpha;
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+template <bool JMODE, bool Q1>
+__device__ __forceinline__ float gather_finish_async(const TileDesc& d, const VoiceGather& g, const unsigned char* stage, int lane, float laneF,
+                                                     float (&accL)[kNC], float (&accR)[kNC]) {
+    Taps t;
+    const float2* ta = reinterpret_cast<const float2*>(stage) + lane;
+    const float* al = reinterpret_cast<const float*>(stage + kNC * 512) + lane;
+#pragma unroll
+    for (int ch = 0; ch < kNC; ++ch) {
+        t.a[ch] = ta[ch * 32]; t.b[ch] = ta[kNC * 32 + ch * 32]; t.alpha[ch] = al[ch * 32];
+        t.env[ch] = d.Ea == 0.0f ? d.e0a : __fmaf_rn(__fadd_rn(laneF, (float) (ch * 32)), d.Ea, d.e0a);
+    }
+    return gather_finish<JMODE, Q1, true>(g, t, kNC, accL, accR);
+}
+
+template <bool JMODE, bool Q1, bool Q2, bool STAGED>
 __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kernel(const RenderParams P) {
     constexpr int QS = Q2 ? 1 : 0;                            // frame f lands at output index f + QS   :218-221
-    // per warp: this tile's V descriptors and the block's V gather records (V <= kStageV)
-    __shared__ TileDesc sDesc[ZL_GATHER_THREADS / 32][kStageV];
-    __shared__ VoiceGather sVg[ZL_GATHER_THREADS / 32][kStageV];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int gbw = blockIdx.x * (ZL_GATHER_THREADS / 32) + warp;   // global bus
+    constexpr int W = ZL_GATHER_THREADS / 32;
+    // per warp: this tile's V descriptors, the block's V gather records (V <= kStageV) and two tap stages
+    __shared__ TileDesc sDesc[STAGED ? W : 1][kStageV];
+    __shared__ VoiceGather sVg[STAGED ? W : 1][kStageV];
+    __shared__ __align__(16) unsigned char sTap[STAGED ? W : 1][2][kTapStage];
+    const int lane = threadIdx.x & 31, warp = STAGED ? (threadIdx.x >> 5) : 0;
+    const int gbw = blockIdx.x * W + (threadIdx.x >> 5);      // global bus
     if (gbw >= P.nSessions * P.B) return;
     const unsigned FULL = 0xffffffffu;
     const int V = P.V, nframes = P.nframes, blk = P.blk;
-    const bool staged = V <= kStageV;                         // then V * 4 <= 64 int4: two per lane at most
     const double laneD = (double) lane;
     const float laneF = (float) lane;
     const zl_passthrough_params pt = P.buses[gbw].pt;
@@ -421,7 +463,7 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
 
     // descriptor pipeline: tile t + 1's descriptors travel in two registers per lane while tile t is gathered
     int4 nx0 = make_int4(0, 0, 0, 0), nx1 = nx0;
-    if (staged) {
+    if (STAGED) {
         const int4* q = reinterpret_cast<const int4*>(P.descs + v0);
         if (lane < V * 4) nx0 = __ldg(q + lane);
         if (lane + 32 < V * 4) nx1 = __ldg(q + lane + 32);
@@ -433,7 +475,7 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
         const int n = min(kT, nframes - t0);
         const int nchunks = (n + 31) >> 5;
         const TileDesc* __restrict__ dp = P.descs + (size_t) t * P.nVoices + v0;
-        if (staged) {
+        if (STAGED) {
             __syncwarp();                                     // the previous tile's descriptors are no longer read
             if (lane < V * 4) reinterpret_cast<int4*>(sDesc[warp])[lane] = nx0;
             if (lane + 32 < V * 4) reinterpret_cast<int4*>(sDesc[warp])[lane + 32] = nx1;
@@ -447,11 +489,37 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
         float accL[kNC], accR[kNC];
 #pragma unroll
         for (int ch = 0; ch < kNC; ++ch) { accL[ch] = 0.0f; accR[ch] = 0.0f; }
+        // block peak of a voice -> positions model gain  :213-216, :265
+        auto take_peak = [&](float vmax, int vs, int flags) {
+            if (!JMODE && (flags & kWantPeak)) {
+                const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));   // vmax >= +0: int order == float order
+                if (V <= 32) { if (lane == vs) vpk = max(vpk, pk); }
+                else if (lane == 0 && pk > 0)
+                    atomicMax(reinterpret_cast<int*>(&P.voices[v0 + vs].posGain), __float_as_int(__fmul_rn(__int_as_float(pk), 0.5f)));
+            }
+        };
+        int pendV = -1, pb = 0;                               // STAGED: the voice whose taps are in flight, and its stage
         for (int vs = 0; vs < V; ++vs) {
-            const TileDesc d = staged ? sDesc[warp][vs] : load_desc(dp + vs);
+            const TileDesc d = STAGED ? sDesc[warp][vs] : load_desc(dp + vs);
             const int nr = d.nrend & kCountMask;              // warp-uniform
             if (nr == 0) continue;
-            const VoiceGather g = staged ? sVg[warp][vs] : load_vg(P.vgs + v0 + vs);
+            const VoiceGather g = STAGED ? sVg[warp][vs] : load_vg(P.vgs + v0 + vs);
+            if (STAGED && (d.nrend & kSimpleBit) && nr == kT) {
+                gather_issue_async(d, g, lane, laneD, sTap[warp][pb ^ 1]);
+                if (pendV >= 0) {                             // slot order: the earlier voice is accumulated first
+                    cp_async_wait<1>();
+                    const VoiceGather gp = sVg[warp][pendV];
+                    take_peak(gather_finish_async<JMODE, Q1>(sDesc[warp][pendV], gp, sTap[warp][pb], lane, laneF, accL, accR), pendV, gp.nch);
+                }
+                pendV = vs; pb ^= 1;
+                continue;
+            }
+            if (STAGED && pendV >= 0) {
+                cp_async_wait<0>();
+                const VoiceGather gp = sVg[warp][pendV];
+                take_peak(gather_finish_async<JMODE, Q1>(sDesc[warp][pendV], gp, sTap[warp][pb], lane, laneF, accL, accR), pendV, gp.nch);
+                pendV = -1;
+            }
             Taps tp;
             float vmax;
             if ((d.nrend & kSimpleBit) && nr == kT) {
@@ -465,12 +533,12 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
                 }
                 vmax = gather_finish<JMODE, Q1, false>(g, tp, nchunks, accL, accR);
             }
-            if (!JMODE && (g.nch & kWantPeak)) {               // block peak of the voice -> positions model gain  :213-216, :265
-                const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));   // vmax >= +0: int order == float order
-                if (V <= 32) { if (lane == vs) vpk = max(vpk, pk); }
-                else if (lane == 0 && pk > 0)
-                    atomicMax(reinterpret_cast<int*>(&P.voices[v0 + vs].posGain), __float_as_int(__fmul_rn(__int_as_float(pk), 0.5f)));
-            }
+            take_peak(vmax, vs, g.nch);
+        }
+        if (STAGED && pendV >= 0) {
+            cp_async_wait<0>();
+            const VoiceGather gp = sVg[warp][pendV];
+            take_peak(gather_finish_async<JMODE, Q1>(sDesc[warp][pendV], gp, sTap[warp][pb], lane, laneF, accL, accR), pendV, gp.nch);
         }
         // raw SamplerChannel ports, then JackPassthrough and the meters on the register accumulators
 #pragma unroll
@@ -608,11 +676,17 @@ cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream, cudaEvent_
     if (gatherBegin && (e = cudaEventRecord(gatherBegin, stream)) != cudaSuccess) return e;
     const int gGrid = (nBuses + ZL_GATHER_THREADS / 32 - 1) / (ZL_GATHER_THREADS / 32);
     const bool q1 = (P.quirks & ZL_Q1_TAP_GAIN) != 0, q2 = (P.quirks & ZL_Q2_PREINC) != 0;
-    if (P.mode == ZL_MODE_J) gather_kernel<true, false, false><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
-    else if (q1 && q2) gather_kernel<false, true, true><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
-    else if (q1) gather_kernel<false, true, false><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
-    else if (q2) gather_kernel<false, false, true><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
-    else gather_kernel<false, false, false><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);
+#define ZL_LAUNCH_GATHER(J, A, B2)                                                                          \
+    do {                                                                                                   \
+        if (V <= kStageV) gather_kernel<J, A, B2, true><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);       \
+        else gather_kernel<J, A, B2, false><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);                   \
+    } while (0)
+    if (P.mode == ZL_MODE_J) ZL_LAUNCH_GATHER(true, false, false);
+    else if (q1 && q2) ZL_LAUNCH_GATHER(false, true, true);
+    else if (q1) ZL_LAUNCH_GATHER(false, true, false);
+    else if (q2) ZL_LAUNCH_GATHER(false, false, true);
+    else ZL_LAUNCH_GATHER(false, false, false);
+#undef ZL_LAUNCH_GATHER
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     if (gatherEnd) return cudaEventRecord(gatherEnd, stream);
     return cudaSuccess;
