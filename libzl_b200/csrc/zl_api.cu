@@ -14,7 +14,8 @@
 #include "zl_device.cuh"
 
 namespace zl {
-cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream, cudaEvent_t gatherBegin, cudaEvent_t gatherEnd);
+cudaError_t launch_plan(RenderParams& P, cudaStream_t stream);
+cudaError_t launch_gather(RenderParams& P, cudaStream_t stream, cudaEvent_t gatherBegin, cudaEvent_t gatherEnd);
 size_t render_scratch_bytes(int nVoices, int nframes, size_t off[5]);
 void render_bind_scratch(RenderParams& P, void* scratch, int nVoices, int nframes);
 cudaError_t launch_master_mix(const float* raw, const BusDev* buses, float* master, int nSessions, int B, int64_t stride, int64_t n, cudaStream_t stream);
@@ -132,7 +133,9 @@ struct zl_ctx {
     cudaStream_t copyStream = nullptr; cudaEvent_t renderDone = nullptr; cudaEvent_t copyDone[2] = {nullptr, nullptr};
     bool copyPending[2] = {false, false};
     int32_t* d_peaks = nullptr; double* d_sumsq = nullptr;
-    void* d_scratch = nullptr; size_t scratchCap = 0;   // plan -> gather hand-over of one block
+    void* d_scratch = nullptr; size_t scratchCap = 0;   // plan -> gather hand-over: two blocks (double-buffered by block parity)
+    cudaStream_t planStream = nullptr;                  // high priority: plan/walk of period b + 1 overlap the gather of period b
+    cudaEvent_t evStart = nullptr, evPlan[2] = {nullptr, nullptr}, evGather[2] = {nullptr, nullptr};
     int32_t* d_walkCount = nullptr; int walkCountCap = 0;
     int64_t stride = 0; size_t lvlCap = 0;
     int nblocks = 0, nframes = 0;
@@ -309,6 +312,9 @@ int zl_ctx_destroy(zl_ctx* ctx) {
                      ctx->d_out[2], ctx->d_out[3], ctx->d_masterBuf[0], ctx->d_masterBuf[1], ctx->d_peaks, ctx->d_sumsq};
     for (void* p : frees) if (p) cudaFree(p);
     if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+    if (ctx->planStream) { cudaStreamSynchronize(ctx->planStream); cudaStreamDestroy(ctx->planStream); }
+    if (ctx->evStart) cudaEventDestroy(ctx->evStart);
+    for (int k = 0; k < 2; ++k) { if (ctx->evPlan[k]) cudaEventDestroy(ctx->evPlan[k]); if (ctx->evGather[k]) cudaEventDestroy(ctx->evGather[k]); }
     if (ctx->copyStream) { cudaStreamSynchronize(ctx->copyStream); cudaStreamDestroy(ctx->copyStream); }
     if (ctx->renderDone) cudaEventDestroy(ctx->renderDone);
     for (int k = 0; k < 2; ++k) if (ctx->copyDone[k]) cudaEventDestroy(ctx->copyDone[k]);
@@ -506,9 +512,8 @@ static int ensure_outputs(zl_ctx* ctx, int nblocks, int nframes) {
         const size_t need = render_scratch_bytes((int) (NB * ctx->cfg.voices_per_bus), nframes, off);
         if (need > ctx->scratchCap) {
             if (ctx->d_scratch) cudaFree(ctx->d_scratch);
-    if (ctx->d_walkCount) cudaFree(ctx->d_walkCount);
             ctx->d_scratch = nullptr; ctx->scratchCap = 0;
-            CK(cudaMalloc(&ctx->d_scratch, need));
+            CK(cudaMalloc(&ctx->d_scratch, 2 * need));   // two hand-over buffers, by block parity
             ctx->scratchCap = need;
         }
     }
@@ -611,7 +616,6 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     P.nSessions = ctx->cfg.n_sessions; P.B = ctx->cfg.buses_per_session; P.V = ctx->cfg.voices_per_bus;
     P.nClips = (int) ctx->clips.size();
     P.nblocks = nblocks; P.nframes = nframes; P.mode = ctx->cfg.mode; P.quirks = ctx->cfg.quirks;
-    render_bind_scratch(P, ctx->d_scratch, (int) (NB * ctx->cfg.voices_per_bus), nframes);
     if (nblocks > ctx->walkCountCap) {
         if (ctx->d_walkCount) cudaFree(ctx->d_walkCount);
         ctx->d_walkCount = nullptr; ctx->walkCountCap = 0;
@@ -620,20 +624,49 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     }
     CK(cudaMemsetAsync(ctx->d_walkCount, 0, sizeof(int32_t) * (size_t) nblocks, st));
     P.walkCount = ctx->d_walkCount;
+    // Two streams: plan/walk of period b + 1 (high priority) run beside the gather of period b.  The positions-model gain
+    // is then written by the gather alone (V <= 32); with more voices per bus it needs the planner's reset first -> one stream.
+    const bool overlap = ctx->cfg.voices_per_bus <= 32 && nblocks > 1;
+    if (overlap && !ctx->planStream) {
+        int lo = 0, hi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CK(cudaStreamCreateWithPriority(&ctx->planStream, cudaStreamNonBlocking, hi));
+        CK(cudaEventCreateWithFlags(&ctx->evStart, cudaEventDisableTiming));
+        for (int k = 0; k < 2; ++k) {
+            CK(cudaEventCreateWithFlags(&ctx->evPlan[k], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&ctx->evGather[k], cudaEventDisableTiming));
+        }
+    }
+    cudaStream_t ps = overlap ? ctx->planStream : st;
     // timing 1: one event pair around the whole plan/walk/gather sequence of this call; 2: one pair per gather_kernel launch
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->timing == 1) {
         CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
         CK(cudaEventRecord(e0, st));
     }
+    if (overlap) {                                  // everything queued on st so far (tables, commands, counters) precedes the planner
+        CK(cudaEventRecord(ctx->evStart, st));
+        CK(cudaStreamWaitEvent(ps, ctx->evStart, 0));
+    }
+    size_t soff[5];
+    const size_t scratchBytes = render_scratch_bytes((int) (NB * ctx->cfg.voices_per_bus), nframes, soff);
     for (int blk = 0; blk < nblocks; ++blk) {      // one JACK period = plan_kernel + walk_kernel + gather_kernel
+        const int par = blk & 1;
         P.blk = blk;
+        render_bind_scratch(P, static_cast<unsigned char*>(ctx->d_scratch) + (size_t) par * scratchBytes, (int) (NB * ctx->cfg.voices_per_bus), nframes);
+        if (overlap && blk >= 2) CK(cudaStreamWaitEvent(ps, ctx->evGather[par], 0));   // gather(blk - 2) has released this hand-over buffer
+        CK(launch_plan(P, ps));
+        if (overlap) {
+            CK(cudaEventRecord(ctx->evPlan[par], ps));
+            CK(cudaStreamWaitEvent(st, ctx->evPlan[par], 0));
+        }
         cudaEvent_t g0 = nullptr, g1 = nullptr;
         if (ctx->timing == 2) {
             CK(cudaEventCreate(&g0)); CK(cudaEventCreate(&g1));
             ctx->tev.push_back(g0); ctx->tev.push_back(g1);
         }
-        CK(launch_render_block(P, st, g0, g1));
+        CK(launch_gather(P, st, g0, g1));
+        if (overlap) CK(cudaEventRecord(ctx->evGather[par], st));
         ctx->launches += 3;
     }
     if (ctx->timing == 1) {

@@ -296,7 +296,9 @@ __device__ __forceinline__ bool plan_voice_block(const RenderParams& P, int vIdx
         // positions model update   lib/SamplerSynthVoice.cpp:265-267.  Z: the gain is this block's peak of l + r, which only
         // the gather knows: it is reset here and max-ed in by gather_kernel (kWantPeak).
         if (h.clip >= 0 && (JMODE || (h.flags & VF_HAS_POSID))) {
-            h.posGain = 0.0f;
+            // J: gain 0.  Z, V <= 32: gather_kernel stores the peak (a plain store by the lane that owns the voice, so this
+            // kernel may already be planning the next period on another stream).  Z, V > 32: reset here, atomicMax there.
+            if (JMODE || P.V > 32) rec->posGain = 0.0f;
             if (!JMODE) g.nch |= kWantPeak;
             h.posProgress = __double2float_rn(__ddiv_rn(h.p, h.srcLen));
         }
@@ -568,8 +570,10 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
             }
         }
     }
-    if (!JMODE && V <= 32 && vpk > 0)                              // plan_kernel reset posGain to 0 where the peak is wanted
-        P.voices[v0 + lane].posGain = __fmul_rn(__int_as_float(vpk), 0.5f);
+    if (!JMODE && V <= 32 && lane < V) {                           // the positions-model gain of the voices that take it this period
+        const int flags = STAGED ? sVg[warp][lane].nch : __ldg(&P.vgs[v0 + lane].nch);
+        if (flags & kWantPeak) P.voices[v0 + lane].posGain = __fmul_rn(__int_as_float(vpk), 0.5f);
+    }
     if (Q2 && lane == 0) {                                         // index 0 is never accumulated into (:218): stays zero
 #pragma unroll 1
         for (int w = 0; w < 4; ++w)
@@ -648,8 +652,10 @@ void render_bind_scratch(RenderParams& P, void* scratch, int nVoices, int nframe
     P.tilesPerBlock = (nframes + kT - 1) / kT;
 }
 
-// One block (P.blk) of every session: plan, then gather, stream-ordered.
-cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream, cudaEvent_t gatherBegin, cudaEvent_t gatherEnd) {
+// One block (P.blk) of every session: launch_plan (plan_kernel + walk_kernel), then launch_gather.  The two may sit on
+// different streams (zl_api.cu orders them with events and double-buffers the hand-over), so that the latency-bound
+// planner of period b + 1 fills the issue slots the gather of period b leaves idle.
+cudaError_t launch_plan(RenderParams& P, cudaStream_t stream) {
     const int V = P.V, nBuses = P.nSessions * P.B;
     if (V < 1 || V > 1024) return cudaErrorInvalidValue;
     P.planBusesPerCta = V >= 128 ? 1 : 128 / V;
@@ -671,8 +677,12 @@ cudaError_t launch_render_block(RenderParams& P, cudaStream_t stream, cudaEvent_
     if (P.mode == ZL_MODE_J) walk_kernel<true, false><<<wGrid, 128, 0, stream>>>(P);
     else if (q3) walk_kernel<false, true><<<wGrid, 128, 0, stream>>>(P);
     else walk_kernel<false, false><<<wGrid, 128, 0, stream>>>(P);
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_gather(RenderParams& P, cudaStream_t stream, cudaEvent_t gatherBegin, cudaEvent_t gatherEnd) {
+    const int V = P.V, nBuses = P.nSessions * P.B;
+    cudaError_t e;
     if (gatherBegin && (e = cudaEventRecord(gatherBegin, stream)) != cudaSuccess) return e;
     const int gGrid = (nBuses + ZL_GATHER_THREADS / 32 - 1) / (ZL_GATHER_THREADS / 32);
     const bool q1 = (P.quirks & ZL_Q1_TAP_GAIN) != 0, q2 = (P.quirks & ZL_Q2_PREINC) != 0;

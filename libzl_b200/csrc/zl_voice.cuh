@@ -72,7 +72,7 @@ __device__ __forceinline__ void hot_load(VoiceHot& h, const VoiceDev& v) {
 __device__ __forceinline__ void hot_store(const VoiceHot& h, VoiceDev& v) {
     v.p = h.p; v.nextLoopTick = h.nextLoopTick; v.nextLoopUsecs = h.nextLoopUsecs;
     v.env = h.env; v.rRate = h.rRate;
-    v.posGain = h.posGain; v.posProgress = h.posProgress;
+    v.posProgress = h.posProgress;      // posGain is written where it is produced (plan_voice_block / gather_kernel), never copied back
     v.adsrState = h.adsrState; v.flags = h.flags; v.sound = h.sound; v.clip = h.clip;
 }
 
