@@ -8,7 +8,9 @@ CSRC = os.path.join(HERE, "csrc")
 SOURCES = ["zl_api.cu", "zl_render.cu", "zl_thumb.cu"]
 HEADERS = ["zl_device.cuh", "zl_voice.cuh", os.path.join("..", "..", "include", "zl_b200.h")]
 OUT = os.path.join(HERE, "libzl_b200.so")
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+# -fmad=false: no a*b+c contraction anywhere (the scalar audio math uses _rn intrinsics already; the packed f32x2
+# intrinsics __fmul2_rn/__fadd2_rn would otherwise be fused into FFMA2 and break bit-exactness); explicit __fma_rn stays an FMA
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared", "-cudart", "shared"]
 
 

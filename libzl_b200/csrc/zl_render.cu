@@ -42,13 +42,6 @@ constexpr int kSimpleBit = 1 << 29;   // one position segment, one envelope segm
 constexpr int kCountMask = (1 << 20) - 1;
 constexpr int kWantPeak = 1 << 8;     // VoiceGather.nch flag: the positions model takes this block's peak  :265-267
 
-template <bool Q1>
-__device__ __forceinline__ float lerp_gain_z(float a, float b, float ia, float alpha, float g, float env, float vol) {
-    if (Q1)   // lib/SamplerSynthVoice.cpp:204-205 as written: gain/env/volume multiply only the second tap
-        return __fadd_rn(__fmul_rn(a, ia), __fmul_rn(__fmul_rn(__fmul_rn(__fmul_rn(b, alpha), g), env), vol));
-    return __fmul_rn(__fmul_rn(__fmul_rn(__fadd_rn(__fmul_rn(a, ia), __fmul_rn(b, alpha)), g), env), vol);
-}
-
 // The gather of one voice x one tile is split in two so all of the tile's loads are in flight together:
 // gather_issue computes (pos, alpha, env) per lane-frame and issues both tap loads of every chunk; gather_finish does
 // the arithmetic.  Lanes past the voice's last frame read zeros (from the clip's zero padding or not at all), so they add
@@ -130,32 +123,40 @@ __device__ __forceinline__ void gather_issue_simple(const TileDesc& d, const Voi
 }
 
 // Interpolation, gains, (Z) M/S pan, bus accumulate.  J: juce_Sampler.cpp:128-152, Z: lib/SamplerSynthVoice.cpp:198-221
+// The left and right channels go through the same chain, so they ride together in Blackwell's packed FP32x2 instructions
+// (FMUL2 / FADD2: two independently IEEE-rounded f32 operations per lane per issue slot; no contraction, _rn intrinsics).
+// acc[ch] = (L, R) of the bus for this lane's frame of chunk ch.
 template <bool JMODE, bool Q1, bool FULL>
-__device__ __forceinline__ float gather_finish(const VoiceGather& g, const Taps& t, int nchunks, float (&accL)[kNC], float (&accR)[kNC]) {
+__device__ __forceinline__ float gather_finish(const VoiceGather& g, const Taps& t, int nchunks, float nz, float2 (&acc)[kNC]) {
     float vmax = 0.0f;
+    const float2 g2 = make_float2(g.gain, g.gain), vol2 = make_float2(g.vol, g.vol), nz2 = make_float2(nz, nz);
 #pragma unroll
     for (int ch = 0; ch < kNC; ++ch) {
         if (FULL || ch < nchunks) {                                   // warp-uniform
             const float alpha = t.alpha[ch], env = t.env[ch];
             const float ia = __fsub_rn(1.0f, alpha);
-            float l, r;
+            const float2 al2 = make_float2(alpha, alpha), ia2 = make_float2(ia, ia), env2 = make_float2(env, env);
+            // ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 (it does not for the scalar forms), which would change
+            // the rounding: every product that feeds an add is therefore written as fma(x, y, nz) with nz = -0.0f that the
+            // compiler cannot see through (derived from a kernel parameter) - exactly RN(x*y), sign of zero included.
+            float2 lr;
             if (JMODE) {
-                l = __fadd_rn(__fmul_rn(t.a[ch].x, ia), __fmul_rn(t.b[ch].x, alpha));
-                r = __fadd_rn(__fmul_rn(t.a[ch].y, ia), __fmul_rn(t.b[ch].y, alpha));
+                lr = __fadd2_rn(__ffma2_rn(t.a[ch], ia2, nz2), __ffma2_rn(t.b[ch], al2, nz2));
                 const float ge = __fmul_rn(g.gain, env);
-                l = __fmul_rn(l, ge);
-                r = __fmul_rn(r, ge);
+                lr = __ffma2_rn(lr, make_float2(ge, ge), nz2);
             } else {
-                l = lerp_gain_z<Q1>(t.a[ch].x, t.b[ch].x, ia, alpha, g.gain, env, g.vol);
-                r = lerp_gain_z<Q1>(t.a[ch].y, t.b[ch].y, ia, alpha, g.gain, env, g.vol);
-                const float m = __fmul_rn(0.5f, __fadd_rn(l, r));   // :208 (0.5*(l+r) in f64 is exact)
-                const float sd = __fsub_rn(l, r);
-                l = __fadd_rn(__fmul_rn(g.lPan, m), sd);
-                r = __fsub_rn(__fmul_rn(g.rPan, m), sd);
+                if (Q1)   // lib/SamplerSynthVoice.cpp:204-205 as written: gain/env/volume multiply only the second tap
+                    lr = __fadd2_rn(__ffma2_rn(t.a[ch], ia2, nz2),
+                                    __ffma2_rn(__fmul2_rn(__fmul2_rn(__fmul2_rn(t.b[ch], al2), g2), env2), vol2, nz2));
+                else
+                    lr = __fmul2_rn(__fmul2_rn(__fmul2_rn(__fadd2_rn(__ffma2_rn(t.a[ch], ia2, nz2), __ffma2_rn(t.b[ch], al2, nz2)), g2), env2), vol2);
+                const float m = __fmul_rn(0.5f, __fadd_rn(lr.x, lr.y));   // :208 (0.5*(l+r) in f64 is exact)
+                const float sd = __fsub_rn(lr.x, lr.y);
+                lr.x = __fadd_rn(__fmul_rn(g.lPan, m), sd);
+                lr.y = __fsub_rn(__fmul_rn(g.rPan, m), sd);
             }
-            accL[ch] = __fadd_rn(accL[ch], l);                      // lanes past the voice's end add +0
-            accR[ch] = __fadd_rn(accR[ch], r);
-            vmax = fmaxf(vmax, __fadd_rn(l, r));
+            acc[ch] = __fadd2_rn(acc[ch], lr);                      // lanes past the voice's end add +0
+            vmax = fmaxf(vmax, __fadd_rn(lr.x, lr.y));
         }
     }
     return vmax;
@@ -428,7 +429,7 @@ __device__ __forceinline__ void gather_issue_async(const TileDesc& d, const Voic
 
 template <bool JMODE, bool Q1>
 __device__ __forceinline__ float gather_finish_async(const TileDesc& d, const VoiceGather& g, const unsigned char* stage, int lane, float laneF,
-                                                     float (&accL)[kNC], float (&accR)[kNC]) {
+                                                     float nz, float2 (&acc)[kNC]) {
     Taps t;
     const float2* ta = reinterpret_cast<const float2*>(stage) + lane;
     const float* al = reinterpret_cast<const float*>(stage + kNC * 512) + lane;
@@ -437,7 +438,7 @@ __device__ __forceinline__ float gather_finish_async(const TileDesc& d, const Vo
         t.a[ch] = ta[ch * 32]; t.b[ch] = ta[kNC * 32 + ch * 32]; t.alpha[ch] = al[ch * 32];
         t.env[ch] = d.Ea == 0.0f ? d.e0a : __fmaf_rn(__fadd_rn(laneF, (float) (ch * 32)), d.Ea, d.e0a);
     }
-    return gather_finish<JMODE, Q1, true>(g, t, kNC, accL, accR);
+    return gather_finish<JMODE, Q1, true>(g, t, kNC, nz, acc);
 }
 
 template <bool JMODE, bool Q1, bool Q2, bool STAGED>
@@ -448,13 +449,15 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
     __shared__ TileDesc sDesc[STAGED ? W : 1][kStageV];
     __shared__ VoiceGather sVg[STAGED ? W : 1][kStageV];
     __shared__ __align__(16) unsigned char sTap[STAGED ? W : 1][2][kTapStage];
-    const int lane = threadIdx.x & 31, warp = STAGED ? (threadIdx.x >> 5) : 0;
+    int lane = threadIdx.x & 31, warp = STAGED ? (threadIdx.x >> 5) : 0;
+    asm volatile("" : "+r"(lane), "+r"(warp));            // opaque: keeps ptxas from re-deriving them from S2R inside the voice loop
     const int gbw = blockIdx.x * W + (threadIdx.x >> 5);      // global bus
     if (gbw >= P.nSessions * P.B) return;
     const unsigned FULL = 0xffffffffu;
     const int V = P.V, nframes = P.nframes, blk = P.blk;
     const double laneD = (double) lane;
     const float laneF = (float) lane;
+    const float nz = __int_as_float((int) (0x80000000u | ((unsigned) P.nframes >> 31)));   // -0.0f, opaque to the compiler (see gather_finish)
     const zl_passthrough_params pt = P.buses[gbw].pt;
     const int64_t off = (int64_t) blk * nframes;
     const int64_t rowL = ((int64_t) gbw * 2) * P.stride + off, rowR = rowL + P.stride;
@@ -488,9 +491,9 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
                 if (lane + 32 < V * 4) nx1 = __ldg(q + lane + 32);
             }
         }
-        float accL[kNC], accR[kNC];
+        float2 acc[kNC];
 #pragma unroll
-        for (int ch = 0; ch < kNC; ++ch) { accL[ch] = 0.0f; accR[ch] = 0.0f; }
+        for (int ch = 0; ch < kNC; ++ch) acc[ch] = make_float2(0.0f, 0.0f);
         // block peak of a voice -> positions model gain  :213-216, :265
         auto take_peak = [&](float vmax, int vs, int flags) {
             if (!JMODE && (flags & kWantPeak)) {
@@ -511,7 +514,7 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
                 if (pendV >= 0) {                             // slot order: the earlier voice is accumulated first
                     cp_async_wait<1>();
                     const VoiceGather gp = sVg[warp][pendV];
-                    take_peak(gather_finish_async<JMODE, Q1>(sDesc[warp][pendV], gp, sTap[warp][pb], lane, laneF, accL, accR), pendV, gp.nch);
+                    take_peak(gather_finish_async<JMODE, Q1>(sDesc[warp][pendV], gp, sTap[warp][pb], lane, laneF, nz, acc), pendV, gp.nch);
                 }
                 pendV = vs; pb ^= 1;
                 continue;
@@ -519,28 +522,28 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
             if (STAGED && pendV >= 0) {
                 cp_async_wait<0>();
                 const VoiceGather gp = sVg[warp][pendV];
-                take_peak(gather_finish_async<JMODE, Q1>(sDesc[warp][pendV], gp, sTap[warp][pb], lane, laneF, accL, accR), pendV, gp.nch);
+                take_peak(gather_finish_async<JMODE, Q1>(sDesc[warp][pendV], gp, sTap[warp][pb], lane, laneF, nz, acc), pendV, gp.nch);
                 pendV = -1;
             }
             Taps tp;
             float vmax;
             if ((d.nrend & kSimpleBit) && nr == kT) {
                 gather_issue_simple<true>(d, g, lane, laneD, laneF, tp);
-                vmax = gather_finish<JMODE, Q1, true>(g, tp, kNC, accL, accR);
+                vmax = gather_finish<JMODE, Q1, true>(g, tp, kNC, nz, acc);
             } else {
                 if (d.nrend & kSimpleBit) gather_issue_simple<false>(d, g, lane, laneD, laneF, tp);
                 else {
                     const size_t vt = (size_t) t * P.nVoices + v0 + vs;
                     gather_issue<JMODE>(d, g, P.te + vt * kT, P.ps + vt * kT, lane, nchunks, tp);
                 }
-                vmax = gather_finish<JMODE, Q1, false>(g, tp, nchunks, accL, accR);
+                vmax = gather_finish<JMODE, Q1, false>(g, tp, nchunks, nz, acc);
             }
             take_peak(vmax, vs, g.nch);
         }
         if (STAGED && pendV >= 0) {
             cp_async_wait<0>();
             const VoiceGather gp = sVg[warp][pendV];
-            take_peak(gather_finish_async<JMODE, Q1>(sDesc[warp][pendV], gp, sTap[warp][pb], lane, laneF, accL, accR), pendV, gp.nch);
+            take_peak(gather_finish_async<JMODE, Q1>(sDesc[warp][pendV], gp, sTap[warp][pb], lane, laneF, nz, acc), pendV, gp.nch);
         }
         // raw SamplerChannel ports, then JackPassthrough and the meters on the register accumulators
 #pragma unroll
@@ -549,17 +552,17 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
             const int j = t0 + c + QS;                            // output index in the block
             if (c < n && j < nframes) {
                 float dL, dR;
-                if (P.out[0]) { P.out[0][rowL + j] = accL[ch]; P.out[0][rowR + j] = accR[ch]; }
-                passthrough_pair(pt, pt.dry_amount, accL[ch], accR[ch], dL, dR);
+                if (P.out[0]) { P.out[0][rowL + j] = acc[ch].x; P.out[0][rowR + j] = acc[ch].y; }
+                passthrough_pair(pt, pt.dry_amount, acc[ch].x, acc[ch].y, dL, dR);
                 if (P.out[1]) { P.out[1][rowL + j] = dL; P.out[1][rowR + j] = dR; }
                 if (P.out[2]) {
                     float xL, xR;
-                    passthrough_pair(pt, pt.wet_fx1_amount, accL[ch], accR[ch], xL, xR);
+                    passthrough_pair(pt, pt.wet_fx1_amount, acc[ch].x, acc[ch].y, xL, xR);
                     P.out[2][rowL + j] = xL; P.out[2][rowR + j] = xR;
                 }
                 if (P.out[3]) {
                     float xL, xR;
-                    passthrough_pair(pt, pt.wet_fx2_amount, accL[ch], accR[ch], xL, xR);
+                    passthrough_pair(pt, pt.wet_fx2_amount, acc[ch].x, acc[ch].y, xL, xR);
                     P.out[3][rowL + j] = xL; P.out[3][rowR + j] = xR;
                 }
                 pkL = max(pkL, peak_int(dL)); pkR = max(pkR, peak_int(dR));
