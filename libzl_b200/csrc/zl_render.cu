@@ -39,7 +39,10 @@ constexpr int kNC = kT / 32;         // 32-frame chunks per tile
 
 constexpr int kSlotBit = 1 << 30;     // positions come from the voice-tile's position row
 constexpr int kSimpleBit = 1 << 29;   // one position segment, one envelope segment, stereo, every tap inside the sample
+constexpr int kRingBit = 1 << 28;     // simple, full tile, and the source window fits one staging slot: p0b = window address, Rb = (first frame, bytes)
 constexpr int kCountMask = (1 << 20) - 1;
+constexpr int kSlotBytes = 2304;      // one staged source window: 128 frames x ratio 2.2 x 8 B + halo; multiple of 16
+constexpr int kSlots = 3;             // staging slots per warp: two windows in flight behind the one being gathered
 constexpr int kWantPeak = 1 << 8;     // VoiceGather.nch flag: the positions model takes this block's peak  :265-267
 
 // The gather of one voice x one tile is split in two so all of the tile's loads are in flight together:
@@ -176,6 +179,18 @@ __device__ __forceinline__ int peak_int(float x) {   // lib/AudioLevels.cpp:365-
     return __float2int_rz(fabsf(__fmul_rn(131072.0f, x)));
 }
 
+// Simple full tiles whose source window [first tap, last tap + 1] fits a staging slot are gathered through shared memory:
+// the planner leaves the window's 16-byte aligned address and size in the (unused) second position segment.
+__device__ __forceinline__ void mark_ring(TileDesc& d, const float* data, int cnt, int lastPos) {
+    if (cnt != kT || !(d.nrend & kSimpleBit)) return;
+    const int base = (int) d.p0a & ~1;                                   // 16-byte aligned first frame (stereo: 8 B per frame)
+    const int bytes = ((lastPos + 2 - base) * 8 + 15) & ~15;             // frames base .. lastPos + 1
+    if (bytes > kSlotBytes || (reinterpret_cast<uintptr_t>(data) & 15)) return;
+    d.nrend |= kRingBit;
+    d.p0b = __longlong_as_double((long long) (reinterpret_cast<uintptr_t>(data) + (size_t) base * 8));
+    d.Rb = __hiloint2double(base, bytes);
+}
+
 // What a position plan may change before it is accepted.
 struct PlanUndo {
     double p; uint64_t nextLoopTick, nextLoopUsecs; int32_t fWrap, spanStart, lastPos; uint32_t span;
@@ -243,6 +258,7 @@ __device__ __forceinline__ bool plan_voice_block(const RenderParams& P, int vIdx
                     d.cb = n; d.ce = n; d.ct = INT_MAX;
                     const int lastPos = (int) __fma_rn((double) (t0 + n - 1), R, h.p);
                     d.nrend = n | ((bc.nch == 2 && (JMODE || lastPos < sampleDuration)) ? kSimpleBit : 0);
+                    mark_ring(d, g.data, n, lastPos);
                     P.descs[(size_t) t * P.nVoices + vIdx] = d;
                     bc.lastPos = lastPos;
                 }
@@ -277,9 +293,10 @@ __device__ __forceinline__ bool plan_voice_block(const RenderParams& P, int vIdx
             d.p0a = pl.p0a; d.Ra = pl.Ra; d.p0b = pl.p0b; d.Rb = pl.Rb; d.cb = pl.cb;
             d.e0a = ep.e0a; d.Ea = ep.Ea; d.e0b = ep.e0b; d.Eb = ep.Eb; d.ce = ep.ce; d.ct = ep.ct;
             d.nrend = cnt | (pl.irregular ? kSlotBit : 0);
-            if (cnt > 0 && !pl.irregular && pl.cb >= cnt && ep.ce >= cnt && ep.ct >= cnt && bc.nch == 2
-                && (JMODE || (int) __fma_rn((double) (cnt - 1), pl.Ra, pl.p0a) < sampleDuration))
-                d.nrend |= kSimpleBit;
+            if (cnt > 0 && !pl.irregular && pl.cb >= cnt && ep.ce >= cnt && ep.ct >= cnt && bc.nch == 2) {
+                const int lastPos = (int) __fma_rn((double) (cnt - 1), pl.Ra, pl.p0a);
+                if (JMODE || lastPos < sampleDuration) { d.nrend |= kSimpleBit; mark_ring(d, g.data, cnt, lastPos); }
+            }
             if (ended && cnt < pl.nPos) {                          // the ADSR ran out before the tile did: p is frame cnt's
                 if (pl.irregular) h.p = ps[cnt];
                 else h.p = cnt >= pl.cb ? __fma_rn((double) (cnt - pl.cb), pl.Rb, pl.p0b) : __fma_rn((double) cnt, pl.Ra, pl.p0a);
@@ -399,43 +416,37 @@ __device__ __forceinline__ VoiceGather load_vg(const VoiceGather* p) {
 }
 
 constexpr int kStageV = 16;          // voices per bus whose descriptors are staged through shared memory (else: straight from L2)
-constexpr int kTapStage = kNC * 32 * (8 + 8 + 4);   // one voice-tile in flight: taps a, taps b (float2 per lane-frame), alpha
-
-// Asynchronous gather (Ampere-style cp.async, SASS LDGSTS): every lane copies its own two 8-byte taps of each chunk
-// straight into the warp's shared-memory stage, so the loads of voice v + 1 are in flight - at no register cost - while the
-// arithmetic of voice v runs.  A lane only ever reads what it copied itself: cp.async.wait_group is all the
-// synchronisation there is.
-__device__ __forceinline__ void cp_async8(uint32_t saddr, const void* gptr) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(saddr), "l"(gptr) : "memory");
+// Asynchronous window staging (cp.async, SASS LDGSTS.128): the warp copies the source window of voice-tile v + 1 and
+// v + 2 - contiguous, 16 bytes per lane per instruction, so every 128-byte line crosses the L1 data pipe once - into
+// shared-memory slots while the arithmetic of voice-tile v runs on a slot that has already landed.  No registers are
+// held by loads in flight, and the taps themselves are then two LDS.64 per lane-frame.
+__device__ __forceinline__ void cp_async16(uint32_t saddr, const void* gptr) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(saddr), "l"(gptr) : "memory");
 }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
-// full simple voice-tile: positions -> alpha to the stage, taps by cp.async
-__device__ __forceinline__ void gather_issue_async(const TileDesc& d, const VoiceGather& g, int lane, double laneD, unsigned char* stage) {
-    const float2* __restrict__ src = reinterpret_cast<const float2*>(g.data);
-    const uint32_t sa = (uint32_t) __cvta_generic_to_shared(stage) + lane * 8;
-    float* al = reinterpret_cast<float*>(stage + kNC * 512) + lane;
+__device__ __forceinline__ void stage_window(const TileDesc& d, int lane, unsigned char* slot) {
+    const unsigned char* src = reinterpret_cast<const unsigned char*>((uintptr_t) __double_as_longlong(d.p0b));
+    const int bytes = __double2loint(d.Rb);
+    const uint32_t sa = (uint32_t) __cvta_generic_to_shared(slot);
 #pragma unroll
-    for (int ch = 0; ch < kNC; ++ch) {
-        const double p = __fma_rn(__dadd_rn(laneD, (double) (ch * 32)), d.Ra, d.p0a);
-        float alpha;
-        const int pos = split_pos(p, alpha);
-        cp_async8(sa + ch * 256, src + pos);
-        cp_async8(sa + kNC * 256 + ch * 256, src + pos + 1);
-        al[ch * 32] = alpha;
+    for (int k = 0; k < (kSlotBytes + 511) / 512; ++k) {
+        const int o = k * 512 + lane * 16;
+        if (o < bytes) cp_async16(sa + o, src + o);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
 template <bool JMODE, bool Q1>
-__device__ __forceinline__ float gather_finish_async(const TileDesc& d, const VoiceGather& g, const unsigned char* stage, int lane, float laneF,
-                                                     float nz, float2 (&acc)[kNC]) {
+__device__ __forceinline__ float gather_finish_ring(const TileDesc& d, const VoiceGather& g, const unsigned char* slot, double laneD, float laneF,
+                                                    float nz, float2 (&acc)[kNC]) {
     Taps t;
-    const float2* ta = reinterpret_cast<const float2*>(stage) + lane;
-    const float* al = reinterpret_cast<const float*>(stage + kNC * 512) + lane;
+    const float2* win = reinterpret_cast<const float2*>(slot) - __double2hiint(d.Rb);   // win[pos] = source frame pos
 #pragma unroll
     for (int ch = 0; ch < kNC; ++ch) {
-        t.a[ch] = ta[ch * 32]; t.b[ch] = ta[kNC * 32 + ch * 32]; t.alpha[ch] = al[ch * 32];
+        const double p = __fma_rn(__dadd_rn(laneD, (double) (ch * 32)), d.Ra, d.p0a);
+        const int pos = split_pos(p, t.alpha[ch]);
+        t.a[ch] = win[pos]; t.b[ch] = win[pos + 1];
         t.env[ch] = d.Ea == 0.0f ? d.e0a : __fmaf_rn(__fadd_rn(laneF, (float) (ch * 32)), d.Ea, d.e0a);
     }
     return gather_finish<JMODE, Q1, true>(g, t, kNC, nz, acc);
@@ -445,10 +456,10 @@ template <bool JMODE, bool Q1, bool Q2, bool STAGED>
 __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kernel(const RenderParams P) {
     constexpr int QS = Q2 ? 1 : 0;                            // frame f lands at output index f + QS   :218-221
     constexpr int W = ZL_GATHER_THREADS / 32;
-    // per warp: this tile's V descriptors, the block's V gather records (V <= kStageV) and two tap stages
+    // per warp: this tile's V descriptors, the block's V gather records (V <= kStageV) and the window staging slots
     __shared__ TileDesc sDesc[STAGED ? W : 1][kStageV];
     __shared__ VoiceGather sVg[STAGED ? W : 1][kStageV];
-    __shared__ __align__(16) unsigned char sTap[STAGED ? W : 1][2][kTapStage];
+    __shared__ __align__(16) unsigned char sWin[STAGED ? W : 1][kSlots][kSlotBytes];
     int lane = threadIdx.x & 31, warp = STAGED ? (threadIdx.x >> 5) : 0;
     asm volatile("" : "+r"(lane), "+r"(warp));            // opaque: keeps ptxas from re-deriving them from S2R inside the voice loop
     const int gbw = blockIdx.x * W + (threadIdx.x >> 5);      // global bus
@@ -503,27 +514,30 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
                     atomicMax(reinterpret_cast<int*>(&P.voices[v0 + vs].posGain), __float_as_int(__fmul_rn(__int_as_float(pk), 0.5f)));
             }
         };
-        int pendV = -1, pb = 0;                               // STAGED: the voice whose taps are in flight, and its stage
+        // STAGED: staged voice-tiles q0 (oldest, slot s0), q1, q2 in consecutive slots; two stay in flight behind the one computed
+        int q0 = -1, q1 = -1, q2 = -1, s0 = 0;
+        auto finish_oldest = [&]() {                          // slot order: the earlier voice is accumulated first
+            __syncwarp();                                     // the window was copied by all lanes
+            const VoiceGather gp = sVg[warp][q0];
+            take_peak(gather_finish_ring<JMODE, Q1>(sDesc[warp][q0], gp, sWin[warp][s0], laneD, laneF, nz, acc), q0, gp.nch);
+            __syncwarp();                                     // every lane is done with the slot before it is staged again
+            q0 = q1; q1 = q2; q2 = -1; s0 = s0 + 1 == kSlots ? 0 : s0 + 1;
+        };
         for (int vs = 0; vs < V; ++vs) {
             const TileDesc d = STAGED ? sDesc[warp][vs] : load_desc(dp + vs);
             const int nr = d.nrend & kCountMask;              // warp-uniform
             if (nr == 0) continue;
             const VoiceGather g = STAGED ? sVg[warp][vs] : load_vg(P.vgs + v0 + vs);
-            if (STAGED && (d.nrend & kSimpleBit) && nr == kT) {
-                gather_issue_async(d, g, lane, laneD, sTap[warp][pb ^ 1]);
-                if (pendV >= 0) {                             // slot order: the earlier voice is accumulated first
-                    cp_async_wait<1>();
-                    const VoiceGather gp = sVg[warp][pendV];
-                    take_peak(gather_finish_async<JMODE, Q1>(sDesc[warp][pendV], gp, sTap[warp][pb], lane, laneF, nz, acc), pendV, gp.nch);
-                }
-                pendV = vs; pb ^= 1;
+            if (STAGED && (d.nrend & kRingBit)) {
+                int slot = s0 + (q0 >= 0 ? 1 : 0) + (q1 >= 0 ? 1 : 0); if (slot >= kSlots) slot -= kSlots;
+                stage_window(d, lane, sWin[warp][slot]);
+                if (q0 < 0) q0 = vs; else if (q1 < 0) q1 = vs; else q2 = vs;
+                if (q2 >= 0) { cp_async_wait<2>(); finish_oldest(); }          // three staged: the oldest has landed; two stay in flight
                 continue;
             }
-            if (STAGED && pendV >= 0) {
-                cp_async_wait<0>();
-                const VoiceGather gp = sVg[warp][pendV];
-                take_peak(gather_finish_async<JMODE, Q1>(sDesc[warp][pendV], gp, sTap[warp][pb], lane, laneF, nz, acc), pendV, gp.nch);
-                pendV = -1;
+            if (STAGED) {                                     // a voice-tile that cannot be staged: drain, then gather it directly
+                if (q0 >= 0) { if (q1 >= 0) cp_async_wait<1>(); else cp_async_wait<0>(); finish_oldest(); }
+                if (q0 >= 0) { cp_async_wait<0>(); finish_oldest(); }
             }
             Taps tp;
             float vmax;
@@ -540,10 +554,9 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
             }
             take_peak(vmax, vs, g.nch);
         }
-        if (STAGED && pendV >= 0) {
-            cp_async_wait<0>();
-            const VoiceGather gp = sVg[warp][pendV];
-            take_peak(gather_finish_async<JMODE, Q1>(sDesc[warp][pendV], gp, sTap[warp][pb], lane, laneF, nz, acc), pendV, gp.nch);
+        if (STAGED) {
+            if (q0 >= 0) { if (q1 >= 0) cp_async_wait<1>(); else cp_async_wait<0>(); finish_oldest(); }
+            if (q0 >= 0) { cp_async_wait<0>(); finish_oldest(); }
         }
         // raw SamplerChannel ports, then JackPassthrough and the meters on the register accumulators
 #pragma unroll
