@@ -254,6 +254,16 @@ def run_cuda(args, rank, world, local_rank):
     for i in range(args.warmup):
         step(i)
     barrier()
+    # gather_kernel alone (no planner beside it): one extra untimed step on one stream, per-launch events
+    e._chk(e.lib.ctx_set_overlap(e.ctx, 0), "ctx_set_overlap")
+    e._chk(e.lib.kernel_timing(e.ctx, 2), "kernel_timing")
+    step(2 * total_steps)
+    barrier()
+    kms0, kn0 = C.c_double(), C.c_uint64()
+    e._chk(e.lib.kernel_time(e.ctx, C.byref(kms0), C.byref(kn0)), "kernel_time")
+    e._chk(e.lib.kernel_timing(e.ctx, 0), "kernel_timing")
+    e._chk(e.lib.ctx_set_overlap(e.ctx, 1), "ctx_set_overlap")
+    gather_alone_ms = kms0.value / max(1, kn0.value)
     sampler = ClockSampler(local_rank) if rank == 0 else None
     launches0 = e.launch_count()
     vf0, src0 = e.total_counters()
@@ -309,7 +319,7 @@ def run_cuda(args, rank, world, local_rank):
     del ref
     for hp in hostp:
         e.lib.host_free(hp)
-    return dict(e=e, kernel_ms=kernel_ms, gather_ms_per_step=gather_ms_per_step, elapsed_ms=elapsed_ms, step_ms=step_ms, timed_vf=timed_vf, timed_src=timed_src, launches=kernel_launches,
+    return dict(e=e, kernel_ms=kernel_ms, gather_ms_per_step=gather_ms_per_step, gather_alone_ms=gather_alone_ms, elapsed_ms=elapsed_ms, step_ms=step_ms, timed_vf=timed_vf, timed_src=timed_src, launches=kernel_launches,
                 clocks=clocks, e2e_s=e2e_s, e2e_vf=e2e_vf, h2d=h2d, d2h=d2h, out_bytes=out_bytes, state_bytes=state_bytes,
                 dist=dist, dev=dev, wl=wl, keep=pcm)
 
@@ -451,6 +461,8 @@ def main():
                              "bytes_per_voice_frame": step_alg_bytes / (r["timed_vf"] / args.steps),
                              "kernel": "zl::gather_kernel", "kernel_ms": mean_ms, "launches_per_step": args.blocks,
                              "gather_ms_per_step": r["gather_ms_per_step"],
+                             "note": "kernel_ms is measured live in the timed region, where plan_kernel/walk_kernel of the next period run beside gather_kernel on a second stream and share its SMs; kernel_alone_ms is the same launch with the overlap switched off (one extra untimed step)",
+                             "kernel_alone_ms": r["gather_alone_ms"], "frac_alone": alg_bytes / (r["gather_alone_ms"] * 1e-3) / 1e9 / peak,
                              "whole_step_frac": step_alg_bytes / (el_ms / args.steps * 1e-3) / 1e9 / peak,
                              "whole_step_note": "all algorithmic bytes of a step (source + voice state + raw planes + master + peaks) / ms_per_step: plan, walk, gather and master mix together"},
                 "voice_frames_per_step": vf / args.steps / world}

@@ -176,6 +176,9 @@ ZL_EXPORT const char* ZL_FN(last_error)(zl_ctx* ctx);
 ZL_EXPORT int ZL_FN(config_default)(zl_config* cfg);
 /* Use an externally created cudaStream_t (e.g. torch's current stream). NULL = context's own. */
 ZL_EXPORT int ZL_FN(ctx_set_stream)(zl_ctx* ctx, void* cuda_stream);
+/* Two-stream render (default on): the planner of period b + 1 runs beside the gather of period b.  0 = everything on
+ * the context stream in order (used by bench.py to time gather_kernel alone). */
+ZL_EXPORT int ZL_FN(ctx_set_overlap)(zl_ctx* ctx, int32_t enable);
 ZL_EXPORT int ZL_FN(sync)(zl_ctx* ctx);
 
 /* ---- clips: ClipAudioSource + SamplerSynthSound ------------------------------------- */

@@ -134,6 +134,7 @@ struct zl_ctx {
     bool copyPending[2] = {false, false};
     int32_t* d_peaks = nullptr; double* d_sumsq = nullptr;
     void* d_scratch = nullptr; size_t scratchCap = 0;   // plan -> gather hand-over: two blocks (double-buffered by block parity)
+    bool overlapEnabled = true;
     cudaStream_t planStream = nullptr;                  // high priority: plan/walk of period b + 1 overlap the gather of period b
     cudaEvent_t evStart = nullptr, evPlan[2] = {nullptr, nullptr}, evGather[2] = {nullptr, nullptr};
     int32_t* d_walkCount = nullptr; int walkCountCap = 0;
@@ -330,6 +331,12 @@ int zl_ctx_destroy(zl_ctx* ctx) {
 }
 
 const char* zl_last_error(zl_ctx* ctx) { return ctx ? ctx->err.c_str() : "null ctx"; }
+
+int zl_ctx_set_overlap(zl_ctx* ctx, int32_t enable) {
+    if (!ctx) return ZL_ERR_INVALID;
+    ctx->overlapEnabled = enable != 0;
+    return ZL_OK;
+}
 
 int zl_ctx_set_stream(zl_ctx* ctx, void* s) {
     if (!ctx) return ZL_ERR_INVALID;
@@ -626,11 +633,13 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     P.walkCount = ctx->d_walkCount;
     // Two streams: plan/walk of period b + 1 (high priority) run beside the gather of period b.  The positions-model gain
     // is then written by the gather alone (V <= 32); with more voices per bus it needs the planner's reset first -> one stream.
-    const bool overlap = ctx->cfg.voices_per_bus <= 32 && nblocks > 1;
+    const bool overlap = ctx->overlapEnabled && ctx->cfg.voices_per_bus <= 32 && nblocks > 1;
     if (overlap && !ctx->planStream) {
         int lo = 0, hi = 0;
         CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-        CK(cudaStreamCreateWithPriority(&ctx->planStream, cudaStreamNonBlocking, hi));
+        const char* pe = getenv("ZL_B200_PLAN_PRIORITY");     // experiment knob: "low" / "same" / default high
+        const int prio = pe && !strcmp(pe, "low") ? lo : (pe && !strcmp(pe, "same") ? 0 : hi);
+        CK(cudaStreamCreateWithPriority(&ctx->planStream, cudaStreamNonBlocking, prio));
         CK(cudaEventCreateWithFlags(&ctx->evStart, cudaEventDisableTiming));
         for (int k = 0; k < 2; ++k) {
             CK(cudaEventCreateWithFlags(&ctx->evPlan[k], cudaEventDisableTiming));

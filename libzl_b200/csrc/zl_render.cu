@@ -206,8 +206,8 @@ __device__ __forceinline__ void plan_restore(const PlanUndo& u, VoiceHot& h, Voi
 
 // ---------------------------------------------------------------------------------------------------------------------
 // One voice, one block: prelude, tiles, epilogue.  Returns false (and changes nothing) when DEFER is set and the voice
-// will need a frame-by-frame envelope walk in this block; such voices are queued and planned by walk_kernel, packed
-// 32 to a warp, instead of holding a whole warp of plan_kernel hostage with one busy lane.
+// is not on the event-free fast path; such voices are queued and planned by walk_kernel, packed 32 to a warp, instead
+// of holding a whole warp of plan_kernel hostage with a few busy lanes.
 template <bool JMODE, bool Q3, bool DEFER>
 __device__ __forceinline__ bool plan_voice_block(const RenderParams& P, int vIdx, int gb, unsigned long long& nVoiceFrames,
                                                  unsigned long long& nSrcFloats) {
@@ -225,14 +225,6 @@ __device__ __forceinline__ bool plan_voice_block(const RenderParams& P, int vIdx
     bool active = false;
     if (P.buses[gb].enabled && (h.flags & VF_PLAYING))                              // :136-140
         active = voice_block_begin<JMODE>(h, P, ck, nframes, bc, g);
-    if (DEFER && active) {
-        // attack from 0 is stepped frame by frame (zl_voice.cuh); so is quirk Q3's release window, which a one-shot voice
-        // enters once p reaches relStart (:253) - a conservative test: a deferred voice is planned all the same
-        bool slow = h.adsrState == kAttack && h.env == 0.0f;
-        if (!JMODE && Q3 && !h.looping)
-            slow = slow || __fma_rn((double) nframes * 1.0000001, h.ratio, h.p) >= bc.relStart;
-        if (slow) return false;
-    }
     const bool walked = active;
     const int sampleDuration = g.sampleDuration;
     int nrendBlock = 0;
@@ -268,7 +260,19 @@ __device__ __forceinline__ bool plan_voice_block(const RenderParams& P, int vIdx
         }
     }
 
-    for (int t = 0; t < (fast ? 0 : P.tilesPerBlock); ++t) {
+    // plan_kernel (DEFER) takes only the event-free voices: everything else - envelope segments in attack/decay/release,
+    // loop wraps, binade crossings, the frame-by-frame walks of an attack from 0 and of quirk Q3's release window - would
+    // drag the other 31 lanes of its warp through the generic planner, so it is queued for walk_kernel, which runs the
+    // same code with those voices packed 32 to a warp.  Nothing has been written yet.
+    if (DEFER && active && !fast) return false;
+
+    if (DEFER && !fast) {                                     // not playing: empty tiles (the gather skips them)
+        TileDesc d;
+        d.p0a = 0.0; d.Ra = 0.0; d.p0b = 0.0; d.Rb = 0.0; d.e0a = 0.0f; d.Ea = 0.0f; d.e0b = 0.0f; d.Eb = 0.0f;
+        d.cb = 0; d.ce = 0; d.ct = INT_MAX; d.nrend = 0;
+        for (int t = 0; t < P.tilesPerBlock; ++t) P.descs[(size_t) t * P.nVoices + vIdx] = d;
+    }
+    for (int t = 0; t < ((DEFER || fast) ? 0 : P.tilesPerBlock); ++t) {
         const int t0 = t * kT;
         const int n = min(kT, nframes - t0);
         const size_t vt = (size_t) t * P.nVoices + vIdx;    // voice-tile
@@ -329,7 +333,7 @@ __device__ __forceinline__ bool plan_voice_block(const RenderParams& P, int vIdx
 // ---------------------------------------------------------------------------------------------------------------------
 // plan_kernel: thread = voice, CTA = whole buses (planBusesPerCta x V threads, rounded up to a warp).
 #ifndef ZL_PLAN_MINB
-#define ZL_PLAN_MINB 4
+#define ZL_PLAN_MINB 6
 #endif
 template <bool JMODE, bool Q3, int MAXT>
 __global__ void __launch_bounds__(MAXT, MAXT == 128 ? ZL_PLAN_MINB : 1) plan_kernel(const RenderParams P) {
