@@ -626,10 +626,10 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     if (nblocks > ctx->walkCountCap) {
         if (ctx->d_walkCount) cudaFree(ctx->d_walkCount);
         ctx->d_walkCount = nullptr; ctx->walkCountCap = 0;
-        CK(cudaMalloc((void**) &ctx->d_walkCount, sizeof(int32_t) * (size_t) nblocks));
+        CK(cudaMalloc((void**) &ctx->d_walkCount, sizeof(int32_t) * 2 * (size_t) nblocks));
         ctx->walkCountCap = nblocks;
     }
-    CK(cudaMemsetAsync(ctx->d_walkCount, 0, sizeof(int32_t) * (size_t) nblocks, st));
+    CK(cudaMemsetAsync(ctx->d_walkCount, 0, sizeof(int32_t) * 2 * (size_t) nblocks, st));
     P.walkCount = ctx->d_walkCount;
     // Two streams: plan/walk of period b + 1 (high priority) run beside the gather of period b.  The positions-model gain
     // is then written by the gather alone (V <= 32); with more voices per bus it needs the planner's reset first -> one stream.

@@ -104,7 +104,7 @@ struct RenderParams {
     float* te;               // [tilesPerBlock][nVoices][kT] envelope rows (only frames >= TileDesc.ct are used)
     double* ps;              // [tilesPerBlock][nVoices][kT] position rows (only kSlotBit voice-tiles)
     int32_t* walkQueue;      // [nVoices] voices deferred by plan_kernel to walk_kernel in this block
-    int32_t* walkCount;      // [nblocks] queue lengths (zeroed per launch)
+    int32_t* walkCount;      // [nblocks][2] queue lengths: serial walkers (front of the queue), others (back); zeroed per launch
     int32_t nVoices, tilesPerBlock, blk, planBusesPerCta;
 };
 

@@ -205,11 +205,11 @@ __device__ __forceinline__ void plan_restore(const PlanUndo& u, VoiceHot& h, Voi
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// One voice, one block: prelude, tiles, epilogue.  Returns false (and changes nothing) when DEFER is set and the voice
+// One voice, one block: prelude, tiles, epilogue.  Returns non-zero (and changes nothing) when DEFER is set and the voice
 // is not on the event-free fast path; such voices are queued and planned by walk_kernel, packed 32 to a warp, instead
 // of holding a whole warp of plan_kernel hostage with a few busy lanes.
 template <bool JMODE, bool Q3, bool DEFER>
-__device__ __forceinline__ bool plan_voice_block(const RenderParams& P, int vIdx, int gb, unsigned long long& nVoiceFrames,
+__device__ __forceinline__ int plan_voice_block(const RenderParams& P, int vIdx, int gb, unsigned long long& nVoiceFrames,
                                                  unsigned long long& nSrcFloats) {
     const int blk = P.blk, nframes = P.nframes;
     VoiceDev* rec = P.voices + vIdx;
@@ -264,7 +264,14 @@ __device__ __forceinline__ bool plan_voice_block(const RenderParams& P, int vIdx
     // loop wraps, binade crossings, the frame-by-frame walks of an attack from 0 and of quirk Q3's release window - would
     // drag the other 31 lanes of its warp through the generic planner, so it is queued for walk_kernel, which runs the
     // same code with those voices packed 32 to a warp.  Nothing has been written yet.
-    if (DEFER && active && !fast) return false;
+    if (DEFER && active && !fast) {
+        // kind 1: will step an envelope frame by frame for (most of) the period - quirk Q3's release window of a one-shot
+        // (conservative test on p reaching relStart, :253) or an attack from 0; kind 2: everything else (O(1) per tile).
+        // The two kinds are queued apart so a warp of walk_kernel is not a mix of 10 us and 100 us voices.
+        bool serial = h.adsrState == kAttack && h.env == 0.0f;
+        if (!JMODE && Q3 && !h.looping) serial = serial || __fma_rn((double) nframes * 1.0000001, h.ratio, h.p) >= bc.relStart;
+        return serial ? 1 : 2;
+    }
 
     if (DEFER && !fast) {                                     // not playing: empty tiles (the gather skips them)
         TileDesc d;
@@ -327,7 +334,7 @@ __device__ __forceinline__ bool plan_voice_block(const RenderParams& P, int vIdx
     }
     P.vgs[vIdx] = g;
     hot_store(h, *rec);
-    return true;
+    return 0;
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -357,15 +364,21 @@ __global__ void __launch_bounds__(MAXT, MAXT == 128 ? ZL_PLAN_MINB : 1) plan_ker
         __syncthreads();
     }
     unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
-    bool deferred = false;
-    if (hasVoice) deferred = !plan_voice_block<JMODE, Q3, true>(P, vIdx, gb, nVoiceFrames, nSrcFloats);
-    // queue the deferred voices of this warp with one atomic
-    const unsigned dm = __ballot_sync(FULL, deferred);
-    if (dm) {
-        int base = 0;
-        if ((tid & 31) == 0) base = atomicAdd(P.walkCount + blk, __popc(dm));
-        base = __shfl_sync(FULL, base, 0);
-        if (deferred) P.walkQueue[base + __popc(dm & ((1u << (tid & 31)) - 1u))] = vIdx;
+    int kind = 0;
+    if (hasVoice) kind = plan_voice_block<JMODE, Q3, true>(P, vIdx, gb, nVoiceFrames, nSrcFloats);
+    // queue the deferred voices of this warp: serial walkers from the front of the queue, the others from its back; one
+    // atomic per warp and kind
+    const unsigned lt = (1u << (tid & 31)) - 1u;
+    const unsigned mA = __ballot_sync(FULL, kind == 1), mB = __ballot_sync(FULL, kind == 2);
+    if (mA | mB) {
+        int baseA = 0, baseB = 0;
+        if ((tid & 31) == 0) {
+            if (mA) baseA = atomicAdd(P.walkCount + 2 * blk, __popc(mA));
+            if (mB) baseB = atomicAdd(P.walkCount + 2 * blk + 1, __popc(mB));
+        }
+        baseA = __shfl_sync(FULL, baseA, 0); baseB = __shfl_sync(FULL, baseB, 0);
+        if (kind == 1) P.walkQueue[baseA + __popc(mA & lt)] = vIdx;
+        if (kind == 2) P.walkQueue[P.nVoices - 1 - (baseB + __popc(mB & lt))] = vIdx;
     }
     for (int o = 16; o > 0; o >>= 1) {
         nVoiceFrames += __shfl_down_sync(FULL, nVoiceFrames, o);
@@ -378,18 +391,24 @@ __global__ void __launch_bounds__(MAXT, MAXT == 128 ? ZL_PLAN_MINB : 1) plan_ker
 }
 
 
-// walk_kernel: thread = queued voice (the ones plan_kernel deferred), grid-stride over the queue.
+// walk_kernel: thread = queued voice (the ones plan_kernel deferred); CTA = one warp, grid-stride over the warps of
+// the two queues (serial walkers first, so the long ones start first).
 template <bool JMODE, bool Q3>
-__global__ void __launch_bounds__(128) walk_kernel(const RenderParams P) {
+__global__ void __launch_bounds__(32) walk_kernel(const RenderParams P) {
     const unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x;
-    const int count = P.walkCount[P.blk];
+    const int cA = P.walkCount[2 * P.blk], cB = P.walkCount[2 * P.blk + 1];
+    const int wA = (cA + 31) >> 5, wB = (cB + 31) >> 5;
     unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
-    for (int i = blockIdx.x * blockDim.x + tid; i < count; i += gridDim.x * blockDim.x) {
-        const int vIdx = P.walkQueue[i];
-        unsigned long long a = 0, b = 0;
-        plan_voice_block<JMODE, Q3, false>(P, vIdx, vIdx / P.V, a, b);
-        nVoiceFrames += a; nSrcFloats += b;
+    for (int w = blockIdx.x; w < wA + wB; w += gridDim.x) {
+        int vIdx = -1;
+        if (w < wA) { const int i = w * 32 + tid; if (i < cA) vIdx = P.walkQueue[i]; }
+        else { const int j = (w - wA) * 32 + tid; if (j < cB) vIdx = P.walkQueue[P.nVoices - 1 - j]; }
+        if (vIdx >= 0) {
+            unsigned long long a = 0, b = 0;
+            plan_voice_block<JMODE, Q3, false>(P, vIdx, vIdx / P.V, a, b);
+            nVoiceFrames += a; nSrcFloats += b;
+        }
     }
     for (int o = 16; o > 0; o >>= 1) {
         nVoiceFrames += __shfl_down_sync(FULL, nVoiceFrames, o);
@@ -693,10 +712,10 @@ cudaError_t launch_plan(RenderParams& P, cudaStream_t stream) {
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    const int wGrid = min((P.nVoices + 127) / 128, 148 * 4);
-    if (P.mode == ZL_MODE_J) walk_kernel<true, false><<<wGrid, 128, 0, stream>>>(P);
-    else if (q3) walk_kernel<false, true><<<wGrid, 128, 0, stream>>>(P);
-    else walk_kernel<false, false><<<wGrid, 128, 0, stream>>>(P);
+    const int wGrid = min((P.nVoices + 31) / 32 + 1, 148 * 16);
+    if (P.mode == ZL_MODE_J) walk_kernel<true, false><<<wGrid, 32, 0, stream>>>(P);
+    else if (q3) walk_kernel<false, true><<<wGrid, 32, 0, stream>>>(P);
+    else walk_kernel<false, false><<<wGrid, 32, 0, stream>>>(P);
     return cudaGetLastError();
 }
 
