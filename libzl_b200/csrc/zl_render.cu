@@ -41,7 +41,7 @@ constexpr int kSlotBit = 1 << 30;     // positions come from the voice-tile's po
 constexpr int kSimpleBit = 1 << 29;   // one position segment, one envelope segment, stereo, every tap inside the sample
 constexpr int kRingBit = 1 << 28;     // simple, full tile, and the source window fits one staging slot: p0b = window address, Rb = (first frame, bytes)
 constexpr int kCountMask = (1 << 20) - 1;
-constexpr int kSlotBytes = 2304;      // one staged source window: 128 frames x ratio 2.2 x 8 B + halo; multiple of 16
+constexpr int kSlotBytes = 2560;      // one staged source window: 128 frames x ratio 2.4 x 8 B + halo, copied in 512-byte rows
 constexpr int kSlots = 3;             // staging slots per warp: two windows in flight behind the one being gathered
 constexpr int kWantPeak = 1 << 8;     // VoiceGather.nch flag: the positions model takes this block's peak  :265-267
 
@@ -181,11 +181,12 @@ __device__ __forceinline__ int peak_int(float x) {   // lib/AudioLevels.cpp:365-
 
 // Simple full tiles whose source window [first tap, last tap + 1] fits a staging slot are gathered through shared memory:
 // the planner leaves the window's 16-byte aligned address and size in the (unused) second position segment.
-__device__ __forceinline__ void mark_ring(TileDesc& d, const float* data, int cnt, int lastPos) {
+__device__ __forceinline__ void mark_ring(TileDesc& d, const float* data, int sampleDur, int cnt, int lastPos) {
     if (cnt != kT || !(d.nrend & kSimpleBit)) return;
     const int base = (int) d.p0a & ~1;                                   // 16-byte aligned first frame (stereo: 8 B per frame)
-    const int bytes = ((lastPos + 2 - base) * 8 + 15) & ~15;             // frames base .. lastPos + 1
-    if (bytes > kSlotBytes || (reinterpret_cast<uintptr_t>(data) & 15)) return;
+    const int bytes = ((lastPos + 2 - base) * 8 + 511) & ~511;           // frames base .. lastPos + 1, in whole 512-byte rows
+    // the rows must fit a slot and stay inside the clip buffer (length + 8 frames, sampleDur = length - 1)
+    if (bytes > kSlotBytes || base * 8 + bytes > (sampleDur + 9) * 8 || (reinterpret_cast<uintptr_t>(data) & 15)) return;
     d.nrend |= kRingBit;
     d.p0b = __longlong_as_double((long long) (reinterpret_cast<uintptr_t>(data) + (size_t) base * 8));
     d.Rb = __hiloint2double(base, bytes);
@@ -250,7 +251,7 @@ __device__ __forceinline__ int plan_voice_block(const RenderParams& P, int vIdx,
                     d.cb = n; d.ce = n; d.ct = INT_MAX;
                     const int lastPos = (int) __fma_rn((double) (t0 + n - 1), R, h.p);
                     d.nrend = n | ((bc.nch == 2 && (JMODE || lastPos < sampleDuration)) ? kSimpleBit : 0);
-                    mark_ring(d, g.data, n, lastPos);
+                    mark_ring(d, g.data, sampleDuration, n, lastPos);
                     P.descs[(size_t) t * P.nVoices + vIdx] = d;
                     bc.lastPos = lastPos;
                 }
@@ -306,7 +307,7 @@ __device__ __forceinline__ int plan_voice_block(const RenderParams& P, int vIdx,
             d.nrend = cnt | (pl.irregular ? kSlotBit : 0);
             if (cnt > 0 && !pl.irregular && pl.cb >= cnt && ep.ce >= cnt && ep.ct >= cnt && bc.nch == 2) {
                 const int lastPos = (int) __fma_rn((double) (cnt - 1), pl.Ra, pl.p0a);
-                if (JMODE || lastPos < sampleDuration) { d.nrend |= kSimpleBit; mark_ring(d, g.data, cnt, lastPos); }
+                if (JMODE || lastPos < sampleDuration) { d.nrend |= kSimpleBit; mark_ring(d, g.data, sampleDuration, cnt, lastPos); }
             }
             if (ended && cnt < pl.nPos) {                          // the ADSR ran out before the tile did: p is frame cnt's
                 if (pl.irregular) h.p = ps[cnt];
@@ -449,14 +450,12 @@ __device__ __forceinline__ void cp_async16(uint32_t saddr, const void* gptr) {
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
 __device__ __forceinline__ void stage_window(const TileDesc& d, int lane, unsigned char* slot) {
-    const unsigned char* src = reinterpret_cast<const unsigned char*>((uintptr_t) __double_as_longlong(d.p0b));
-    const int bytes = __double2loint(d.Rb);
-    const uint32_t sa = (uint32_t) __cvta_generic_to_shared(slot);
+    const unsigned char* src = reinterpret_cast<const unsigned char*>((uintptr_t) __double_as_longlong(d.p0b)) + lane * 16;
+    const int rows = __double2loint(d.Rb) >> 9;                          // whole 512-byte rows (warp-uniform)
+    const uint32_t sa = (uint32_t) __cvta_generic_to_shared(slot) + lane * 16;
 #pragma unroll
-    for (int k = 0; k < (kSlotBytes + 511) / 512; ++k) {
-        const int o = k * 512 + lane * 16;
-        if (o < bytes) cp_async16(sa + o, src + o);
-    }
+    for (int k = 0; k < kSlotBytes / 512; ++k)
+        if (k < rows) cp_async16(sa + k * 512, src + k * 512);
     asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
@@ -470,7 +469,7 @@ __device__ __forceinline__ float gather_finish_ring(const TileDesc& d, const Voi
         const double p = __fma_rn(__dadd_rn(laneD, (double) (ch * 32)), d.Ra, d.p0a);
         const int pos = split_pos(p, t.alpha[ch]);
         t.a[ch] = win[pos]; t.b[ch] = win[pos + 1];
-        t.env[ch] = d.Ea == 0.0f ? d.e0a : __fmaf_rn(__fadd_rn(laneF, (float) (ch * 32)), d.Ea, d.e0a);
+        t.env[ch] = __fmaf_rn(__fadd_rn(laneF, (float) (ch * 32)), d.Ea, d.e0a);     // Ea == 0 (sustain): exactly e0a
     }
     return gather_finish<JMODE, Q1, true>(g, t, kNC, nz, acc);
 }
@@ -532,35 +531,40 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
         auto take_peak = [&](float vmax, int vs, int flags) {
             if (!JMODE && (flags & kWantPeak)) {
                 const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));   // vmax >= +0: int order == float order
-                if (V <= 32) { if (lane == vs) vpk = max(vpk, pk); }
+                if (STAGED || V <= 32) { if (lane == vs) vpk = max(vpk, pk); }
                 else if (lane == 0 && pk > 0)
                     atomicMax(reinterpret_cast<int*>(&P.voices[v0 + vs].posGain), __float_as_int(__fmul_rn(__int_as_float(pk), 0.5f)));
             }
         };
-        // STAGED: staged voice-tiles q0 (oldest, slot s0), q1, q2 in consecutive slots; two stay in flight behind the one computed
-        int q0 = -1, q1 = -1, q2 = -1, s0 = 0;
-        auto finish_oldest = [&]() {                          // slot order: the earlier voice is accumulated first
-            __syncwarp();                                     // the window was copied by all lanes
-            const VoiceGather gp = sVg[warp][q0];
-            take_peak(gather_finish_ring<JMODE, Q1>(sDesc[warp][q0], gp, sWin[warp][s0], laneD, laneF, nz, acc), q0, gp.nch);
-            __syncwarp();                                     // every lane is done with the slot before it is staged again
-            q0 = q1; q1 = q2; q2 = -1; s0 = s0 + 1 == kSlots ? 0 : s0 + 1;
-        };
+        // STAGED: the tile's staged voice-tiles, in slot order, form a queue through the kSlots window slots: two windows
+        // are in flight behind the one being computed.  toStage = voices not yet staged; si / sd = next slot to stage / to read.
+        unsigned toStage = 0;
+        int si = 0, sd = 0, inFlight = 0;
+        if (STAGED) {
+            toStage = __ballot_sync(FULL, lane < V && (sDesc[warp][lane < V ? lane : 0].nrend & kRingBit) != 0);
+#pragma unroll
+            for (int k = 0; k < kSlots - 1; ++k)
+                if (toStage) {
+                    stage_window(sDesc[warp][__ffs(toStage) - 1], lane, sWin[warp][si]);
+                    toStage &= toStage - 1; si = si + 1 == kSlots ? 0 : si + 1; ++inFlight;
+                }
+        }
         for (int vs = 0; vs < V; ++vs) {
             const TileDesc d = STAGED ? sDesc[warp][vs] : load_desc(dp + vs);
             const int nr = d.nrend & kCountMask;              // warp-uniform
             if (nr == 0) continue;
             const VoiceGather g = STAGED ? sVg[warp][vs] : load_vg(P.vgs + v0 + vs);
             if (STAGED && (d.nrend & kRingBit)) {
-                int slot = s0 + (q0 >= 0 ? 1 : 0) + (q1 >= 0 ? 1 : 0); if (slot >= kSlots) slot -= kSlots;
-                stage_window(d, lane, sWin[warp][slot]);
-                if (q0 < 0) q0 = vs; else if (q1 < 0) q1 = vs; else q2 = vs;
-                if (q2 >= 0) { cp_async_wait<2>(); finish_oldest(); }          // three staged: the oldest has landed; two stay in flight
+                if (toStage) {                                // keep the queue full: the slot read last time is free
+                    stage_window(sDesc[warp][__ffs(toStage) - 1], lane, sWin[warp][si]);
+                    toStage &= toStage - 1; si = si + 1 == kSlots ? 0 : si + 1; ++inFlight;
+                }
+                if (inFlight >= 3) cp_async_wait<2>(); else if (inFlight == 2) cp_async_wait<1>(); else cp_async_wait<0>();
+                __syncwarp();                                 // the window was copied by all lanes
+                take_peak(gather_finish_ring<JMODE, Q1>(d, g, sWin[warp][sd], laneD, laneF, nz, acc), vs, g.nch);
+                __syncwarp();                                 // every lane is done with the slot before it is staged again
+                sd = sd + 1 == kSlots ? 0 : sd + 1; --inFlight;
                 continue;
-            }
-            if (STAGED) {                                     // a voice-tile that cannot be staged: drain, then gather it directly
-                if (q0 >= 0) { if (q1 >= 0) cp_async_wait<1>(); else cp_async_wait<0>(); finish_oldest(); }
-                if (q0 >= 0) { cp_async_wait<0>(); finish_oldest(); }
             }
             Taps tp;
             float vmax;
@@ -576,10 +580,6 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
                 vmax = gather_finish<JMODE, Q1, false>(g, tp, nchunks, nz, acc);
             }
             take_peak(vmax, vs, g.nch);
-        }
-        if (STAGED) {
-            if (q0 >= 0) { if (q1 >= 0) cp_async_wait<1>(); else cp_async_wait<0>(); finish_oldest(); }
-            if (q0 >= 0) { cp_async_wait<0>(); finish_oldest(); }
         }
         // raw SamplerChannel ports, then JackPassthrough and the meters on the register accumulators
 #pragma unroll
@@ -609,7 +609,7 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
             }
         }
     }
-    if (!JMODE && V <= 32 && lane < V) {                           // the positions-model gain of the voices that take it this period
+    if (!JMODE && (STAGED || V <= 32) && lane < V) {               // the positions-model gain of the voices that take it this period
         const int flags = STAGED ? sVg[warp][lane].nch : __ldg(&P.vgs[v0 + lane].nch);
         if (flags & kWantPeak) P.voices[v0 + lane].posGain = __fmul_rn(__int_as_float(vpk), 0.5f);
     }
