@@ -639,29 +639,52 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
 // JackPassthroughPrivate::process applied to the raw SamplerChannel port (lib/JackPassthrough.cpp:94-101) — recomputed
 // here from the raw plane with the same arithmetic the gather used, so the dry plane need not exist.
 // One thread per (session, frame); both channels; the raw rows are read fully coalesced.
+template <int VEC>
 __global__ void __launch_bounds__(256)
 master_mix_kernel(const float* __restrict__ raw, const BusDev* __restrict__ buses, float* __restrict__ master,
                   int nSessions, int B, int64_t stride, int64_t n) {
-    const int64_t j = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t j = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) * VEC;   // VEC consecutive frames per thread (float4 rows)
     const int s = blockIdx.y;
     if (j >= n) return;
-    float mL = 0.0f, mR = 0.0f;
+    float mL[VEC], mR[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) { mL[k] = 0.0f; mR[k] = 0.0f; }
     for (int b = 0; b < B; ++b) {
         const int gb = s * B + b;
         const zl_passthrough_params pt = buses[gb].pt;
-        const float inL = raw[((int64_t) gb * 2) * stride + j], inR = raw[((int64_t) gb * 2 + 1) * stride + j];
-        float dL, dR;
-        passthrough_pair(pt, pt.dry_amount, inL, inR, dL, dR);
-        if (b == 0) { mL = dL; mR = dR; } else { mL = __fadd_rn(mL, dL); mR = __fadd_rn(mR, dR); }
+        float inL[VEC], inR[VEC];
+        if (VEC == 4) {
+            const float4 l = __ldcs(reinterpret_cast<const float4*>(raw + ((int64_t) gb * 2) * stride + j));       // streamed once
+            const float4 r = __ldcs(reinterpret_cast<const float4*>(raw + ((int64_t) gb * 2 + 1) * stride + j));
+            inL[0] = l.x; inL[1 % VEC] = l.y; inL[2 % VEC] = l.z; inL[3 % VEC] = l.w;
+            inR[0] = r.x; inR[1 % VEC] = r.y; inR[2 % VEC] = r.z; inR[3 % VEC] = r.w;
+        } else {
+            inL[0] = raw[((int64_t) gb * 2) * stride + j]; inR[0] = raw[((int64_t) gb * 2 + 1) * stride + j];
+        }
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+            float dL, dR;
+            passthrough_pair(pt, pt.dry_amount, inL[k], inR[k], dL, dR);
+            if (b == 0) { mL[k] = dL; mR[k] = dR; } else { mL[k] = __fadd_rn(mL[k], dL); mR[k] = __fadd_rn(mR[k], dR); }
+        }
     }
-    master[((int64_t) s * 2) * stride + j] = mL;
-    master[((int64_t) s * 2 + 1) * stride + j] = mR;
+    float* oL = master + ((int64_t) s * 2) * stride + j;
+    float* oR = oL + stride;
+    if (VEC == 4) {
+        *reinterpret_cast<float4*>(oL) = make_float4(mL[0], mL[1 % VEC], mL[2 % VEC], mL[3 % VEC]);
+        *reinterpret_cast<float4*>(oR) = make_float4(mR[0], mR[1 % VEC], mR[2 % VEC], mR[3 % VEC]);
+    } else { oL[0] = mL[0]; oR[0] = mR[0]; }
 }
 
 cudaError_t launch_master_mix(const float* raw, const BusDev* buses, float* master, int nSessions, int B, int64_t stride,
                               int64_t n, cudaStream_t stream) {
-    const dim3 grid((unsigned) ((n + 255) / 256), (unsigned) nSessions);
-    master_mix_kernel<<<grid, 256, 0, stream>>>(raw, buses, master, nSessions, B, stride, n);
+    if ((n & 3) == 0 && (stride & 3) == 0) {
+        const dim3 grid((unsigned) ((n / 4 + 255) / 256), (unsigned) nSessions);
+        master_mix_kernel<4><<<grid, 256, 0, stream>>>(raw, buses, master, nSessions, B, stride, n);
+    } else {
+        const dim3 grid((unsigned) ((n + 255) / 256), (unsigned) nSessions);
+        master_mix_kernel<1><<<grid, 256, 0, stream>>>(raw, buses, master, nSessions, B, stride, n);
+    }
     return cudaGetLastError();
 }
 
