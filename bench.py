@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--cpu-sessions", type=int, default=0, help="sessions of the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--no-thumb", action="store_true", help="skip the WaveFormItem thumbnail probe (BASELINE configs[3])")
     ap.add_argument("--span-mix", type=int, default=0, help="G>1: groups of G GPUs share one mix -> NCCL reduce of the masters")
     ap.add_argument("--seed", type=int, default=5)
     ap.add_argument("--quirks", type=int, default=7, help="ZL_Q* bits of the Z-mode voice (7 = faithful to libzl, the default)")
@@ -395,6 +396,51 @@ def latency_probe(local_rank, iters=1500):
             "what": "one 512-frame period of one 128-voice session: zl_render + zl_read_master_all to pinned host"}
 
 
+def thumbnail_probe(local_rank, peak):
+    """BASELINE configs[3]: WaveFormItem / juce::AudioThumbnail min/max over a 1 h stereo 48 kHz clip at 4096 pixels.
+    level 0 (512-sample int8 min/max blocks) is the HBM-bound kernel: algorithmic bytes = nch * 4 * frames read."""
+    import torch
+    import libzl_b200
+    from libzl_b200 import _capi as K
+    from libzl_b200.engine import Engine
+    dev = torch.device("cuda", local_rank)
+    frames = 3600 * 48000
+    e = Engine(lib=libzl_b200.load(), n_sessions=1, buses_per_session=1, voices_per_bus=1, max_clips=2, outputs=K.ZL_OUT_RAW, device=local_rank)
+    stream = torch.cuda.Stream(device=dev)
+    e.set_stream(stream.cuda_stream)
+    g = torch.Generator(device=dev); g.manual_seed(4)
+    pcm = torch.zeros((frames + 8, 2), dtype=torch.float32, device=dev)
+    pcm[:frames].uniform_(-1.0, 1.0, generator=g)
+    t = torch.arange(frames, device=dev, dtype=torch.float32) / 48000.0
+    pcm[:frames] *= (0.55 + 0.45 * torch.sin(2 * torch.pi * 0.1 * t)).unsqueeze(1)          # slow 0.1 Hz amplitude envelope
+    pcm[::1000003] = 1.0; pcm[500001::1000003] = -1.0                                        # sparse full-scale clicks
+    pcm[frames:] = 0.0
+    del t
+    torch.cuda.synchronize()
+    cid = e.add_clip_device(pcm.data_ptr(), 2, frames, 48000.0)
+    ms = []
+    for _ in range(6):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        e.thumb_build(cid, 512)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    t0 = time.perf_counter()
+    px = e.thumb_pixels(cid, 0.0, 3600.0, 4096)
+    px_ms = (time.perf_counter() - t0) * 1e3
+    t0 = time.perf_counter()
+    mask = e.thumb_raster(cid, 0, 0.0, 3600.0, 4096, 400)
+    raster_ms = (time.perf_counter() - t0) * 1e3
+    best = min(ms[1:])
+    alg = 2 * 4 * frames
+    e.close()
+    return {"what": "juce::AudioThumbnail level 0 (512-sample int8 min/max) over a 1 h stereo 48 kHz clip, HBM-resident; then 4096 pixels and the 4096x400 column mask to the host",
+            "level0_ms": round(best, 4), "algorithmic_bytes": alg, "achieved_GBps": alg / (best * 1e-3) / 1e9, "frac": alg / (best * 1e-3) / 1e9 / peak,
+            "pixels_4096_host_ms": round(px_ms, 3), "raster_4096x400_host_ms": round(raster_ms, 3),
+            "pixel_checksum": int(px.astype(np.int64).sum()), "mask_on": int(mask.sum()) if mask is not None else None}
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -471,6 +517,12 @@ def main():
                 line["latency"] = latency_probe(local_rank)
             except Exception as ex:   # noqa: BLE001
                 line["latency"] = {"error": str(ex)}
+        if world == 1 and not args.no_thumb:
+            try:
+                del r["keep"]
+                line["thumbnail"] = thumbnail_probe(local_rank, peak)
+            except Exception as ex:   # noqa: BLE001
+                line["thumbnail"] = {"error": str(ex)}
         if world == 1 and not args.no_cpu_baseline:
             sessions = cpu_sample_size(args)
             cvf, cdt, th = run_cpu(args, sessions, 2, 1)
