@@ -166,6 +166,17 @@ def S_BUS_BYTES(args):
     return args.sessions * BUSES * 2 * args.blocks * FRAMES * 4      # raw bus planes of one step on one GPU
 
 
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one gather_kernel launch of this workload, from the committed
+    ncu --set full capture (profiles/r01_final_traffic.json); None when the file is missing or the workload differs."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_final_traffic.json")) as f:
+            t = json.load(f)["gather"]
+        return t["dram_bytes_read"] + t["dram_bytes_write"]
+    except Exception:
+        return None
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -501,7 +512,8 @@ def main():
                 "clocks": r["clocks"], "gpu_launches": r["launches"],
                 "e2e": {"value": e2e_vf / (e2e_ms * 1e-3), "unit": "voice-frames/s", "h2d_bytes_per_step": r["h2d"],
                         "d2h_bytes_per_step": r["d2h"], "what": "per step: zl_command_batch (H2D) + zl_render + zl_read_master_all_async (master of every session D2H to pinned host, overlapping the next step's render); zl_read_wait before the clock stops"},
-                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                             "traffic": (ncu_traffic() if (args.sessions, args.blocks, args.quirks) == (4096, 16, 7) else None),
                              "peak_source": peak_src, "frac_of_nominal_8TBs": ach / 8000.0,
                              "algorithmic_bytes_per_launch": alg_bytes,
                              "bytes_per_voice_frame": step_alg_bytes / (r["timed_vf"] / args.steps),
