@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--cpu-sessions", type=int, default=0, help="sessions of the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--rms", action="store_true", help="also produce the per-bus f64 sum of squares (getRMSLevel extension; libzl's AudioLevels has peaks only)")
     ap.add_argument("--no-thumb", action="store_true", help="skip the WaveFormItem thumbnail probe (BASELINE configs[3])")
     ap.add_argument("--span-mix", type=int, default=0, help="G>1: groups of G GPUs share one mix -> NCCL reduce of the masters")
     ap.add_argument("--seed", type=int, default=5)
@@ -199,7 +200,7 @@ def run_cuda(args, rank, world, local_rank):
     S, NB = args.sessions, args.blocks
     total_steps = args.warmup + args.steps
     wl = Workload(S, NB, total_steps * 2 + 2, args.seed, rank)
-    outputs = K.ZL_OUT_RAW | K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS
+    outputs = K.ZL_OUT_RAW | K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS | (K.ZL_OUT_RMS if args.rms else 0)
     e = Engine(lib=libzl_b200.load(), n_sessions=S, buses_per_session=BUSES, voices_per_bus=VOICES,
                max_clips=S * CLIPS_PER_SESSION, max_frames=FRAMES, max_blocks=NB, outputs=outputs, device=local_rank,
                quirks=args.quirks)
@@ -347,7 +348,7 @@ def run_cpu(args, sessions, steps, warmup, threads=None):
     threads = threads or os.cpu_count() or 1
     NB = args.blocks
     wl = Workload(sessions, NB, warmup + steps + 1, args.seed, rank=0)
-    outputs = K.ZL_OUT_RAW | K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS
+    outputs = K.ZL_OUT_RAW | K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS | (K.ZL_OUT_RMS if args.rms else 0)
     e = Engine(lib=lib, n_sessions=sessions, buses_per_session=BUSES, voices_per_bus=VOICES,
                max_clips=sessions * CLIPS_PER_SESSION, max_frames=FRAMES, max_blocks=NB, outputs=outputs, quirks=args.quirks)
     lib.dll.zlo_set_threads(e.ctx, threads)
@@ -466,7 +467,7 @@ def main():
                 f"shape = 16 buses x 8 voices, batched as configs[4] offline render), {args.blocks} periods x {FRAMES} frames per step")
     config = {"workload": workload, "sessions_per_gpu": args.sessions, "buses": BUSES, "voices_per_bus": VOICES,
               "frames": FRAMES, "blocks_per_step": args.blocks, "mode": "Z (libzl process(), quirks faithful)",
-              "outputs": "raw bus + master + peak meters", "quirks": args.quirks,
+              "outputs": "raw bus + master + peak meters" + (" + RMS sums" if args.rms else " (RMS, an extension over libzl's peak-only AudioLevels: --rms)"), "quirks": args.quirks,
               "kernels_per_period": "plan_kernel + walk_kernel + gather_kernel (+ one master_mix_kernel per step)", "parallelism": (f"sessions sharded over {args.gpus} GPU(s), no collective" if args.span_mix <= 1 else
                               f"sessions sharded over {args.gpus} GPU(s); groups of {args.span_mix} GPUs share one mix: NCCL all-reduce of the master planes per step"),
               "l2": "inputs (clip PCM 3 MB/session) larger than L2; no flush needed"}

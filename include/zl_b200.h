@@ -73,7 +73,7 @@ typedef struct {
     double  sample_rate;        /* output (JACK) rate: juce::Synthesiser::setCurrentPlaybackSampleRate, lib/SamplerSynth.cpp:271-272 */
     int32_t n_sessions;         /* independent mixes (one JACK graph each); 1 for the realtime layout */
     int32_t buses_per_session;  /* SamplerChannels per session; reference 12    lib/SamplerSynth.cpp:258 */
-    int32_t voices_per_bus;     /* SAMPLER_CHANNEL_VOICE_COUNT; reference 8     lib/SamplerSynth.cpp:23; power of two <= 32 */
+    int32_t voices_per_bus;     /* SAMPLER_CHANNEL_VOICE_COUNT; reference 8     lib/SamplerSynth.cpp:23; 1 .. 1024 */
     int32_t max_clips;
     int32_t max_slices;         /* slice table capacity per clip; reference default 16  lib/ClipAudioSource.cpp:204 */
     int32_t max_frames;         /* frames per block upper bound (JACK period) */

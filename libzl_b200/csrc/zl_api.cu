@@ -250,7 +250,7 @@ int zl_config_default(zl_config* c) {
 int zl_ctx_create(const zl_config* cfg, zl_ctx** out) {
     if (!cfg || !out) return ZL_ERR_INVALID;
     const int V = cfg->voices_per_bus;
-    if (cfg->n_sessions < 1 || cfg->buses_per_session < 1 || V < 1 || V > 32 || (V & (V - 1)) || cfg->sample_rate <= 0
+    if (cfg->n_sessions < 1 || cfg->buses_per_session < 1 || V < 1 || V > 1024 || cfg->sample_rate <= 0
         || cfg->max_clips < 1 || cfg->max_slices < 0 || cfg->max_frames < 1 || cfg->max_blocks < 1)
         return ZL_ERR_INVALID;
     int ndev = 0;

@@ -701,7 +701,7 @@ int zlo_config_default(zl_config* c) {
 int zlo_ctx_create(const zl_config* cfg, zl_ctx** out) {
     if (!cfg || !out) return ZL_ERR_INVALID;
     const int V = cfg->voices_per_bus;
-    if (cfg->n_sessions < 1 || cfg->buses_per_session < 1 || V < 1 || V > 32 || (V & (V - 1)) || cfg->sample_rate <= 0) return ZL_ERR_INVALID;
+    if (cfg->n_sessions < 1 || cfg->buses_per_session < 1 || V < 1 || V > 1024 || cfg->sample_rate <= 0) return ZL_ERR_INVALID;
     zl_ctx* c = new zl_ctx;
     c->cfg = *cfg;
     c->channels.resize((size_t) cfg->n_sessions * (size_t) cfg->buses_per_session);

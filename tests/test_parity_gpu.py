@@ -192,3 +192,42 @@ def test_pipelined_master_readback_matches_synchronous(product, oracle):
     for a, b, c in zip(sync, pipe, ref):
         assert np.array_equal(a, b)
         assert np.array_equal(a, c)
+
+
+def test_wide_buses_take_the_unstaged_and_atomic_paths(product, oracle):
+    """V = 24 (> 16: descriptors straight from L2, no window staging) and V = 40 (> 32: positions-model gain by atomicMax,
+    single-stream render) must match the oracle exactly like the common V <= 16 layout."""
+    for voices in (24, 40):
+        a, b = both(S.cfg2_polyphonic, product, oracle, n_sessions=2, buses=2, voices=voices, nframes=256, nblocks=6)
+        assert not S.compare(a, b, exact_audio=True)
+        assert a["voice_frames"].sum() > 10000
+
+
+def test_high_pitch_ratios_bypass_the_window_staging(product, oracle):
+    """Ratios above 2.4 (source windows larger than a staging slot: 96 kHz clips played two octaves up, ratio up to 8)
+    and below 0.1 take the direct-gather path; mixed on one bus with staged voices the slot order must hold."""
+    def run(lib):
+        rng = np.random.default_rng(21)
+        e = Engine(lib=lib, n_sessions=2, buses_per_session=2, voices_per_bus=8)
+        clips = []
+        for k in range(4):
+            pcm = rng.uniform(-1, 1, (2, 60000)).astype(np.float32)
+            c = e.add_clip(pcm, 96000.0 if k & 1 else 48000.0)
+            e.set_clip_params(c, attack=0.001, decay=0.02, sustain=0.7, release=0.05, pan=float(rng.uniform(-1, 1)),
+                              length_beats=float(rng.choice([1.5, 2.25])), root_note=60)
+            clips.append(c)
+        for s in range(2):
+            for b in range(2):
+                for v in range(8):
+                    e.play(clips[(v + b) % 4], loop=bool(v & 1), midi_channel=b - 2, note=int(rng.choice([24, 36, 60, 72, 84])),
+                           volume=float(rng.uniform(0.3, 1.0)), session=s)
+        out = []
+        for step in range(3):
+            e.render(4, 512, e.make_clocks(4, 512, first_block=4 * step))
+            out.append((e.master_all().copy(), np.stack([np.stack(e.bus(s, b, K.ZL_BUS_RAW)) for s in range(2) for b in range(2)]),
+                        e.block_levels()[0].copy(), e.voice_frames()))
+        e.close()
+        return out
+    for (m0, r0, p0, v0), (m1, r1, p1, v1) in zip(run(product), run(oracle)):
+        assert np.array_equal(m0, m1) and np.array_equal(r0, r1) and np.array_equal(p0, p1) and v0 == v1
+        assert np.abs(m0).max() > 0.05
