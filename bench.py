@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--cpu-sessions", type=int, default=0, help="sessions of the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--no-kernel-events", action="store_true", help="experiment: no per-launch event pairs in the timed region")
     ap.add_argument("--rms", action="store_true", help="also produce the per-bus f64 sum of squares (getRMSLevel extension; libzl's AudioLevels has peaks only)")
     ap.add_argument("--no-thumb", action="store_true", help="skip the WaveFormItem thumbnail probe (BASELINE configs[3])")
     ap.add_argument("--span-mix", type=int, default=0, help="G>1: groups of G GPUs share one mix -> NCCL reduce of the masters")
@@ -277,15 +278,17 @@ def run_cuda(args, rank, world, local_rank):
     e._chk(e.lib.kernel_timing(e.ctx, 0), "kernel_timing")
     e._chk(e.lib.ctx_set_overlap(e.ctx, 1), "ctx_set_overlap")
     gather_alone_ms = kms0.value / max(1, kn0.value)
-    sampler = ClockSampler(local_rank) if rank == 0 else None
+    sampler = ClockSampler(local_rank) if rank == 0 and not os.environ.get("ZL_BENCH_NO_SAMPLER") else None
     launches0 = e.launch_count()
     vf0, src0 = e.total_counters()
-    e._chk(e.lib.kernel_timing(e.ctx, 2), "kernel_timing")    # CUDA events around each gather_kernel launch, same stream
+    e._chk(e.lib.kernel_timing(e.ctx, 0 if args.no_kernel_events else 2), "kernel_timing")    # CUDA events around each gather_kernel launch, same stream
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     ev[0].record(stream)
+    th0 = time.perf_counter()
     for k in range(args.steps):
         step(args.warmup + k)
         ev[k + 1].record(stream)
+    host_submit_ms = (time.perf_counter() - th0) * 1e3 / args.steps      # host time to queue one step (commands + launches)
     barrier()
     elapsed_ms = ev[0].elapsed_time(ev[-1])
     kernel_launches = e.launch_count() - launches0
@@ -332,7 +335,7 @@ def run_cuda(args, rank, world, local_rank):
     del ref
     for hp in hostp:
         e.lib.host_free(hp)
-    return dict(e=e, kernel_ms=kernel_ms, gather_ms_per_step=gather_ms_per_step, gather_alone_ms=gather_alone_ms, elapsed_ms=elapsed_ms, step_ms=step_ms, timed_vf=timed_vf, timed_src=timed_src, launches=kernel_launches,
+    return dict(e=e, host_submit_ms=host_submit_ms, kernel_ms=kernel_ms, gather_ms_per_step=gather_ms_per_step, gather_alone_ms=gather_alone_ms, elapsed_ms=elapsed_ms, step_ms=step_ms, timed_vf=timed_vf, timed_src=timed_src, launches=kernel_launches,
                 clocks=clocks, e2e_s=e2e_s, e2e_vf=e2e_vf, h2d=h2d, d2h=d2h, out_bytes=out_bytes, state_bytes=state_bytes,
                 dist=dist, dev=dev, wl=wl, keep=pcm)
 
@@ -505,7 +508,7 @@ def main():
         step_alg_bytes = (4.0 * r["timed_src"] / args.steps) + r["out_bytes"] + r["state_bytes"]
         gather_bytes = (4.0 * r["timed_src"] / args.steps + S_BUS_BYTES(args) + args.blocks * args.sessions * BUSES * 2 * 4) / args.blocks
         alg_bytes = gather_bytes
-        mean_ms = r["kernel_ms"]
+        mean_ms = r["kernel_ms"] or r["gather_alone_ms"]          # --no-kernel-events: fall back to the stand-alone launch
         ach = alg_bytes / (mean_ms * 1e-3) / 1e9
         line = {"metric": "voice_frames_per_s", "value": vf / (el_ms * 1e-3), "unit": "voice-frames/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": el_ms / args.steps, "higher_is_better": True,
@@ -524,7 +527,7 @@ def main():
                              "kernel_alone_ms": r["gather_alone_ms"], "frac_alone": alg_bytes / (r["gather_alone_ms"] * 1e-3) / 1e9 / peak,
                              "whole_step_frac": step_alg_bytes / (el_ms / args.steps * 1e-3) / 1e9 / peak,
                              "whole_step_note": "all algorithmic bytes of a step (source + voice state + raw planes + master + peaks) / ms_per_step: plan, walk, gather and master mix together"},
-                "voice_frames_per_step": vf / args.steps / world}
+                "voice_frames_per_step": vf / args.steps / world, "host_submit_ms_per_step": r["host_submit_ms"]}
         if world == 1 and not args.no_latency:
             try:
                 line["latency"] = latency_probe(local_rank)

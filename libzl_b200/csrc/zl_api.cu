@@ -10,11 +10,18 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <chrono>
 
 #include "zl_device.cuh"
 
 namespace zl {
 cudaError_t launch_plan(RenderParams& P, cudaStream_t stream);
+#ifndef ZL_PLAN_CTAS_PER_SM
+#define ZL_PLAN_CTAS_PER_SM 2      // plan_kernel CTAs per SM beside a running gather (0 = whole grid)
+#endif
+#ifndef ZL_WALK_CTAS_PER_SM
+#define ZL_WALK_CTAS_PER_SM 4      // walk_kernel one-warp CTAs per SM beside a running gather (0 = default grid)
+#endif
 cudaError_t launch_gather(RenderParams& P, cudaStream_t stream, cudaEvent_t gatherBegin, cudaEvent_t gatherEnd);
 size_t render_scratch_bytes(int nVoices, int nframes, size_t off[5]);
 void render_bind_scratch(RenderParams& P, void* scratch, int nVoices, int nframes);
@@ -351,6 +358,16 @@ int zl_sync(zl_ctx* ctx) {
 }
 
 // ---- clips ------------------------------------------------------------------------------------
+static int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e && *e ? atoi(e) : dflt;
+}
+static int ctx_sm_count() {
+    int dev = 0, n = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n;
+}
+
 static int finish_clip(zl_ctx* ctx, int id, int32_t* clip_id) {
     ClipHost& c = ctx->clips[(size_t) id];
     c.live = true;
@@ -464,8 +481,10 @@ int zl_command(zl_ctx* ctx, int32_t session, int32_t block, uint64_t tick, const
 
 int zl_command_batch(zl_ctx* ctx, int32_t n, const int32_t* s, const int32_t* b, const uint64_t* t, const zl_clip_command* c) {
     if (!ctx || n < 0 || (n && (!s || !b || !t || !c))) return invalid(ctx, "command_batch: bad argument");
+    auto hp0 = std::chrono::steady_clock::now();
     ctx->pending.reserve(ctx->pending.size() + (size_t) n);
     for (int i = 0; i < n; ++i) { int rc = zl_command(ctx, s[i], b[i], t[i], &c[i]); if (rc != ZL_OK) return rc; }
+    if (getenv("ZL_B200_HOSTPROF")) fprintf(stderr, "hostprof batch %.1f us\n", std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - hp0).count());
     return ZL_OK;
 }
 
@@ -541,6 +560,7 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     if (nblocks < 1 || nframes < 1 || !clocks || nblocks > ctx->cfg.max_blocks || nframes > ctx->cfg.max_frames)
         return invalid(ctx, "render: nblocks/nframes out of range or null clocks");
     if (ctx->cfg.voices_per_bus > 1024) return invalid(ctx, "render: more than 1024 voices per bus");
+    auto hp0 = std::chrono::steady_clock::now();
     int rc = ensure_outputs(ctx, nblocks, nframes);
     if (rc != ZL_OK) return rc;
     cudaStream_t st = ctx->stream;
@@ -557,17 +577,31 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     std::vector<int> count, begin;
     std::vector<char> keep;
     if (!ctx->pending.empty()) {
-        std::stable_sort(ctx->pending.begin(), ctx->pending.end(), [](const Pending& a, const Pending& b) { return a.block < b.block; });
         count.assign(NB, 0); begin.assign(NB, 0);
-        std::vector<int> inBlock(NB, 0), last(NB, -1);
         keep.assign(ctx->pending.size(), 0);
+        // common case first: no bus holds more than one period's ring of commands in this call, so none can overflow
+        // and the arrival order is all the device needs (it filters by block itself)
+        int most = 0;
         for (size_t i = 0; i < ctx->pending.size(); ++i) {
             const Pending& p = ctx->pending[i];
+            if (p.block >= nblocks) continue;
             const size_t gb = (size_t) p.session * ctx->cfg.buses_per_session + p.bus;
-            if (p.block >= nblocks) { ctx->dropped++; continue; }
-            if (last[gb] != p.block) { last[gb] = p.block; inBlock[gb] = 0; }
-            if (++inBlock[gb] > 256) { ctx->dropped++; continue; }
-            keep[i] = 1; count[gb]++; nCmds++;
+            keep[i] = 1; most = std::max(most, ++count[gb]);
+        }
+        if (most <= 256) {
+            for (size_t i = 0; i < ctx->pending.size(); ++i) { if (keep[i]) nCmds++; else ctx->dropped++; }
+        } else {
+            std::stable_sort(ctx->pending.begin(), ctx->pending.end(), [](const Pending& a, const Pending& b) { return a.block < b.block; });
+            std::fill(count.begin(), count.end(), 0); std::fill(keep.begin(), keep.end(), 0);
+            std::vector<int> inBlock(NB, 0), last(NB, -1);
+            for (size_t i = 0; i < ctx->pending.size(); ++i) {
+                const Pending& p = ctx->pending[i];
+                const size_t gb = (size_t) p.session * ctx->cfg.buses_per_session + p.bus;
+                if (p.block >= nblocks) { ctx->dropped++; continue; }
+                if (last[gb] != p.block) { last[gb] = p.block; inBlock[gb] = 0; }
+                if (++inBlock[gb] > 256) { ctx->dropped++; continue; }
+                keep[i] = 1; count[gb]++; nCmds++;
+            }
         }
     }
     if (ctx->busesDirty) {
@@ -580,7 +614,9 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     const size_t offRanges = (sizeof(zl_block_clock) * (size_t) nblocks + 15) & ~size_t(15);
     const size_t offCmds = offRanges + (nCmds ? ((sizeof(int32_t) * 2 * NB + 15) & ~size_t(15)) : 0);
     const size_t slotBytes = offCmds + sizeof(CmdDev) * nCmds;
+    auto hp1 = std::chrono::steady_clock::now();
     CK(cudaEventSynchronize(ctx->clkEv[slot]));   // the render that used this slot two calls ago is done
+    auto hp2 = std::chrono::steady_clock::now();
     if (slotBytes > ctx->slotCap[slot]) {
         if (ctx->h_slot[slot]) cudaFreeHost(ctx->h_slot[slot]);
         if (ctx->d_slot[slot]) cudaFree(ctx->d_slot[slot]);
@@ -609,6 +645,7 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     }
     ctx->pending.clear();
     CK(cudaMemcpyAsync(ds, hs, slotBytes, cudaMemcpyHostToDevice, st));
+    auto hp3 = std::chrono::steady_clock::now();
     CK(cudaMemsetAsync(ctx->d_counters, 0, 2 * sizeof(unsigned long long), st));
     const zl_block_clock* dck = reinterpret_cast<const zl_block_clock*>(ds);
 
@@ -657,6 +694,15 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         CK(cudaEventRecord(ctx->evStart, st));
         CK(cudaStreamWaitEvent(ps, ctx->evStart, 0));
     }
+    const char* tl = ctx->timing == 2 ? nullptr : getenv("ZL_B200_TIMELINE");
+    std::vector<cudaEvent_t> tlev;
+    static cudaEvent_t tlBase = nullptr;
+    if (tl) {
+        if (!tlBase) { CK(cudaEventCreate(&tlBase)); CK(cudaEventRecord(tlBase, st)); }
+        cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, st)); tlev.push_back(e);
+    }
+    static const int planCap = env_int("ZL_B200_PLAN_CTAS", ZL_PLAN_CTAS_PER_SM) * ctx_sm_count();
+    static const int walkCap = env_int("ZL_B200_WALK_CTAS", ZL_WALK_CTAS_PER_SM) * ctx_sm_count();
     size_t soff[5];
     const size_t scratchBytes = render_scratch_bytes((int) (NB * ctx->cfg.voices_per_bus), nframes, soff);
     for (int blk = 0; blk < nblocks; ++blk) {      // one JACK period = plan_kernel + walk_kernel + gather_kernel
@@ -664,7 +710,13 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         P.blk = blk;
         render_bind_scratch(P, static_cast<unsigned char*>(ctx->d_scratch) + (size_t) par * scratchBytes, (int) (NB * ctx->cfg.voices_per_bus), nframes);
         if (overlap && blk >= 2) CK(cudaStreamWaitEvent(ps, ctx->evGather[par], 0));   // gather(blk - 2) has released this hand-over buffer
+        // beside a running gather the planner gets a few CTAs per SM only: it has the whole gather to finish in, and
+        // a full-size high-priority grid would push the gather off the SMs while it waits on its own latencies
+        P.planCtaCap = overlap && blk >= 1 ? planCap : 0;
+        P.walkCtaCap = overlap && blk >= 1 ? walkCap : 0;
+        if (tl) { cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, ps)); tlev.push_back(e); }
         CK(launch_plan(P, ps));
+        if (tl) { cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, ps)); tlev.push_back(e); }
         if (overlap) {
             CK(cudaEventRecord(ctx->evPlan[par], ps));
             CK(cudaStreamWaitEvent(st, ctx->evPlan[par], 0));
@@ -673,6 +725,9 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         if (ctx->timing == 2) {
             CK(cudaEventCreate(&g0)); CK(cudaEventCreate(&g1));
             ctx->tev.push_back(g0); ctx->tev.push_back(g1);
+        } else if (tl) {
+            CK(cudaEventCreate(&g0)); CK(cudaEventCreate(&g1));
+            tlev.push_back(g0); tlev.push_back(g1);
         }
         CK(launch_gather(P, st, g0, g1));
         if (overlap) CK(cudaEventRecord(ctx->evGather[par], st));
@@ -690,6 +745,32 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     ctx->nblocks = nblocks; ctx->nframes = nframes;
     ctx->lvlCached = false; ctx->vfCached = false;
     CK(cudaEventRecord(ctx->clkEv[slot], st));
+    if (getenv("ZL_B200_HOSTPROF")) {
+        auto hp4 = std::chrono::steady_clock::now();
+        auto us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
+        fprintf(stderr, "hostprof sort/count %.1f wait %.1f fill+copy %.1f launches %.1f us\n", us(hp0, hp1), us(hp1, hp2), us(hp2, hp3), us(hp3, hp4));
+    }
+    if (tl) {                                       // debugging aid: where each period's planner and gather sat in time
+        static std::vector<std::vector<cudaEvent_t>> all;
+        cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, st)); tlev.push_back(e);
+        all.push_back(tlev);
+        if ((int) all.size() == env_int("ZL_B200_TIMELINE_N", 8)) {
+            CK(cudaDeviceSynchronize());
+            if (FILE* f = fopen(tl, "a")) {
+                for (auto& v : all) {
+                    float t0 = 0.0f, t1 = 0.0f;
+                    cudaEventElapsedTime(&t0, tlBase, v.front()); cudaEventElapsedTime(&t1, tlBase, v.back());
+                    fprintf(f, "render %.3f..%.3f\n", t0, t1);
+                    for (size_t i = 1; i + 4 < v.size(); i += 4) {
+                        float t[4];
+                        for (int k = 0; k < 4; ++k) cudaEventElapsedTime(&t[k], tlBase, v[i + k]);
+                        fprintf(f, "blk %zu plan %.3f..%.3f gather %.3f..%.3f\n", (i - 1) / 4, t[0], t[1], t[2], t[3]);
+                    }
+                }
+                fclose(f);
+            }
+        }
+    }
     return ZL_OK;
 }
 

@@ -106,6 +106,7 @@ struct RenderParams {
     int32_t* walkQueue;      // [nVoices] voices deferred by plan_kernel to walk_kernel in this block
     int32_t* walkCount;      // [nblocks][2] queue lengths: serial walkers (front of the queue), others (back); zeroed per launch
     int32_t nVoices, tilesPerBlock, blk, planBusesPerCta;
+    int32_t planGroups, planCtaCap, walkCtaCap;     // bus groups of plan_kernel; grid caps beside a running gather (0 = none)
 };
 
 // ---------------------------------------------------------------------------------------------

@@ -348,11 +348,15 @@ __global__ void __launch_bounds__(MAXT, MAXT == 128 ? ZL_PLAN_MINB : 1) plan_ker
     const int V = P.V, B = P.B;
     const int tid = threadIdx.x;
     const int lb = tid / V, slot = tid - lb * V;              // bus within the CTA, voice slot within the bus
-    const int gb = blockIdx.x * P.planBusesPerCta + lb;        // global bus = session * B + bus
-    const bool hasVoice = lb < P.planBusesPerCta && gb < P.nSessions * B;
-    const int vIdx = gb * V + slot;                            // global voice
     const int blk = P.blk;
     const unsigned FULL = 0xffffffffu;
+    unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
+    // grid-stride over the bus groups: beside a running gather the grid is capped (launch_plan) so that the planner
+    // shares every SM with the gather instead of displacing it
+    for (int grp = blockIdx.x; grp < P.planGroups; grp += gridDim.x) {
+    const int gb = grp * P.planBusesPerCta + lb;               // global bus = session * B + bus
+    const bool hasVoice = lb < P.planBusesPerCta && gb < P.nSessions * B;
+    const int vIdx = gb * V + slot;                            // global voice
 
     // ---- commands of this block: SamplerChannel::process ring drain   lib/SamplerSynth.cpp:118-122 ------------------
     // The bus's slot-0 thread applies them serially on the HBM voice records before anybody loads its state.
@@ -364,9 +368,12 @@ __global__ void __launch_bounds__(MAXT, MAXT == 128 ? ZL_PLAN_MINB : 1) plan_ker
         }
         __syncthreads();
     }
-    unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
     int kind = 0;
-    if (hasVoice) kind = plan_voice_block<JMODE, Q3, true>(P, vIdx, gb, nVoiceFrames, nSrcFloats);
+    if (hasVoice) {
+        unsigned long long a = 0, b = 0;
+        kind = plan_voice_block<JMODE, Q3, true>(P, vIdx, gb, a, b);
+        nVoiceFrames += a; nSrcFloats += b;
+    }
     // queue the deferred voices of this warp: serial walkers from the front of the queue, the others from its back; one
     // atomic per warp and kind
     const unsigned lt = (1u << (tid & 31)) - 1u;
@@ -381,6 +388,7 @@ __global__ void __launch_bounds__(MAXT, MAXT == 128 ? ZL_PLAN_MINB : 1) plan_ker
         if (kind == 1) P.walkQueue[baseA + __popc(mA & lt)] = vIdx;
         if (kind == 2) P.walkQueue[P.nVoices - 1 - (baseB + __popc(mB & lt))] = vIdx;
     }
+    }   // bus groups
     for (int o = 16; o > 0; o >>= 1) {
         nVoiceFrames += __shfl_down_sync(FULL, nVoiceFrames, o);
         nSrcFloats += __shfl_down_sync(FULL, nSrcFloats, o);
@@ -722,7 +730,8 @@ cudaError_t launch_plan(RenderParams& P, cudaStream_t stream) {
     if (V < 1 || V > 1024) return cudaErrorInvalidValue;
     P.planBusesPerCta = V >= 128 ? 1 : 128 / V;
     const int planThreads = ((P.planBusesPerCta * V + 31) / 32) * 32;
-    const int planGrid = (nBuses + P.planBusesPerCta - 1) / P.planBusesPerCta;
+    P.planGroups = (nBuses + P.planBusesPerCta - 1) / P.planBusesPerCta;
+    const int planGrid = P.planCtaCap > 0 ? min(P.planGroups, P.planCtaCap) : P.planGroups;
     const bool q3 = (P.quirks & ZL_Q3_RENOTEOFF) != 0;
     if (planThreads <= 128) {
         if (P.mode == ZL_MODE_J) plan_kernel<true, false, 128><<<planGrid, planThreads, 0, stream>>>(P);
@@ -735,7 +744,7 @@ cudaError_t launch_plan(RenderParams& P, cudaStream_t stream) {
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    const int wGrid = min((P.nVoices + 31) / 32 + 1, 148 * 16);
+    const int wGrid = min((P.nVoices + 31) / 32 + 1, P.walkCtaCap > 0 ? P.walkCtaCap : 148 * 16);
     if (P.mode == ZL_MODE_J) walk_kernel<true, false><<<wGrid, 32, 0, stream>>>(P);
     else if (q3) walk_kernel<false, true><<<wGrid, 32, 0, stream>>>(P);
     else walk_kernel<false, false><<<wGrid, 32, 0, stream>>>(P);
