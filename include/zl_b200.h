@@ -193,6 +193,30 @@ ZL_EXPORT int ZL_FN(clip_create_from_pcm)(zl_ctx* ctx, const float* const* plana
  * lanes past a voice's end from that padding instead of predicating the loads). */
 ZL_EXPORT int ZL_FN(clip_create_from_device)(zl_ctx* ctx, const void* d_interleaved, int32_t nch,
                                              int64_t length, double sample_rate, int32_t* clip_id);
+/* n1: WAV ingest.  What juce::WavAudioFormatReader finds in a RIFF/WAVE (or RF64) image
+ * (JUCE/juce_audio_formats/codecs/juce_WavAudioFormat.cpp:933-1190): PCM 8/16/24/32 bit or IEEE float 32. */
+typedef struct zl_wav_format {
+    int32_t channels;
+    int32_t bits_per_sample;
+    int32_t is_float;           /* usesFloatingPointData  :1008-1033 */
+    int32_t bytes_per_frame;
+    double sample_rate;
+    int64_t frames;             /* lengthInSamples = data bytes / bytes per frame  :1070 */
+    uint64_t data_offset;       /* dataChunkStart */
+    uint64_t data_bytes;
+} zl_wav_format;
+/* Host-only chunk walk (no device needed); ZL_ERR_INVALID when WavAudioFormat::createReaderFor would return no reader
+ * (:1718-1731) or the sample format is not one copySampleData decodes (:1232-1245). */
+ZL_EXPORT int ZL_FN(wav_probe)(const void* wav, uint64_t nbytes, zl_wav_format* out);
+/* ClipAudioSource_new(path) end to end (lib/libzl.cpp:107-128 -> lib/SamplerSynthSound.cpp:28-59): the file's bytes go to
+ * the device as they are and are decoded there - left-justified int32, then f32(i) * 2^-31
+ * (juce_AudioDataConverters.h:134,159,184,209; juce_AudioFormatReader.cpp:39-46,139-183) - into the clip's HBM frames;
+ * the first min(2, channels) channels are kept; bytes the data chunk promises beyond the end of the image read as zero
+ * (juce_WavAudioFormat.cpp:1212-1218).  No JUCE, no CPU decode. */
+ZL_EXPORT int ZL_FN(clip_create_from_wav)(zl_ctx* ctx, const void* wav, uint64_t nbytes, int32_t* clip_id);
+ZL_EXPORT int ZL_FN(clip_create_from_wav_file)(zl_ctx* ctx, const char* path, int32_t* clip_id);
+/* The clip's sample data as SamplerSynthSound::audioData() holds it: planar[ch][length] floats, ch < min(2, channels). */
+ZL_EXPORT int ZL_FN(clip_read_pcm)(zl_ctx* ctx, int32_t clip_id, float* const* planar, int32_t nch, int64_t length);
 ZL_EXPORT int ZL_FN(clip_destroy)(zl_ctx* ctx, int32_t clip_id);
 ZL_EXPORT int ZL_FN(clip_params_default)(zl_ctx* ctx, int32_t clip_id, zl_clip_params* out);
 ZL_EXPORT int ZL_FN(clip_set_params)(zl_ctx* ctx, int32_t clip_id, const zl_clip_params* p);
@@ -306,6 +330,19 @@ ZL_EXPORT int ZL_FN(passthrough_process)(zl_ctx* ctx, const zl_passthrough_param
 /* Peak scan of one period (lib/AudioLevels.cpp:365-382) + sum of squares, HOST buffers. */
 ZL_EXPORT int ZL_FN(levels_scan)(zl_ctx* ctx, const float* l, const float* r, int64_t n,
                                  int32_t* peak_a, int32_t* peak_b, double* sumsq_a, double* sumsq_b);
+
+/* ---- n3: bounce ------------------------------------------------------ */
+/* The last render of one stereo port as the WAV file the reference's DiskWriter leaves on disk (lib/AudioLevels.cpp:35-119:
+ * WavAudioFormat::createWriterFor(stream, rate, 2 channels, 16 bit), AudioFormatWriter::writeFromFloatArrays): floats ->
+ * int32 by convertFloatsToInts (juce_AudioFormatWriter.cpp:64-79), top `bits` (16 or 24) kept
+ * (juce_AudioDataConverters.h:159,184), behind the writer's RIFF | JUNK | fmt | data header (juce_WavAudioFormat.cpp:1391-1500);
+ * converted on the device, one D2H copy of the packed samples.  bus < 0: the session's master mix (ZL_OUT_MASTER), else
+ * plane `which` (0 raw, 1 dry, 2 fx1, 3 fx2) of that bus.  out == NULL or cap too small: *size is set, ZL_ERR_STATE. */
+/* The same writer over HOST floats (r == NULL: a mono file): upload, convert on the device, header on the host. */
+ZL_EXPORT int ZL_FN(wav_encode)(zl_ctx* ctx, const float* l, const float* r, int64_t n, double rate, int32_t bits,
+                                void* out, uint64_t cap, uint64_t* size);
+ZL_EXPORT int ZL_FN(bounce_wav)(zl_ctx* ctx, int32_t session, int32_t bus, int32_t which, int32_t bits,
+                                void* out, uint64_t cap, uint64_t* size);
 
 /* ---- pinned host memory ------------------------------------------------------------- */
 /* Page-locked host buffers for callers that want full-rate PCIe transfers on zl_read_* / clip upload

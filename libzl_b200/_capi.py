@@ -60,6 +60,11 @@ class zl_levels(C.Structure):
                 ("rms_b", C.c_float), ("reserved", C.c_int32)]
 
 
+class zl_wav_format(C.Structure):
+    _fields_ = [("channels", C.c_int32), ("bits_per_sample", C.c_int32), ("is_float", C.c_int32), ("bytes_per_frame", C.c_int32),
+                ("sample_rate", C.c_double), ("frames", C.c_int64), ("data_offset", C.c_uint64), ("data_bytes", C.c_uint64)]
+
+
 _P = C.POINTER
 _ctx = C.c_void_p
 _f32p = _P(C.c_float)
@@ -75,6 +80,12 @@ SIGNATURES = {
     "sync": (C.c_int, [_ctx]),
     "clip_create_from_pcm": (C.c_int, [_ctx, _P(_f32p), C.c_int32, C.c_int64, C.c_double, _P(C.c_int32)]),
     "clip_create_from_device": (C.c_int, [_ctx, C.c_void_p, C.c_int32, C.c_int64, C.c_double, _P(C.c_int32)]),
+    "wav_probe": (C.c_int, [C.c_void_p, C.c_uint64, _P(zl_wav_format)]),
+    "clip_create_from_wav": (C.c_int, [_ctx, C.c_void_p, C.c_uint64, _P(C.c_int32)]),
+    "clip_create_from_wav_file": (C.c_int, [_ctx, C.c_char_p, _P(C.c_int32)]),
+    "clip_read_pcm": (C.c_int, [_ctx, C.c_int32, _P(_f32p), C.c_int32, C.c_int64]),
+    "wav_encode": (C.c_int, [_ctx, _f32p, _f32p, C.c_int64, C.c_double, C.c_int32, C.c_void_p, C.c_uint64, _P(C.c_uint64)]),
+    "bounce_wav": (C.c_int, [_ctx, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint64, _P(C.c_uint64)]),
     "clip_destroy": (C.c_int, [_ctx, C.c_int32]),
     "clip_params_default": (C.c_int, [_ctx, C.c_int32, _P(zl_clip_params)]),
     "clip_set_params": (C.c_int, [_ctx, C.c_int32, _P(zl_clip_params)]),

@@ -17,10 +17,10 @@
 namespace zl {
 cudaError_t launch_plan(RenderParams& P, cudaStream_t stream);
 #ifndef ZL_PLAN_CTAS_PER_SM
-#define ZL_PLAN_CTAS_PER_SM 2      // plan_kernel CTAs per SM beside a running gather (0 = whole grid)
+#define ZL_PLAN_CTAS_PER_SM 0      // plan_kernel CTAs per SM beside a running gather (0 = whole grid)
 #endif
 #ifndef ZL_WALK_CTAS_PER_SM
-#define ZL_WALK_CTAS_PER_SM 4      // walk_kernel one-warp CTAs per SM beside a running gather (0 = default grid)
+#define ZL_WALK_CTAS_PER_SM 0      // walk_kernel one-warp CTAs per SM beside a running gather (0 = default grid)
 #endif
 cudaError_t launch_gather(RenderParams& P, cudaStream_t stream, cudaEvent_t gatherBegin, cudaEvent_t gatherEnd);
 size_t render_scratch_bytes(int nVoices, int nframes, size_t off[5]);
@@ -34,6 +34,11 @@ cudaError_t launch_thumb_raster(const int8_t*, int, int, float, uint8_t*, cudaSt
 cudaError_t launch_passthrough(const zl_passthrough_params&, const float*, const float*, long long, float*, cudaStream_t);
 cudaError_t launch_levels(const float*, const float*, long long, int*, double*, cudaStream_t);
 cudaError_t launch_interleave(const float*, const float*, long long, long long, float*, cudaStream_t);
+cudaError_t launch_deinterleave(const float*, int, long long, float*, cudaStream_t);
+int wav_parse(const void* bytes, uint64_t n, zl_wav_format* f);
+cudaError_t launch_wav_decode(const unsigned char* raw, const zl_wav_format& f, int nchOut, long long padded, float* out, cudaStream_t st);
+cudaError_t launch_wav_encode(const float* l, const float* r, long long n, int bits, unsigned char* out, cudaStream_t st);
+int wav_header(unsigned char* h, int nch, double rate, int bits, uint64_t dataBytes);
 }  // namespace zl
 
 using namespace zl;
@@ -413,6 +418,73 @@ int zl_clip_create_from_device(zl_ctx* ctx, const void* d_interleaved, int32_t n
     return finish_clip(ctx, id, clip_id);
 }
 
+// ---- n1: WAV ingest (csrc/zl_wav.cu) ------------------------------------------------------------------------------
+int zl_wav_probe(const void* wav, uint64_t nbytes, zl_wav_format* out) { return wav_parse(wav, nbytes, out); }
+
+int zl_clip_create_from_wav(zl_ctx* ctx, const void* wav, uint64_t nbytes, int32_t* clip_id) {
+    BIND();
+    if (!wav || !clip_id) return invalid(ctx, "clip_create_from_wav: null argument");
+    zl_wav_format f;
+    if (wav_parse(wav, nbytes, &f) != ZL_OK) return invalid(ctx, "clip_create_from_wav: not a WAV image the reference's reader would open");
+    // SamplerSynthSound::loadSoundData: only sourceSampleRate > 0 && lengthInSamples > 0 makes a valid sound (lib/SamplerSynthSound.cpp:41-48)
+    if (f.frames < 1 || f.frames > 2147483647LL - 8) return invalid(ctx, "clip_create_from_wav: no samples (or more than an int of them)");
+    const int id = new_clip_slot(ctx);
+    if (id < 0) { ctx->err = "clip table full"; return ZL_ERR_STATE; }
+    ClipHost& c = ctx->clips[(size_t) id];
+    c.nch = std::min(2, (int) f.channels); c.length = (int) f.frames; c.rate = f.sample_rate; c.owned = true;
+    const long long padded = f.frames + kPadFrames;
+    const uint64_t need = (uint64_t) f.frames * (uint64_t) f.bytes_per_frame;           // what readSamples asks the stream for
+    const uint64_t have = f.data_offset < nbytes ? std::min(need, nbytes - f.data_offset) : 0;
+    const size_t rawCap = (size_t) ((need + 15) & ~uint64_t(15)) + 16;
+    unsigned char* d_raw = nullptr;
+    cudaError_t e = cudaMalloc((void**) &c.d_data, sizeof(float) * (size_t) padded * c.nch);
+    if (e != cudaSuccess) { ctx->clips.pop_back(); return fail(ctx, e, "cudaMalloc(clip)"); }
+    e = cudaMalloc((void**) &d_raw, rawCap);
+    if (e != cudaSuccess) { cudaFree(c.d_data); ctx->clips.pop_back(); return fail(ctx, e, "cudaMalloc(wav bytes)"); }
+    if (have < rawCap) e = cudaMemsetAsync(d_raw + have, 0, rawCap - have, ctx->stream);   // short file: the missing bytes read as zero
+    if (e == cudaSuccess && have)
+        e = cudaMemcpyAsync(d_raw, static_cast<const unsigned char*>(wav) + f.data_offset, (size_t) have, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = launch_wav_decode(d_raw, f, c.nch, padded, c.d_data, ctx->stream);
+    ctx->launches++;
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_raw);
+    if (e != cudaSuccess) { cudaFree(c.d_data); ctx->clips.pop_back(); return fail(ctx, e, "wav decode"); }
+    return finish_clip(ctx, id, clip_id);
+}
+
+int zl_clip_create_from_wav_file(zl_ctx* ctx, const char* path, int32_t* clip_id) {
+    if (!ctx || !path || !clip_id) return invalid(ctx, "clip_create_from_wav_file: null argument");
+    FILE* fp = fopen(path, "rb");
+    if (!fp) return invalid(ctx, "clip_create_from_wav_file: cannot open the file");
+    fseek(fp, 0, SEEK_END);
+    const long long n = ftell(fp);
+    fseek(fp, 0, SEEK_SET);
+    void* pinned = nullptr;                                    // page-locked: the H2D copy of the data chunk runs at PCIe rate
+    int rc = ZL_OK;
+    if (n <= 0 || cudaMallocHost(&pinned, (size_t) n) != cudaSuccess) rc = invalid(ctx, "clip_create_from_wav_file: empty file or no pinned memory");
+    else if (fread(pinned, 1, (size_t) n, fp) != (size_t) n) rc = invalid(ctx, "clip_create_from_wav_file: short read");
+    fclose(fp);
+    if (rc == ZL_OK) rc = zl_clip_create_from_wav(ctx, pinned, (uint64_t) n, clip_id);
+    if (pinned) cudaFreeHost(pinned);
+    return rc;
+}
+
+int zl_clip_read_pcm(zl_ctx* ctx, int32_t id, float* const* planar, int32_t nch, int64_t length) {
+    BIND();
+    ClipHost* c = find_clip(ctx, id);
+    if (!c || !planar || nch != c->nch || length != c->length) return invalid(ctx, "clip_read_pcm: unknown clip or shape mismatch");
+    float* d_planar = nullptr;
+    CK(cudaMalloc((void**) &d_planar, sizeof(float) * (size_t) length * nch));
+    cudaError_t e = launch_deinterleave(c->d_data, nch, length, d_planar, ctx->stream);
+    ctx->launches++;
+    for (int ch = 0; ch < nch && e == cudaSuccess; ++ch)
+        e = cudaMemcpyAsync(planar[ch], d_planar + (size_t) ch * length, sizeof(float) * (size_t) length, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_planar);
+    if (e != cudaSuccess) return fail(ctx, e, "clip_read_pcm");
+    return ZL_OK;
+}
+
 int zl_clip_destroy(zl_ctx* ctx, int32_t id) {
     BIND();
     ClipHost* c = find_clip(ctx, id);
@@ -761,6 +833,11 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
                     float t0 = 0.0f, t1 = 0.0f;
                     cudaEventElapsedTime(&t0, tlBase, v.front()); cudaEventElapsedTime(&t1, tlBase, v.back());
                     fprintf(f, "render %.3f..%.3f\n", t0, t1);
+                    if (&v == &all.back()) {
+                        std::vector<int32_t> wc(2 * (size_t) nblocks);
+                        cudaMemcpy(wc.data(), ctx->d_walkCount, sizeof(int32_t) * wc.size(), cudaMemcpyDeviceToHost);
+                        for (int b = 0; b < nblocks; ++b) fprintf(f, "walk queue blk %d: %d serial walkers, %d others of %zu voices\n", b, wc[2 * b], wc[2 * b + 1], NB * ctx->cfg.voices_per_bus);
+                    }
                     for (size_t i = 1; i + 4 < v.size(); i += 4) {
                         float t[4];
                         for (int k = 0; k < 4; ++k) cudaEventElapsedTime(&t[k], tlBase, v[i + k]);
@@ -805,6 +882,53 @@ int zl_read_master(zl_ctx* ctx, int32_t s, float* l, float* r, int64_t n) {
     if (rc != ZL_OK) return rc;
     CK(cudaStreamSynchronize(ctx->stream));
     return ZL_OK;
+}
+
+// ---- n3: bounce (csrc/zl_wav.cu) ----------------------------------------------------------------------------------
+// device rows l, r (r may be null) -> the writer's file image in host memory `out`
+static int wav_encode_rows(zl_ctx* ctx, const float* d_l, const float* d_r, int64_t N, double rate, int bits, void* out, uint64_t cap, uint64_t* size) {
+    const int nch = d_r ? 2 : 1;
+    const uint64_t dataBytes = (uint64_t) N * nch * (bits / 8);
+    const uint64_t total = 104 + dataBytes + (dataBytes & 1);
+    *size = total;
+    if (!out || cap < total) { ctx->err = "wav: output buffer too small (size returned)"; return ZL_ERR_STATE; }
+    unsigned char* d_pack = nullptr;
+    CK(cudaMalloc((void**) &d_pack, (size_t) dataBytes));
+    cudaError_t e = launch_wav_encode(d_l, d_r, N, bits, d_pack, ctx->stream);
+    ctx->launches++;
+    unsigned char* o = static_cast<unsigned char*>(out);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(o + 104, d_pack, (size_t) dataBytes, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_pack);
+    if (e != cudaSuccess) return fail(ctx, e, "wav encode");
+    wav_header(o, nch, rate, bits, dataBytes);
+    if (dataBytes & 1) o[104 + dataBytes] = 0;
+    return ZL_OK;
+}
+
+int zl_wav_encode(zl_ctx* ctx, const float* l, const float* r, int64_t n, double rate, int32_t bits, void* out, uint64_t cap, uint64_t* size) {
+    BIND();
+    if (!l || n < 1 || !(rate > 0) || (bits != 16 && bits != 24) || !size) return invalid(ctx, "wav_encode: bad argument");
+    float* d = nullptr;
+    CK(cudaMalloc((void**) &d, sizeof(float) * (size_t) n * 2));
+    cudaError_t e = cudaMemcpyAsync(d, l, sizeof(float) * (size_t) n, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess && r) e = cudaMemcpyAsync(d + n, r, sizeof(float) * (size_t) n, cudaMemcpyHostToDevice, ctx->stream);
+    int rc = e == cudaSuccess ? wav_encode_rows(ctx, d, r ? d + n : nullptr, n, rate, bits, out, cap, size) : fail(ctx, e, "wav_encode upload");
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    return rc;
+}
+
+int zl_bounce_wav(zl_ctx* ctx, int32_t s, int32_t b, int32_t which, int32_t bits, void* out, uint64_t cap, uint64_t* size) {
+    BIND();
+    if (!size || (bits != 16 && bits != 24) || s < 0 || s >= ctx->cfg.n_sessions || b >= ctx->cfg.buses_per_session || (b >= 0 && (which < 0 || which > 3)))
+        return invalid(ctx, "bounce_wav: bad argument");
+    const int64_t N = (int64_t) ctx->nblocks * ctx->nframes;
+    const float* l = nullptr;
+    if (b < 0) { if (ctx->d_master) l = ctx->d_master + (size_t) s * 2 * ctx->stride; }
+    else if (ctx->d_out[which]) l = ctx->d_out[which] + ((size_t) s * ctx->cfg.buses_per_session + b) * 2 * ctx->stride;
+    if (!l || N < 1) { ctx->err = "bounce_wav: nothing rendered yet or the plane is not enabled"; return ZL_ERR_STATE; }
+    return wav_encode_rows(ctx, l, l + ctx->stride, N, ctx->cfg.sample_rate, bits, out, cap, size);
 }
 
 int zl_read_master_all(zl_ctx* ctx, float* out, int64_t n) {

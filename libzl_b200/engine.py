@@ -4,6 +4,7 @@
 CUDA product.  tests/ pass the CPU oracle's library here to run *the same calls* on both sides.
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -94,6 +95,53 @@ class Engine:
         cid = C.c_int32(-1)
         self._chk(self.lib.clip_create_from_pcm(self.ctx, ptrs, nch, n, float(rate), C.byref(cid)), "clip_create_from_pcm")
         return cid.value
+
+    def wav_probe(self, wav):
+        """What the reference's WAV reader would find in the image (host-only chunk walk); raises on images it refuses."""
+        buf = np.frombuffer(bytes(wav), np.uint8) if not isinstance(wav, np.ndarray) else np.ascontiguousarray(wav, np.uint8)
+        f = K.zl_wav_format()
+        self._chk(self.lib.wav_probe(buf.ctypes.data_as(C.c_void_p), buf.size, C.byref(f)), "wav_probe")
+        return f
+
+    def add_clip_wav(self, wav):
+        """ClipAudioSource_new(path) with the file already in memory: bytes of a WAV file -> HBM clip, decoded on the device."""
+        buf = np.frombuffer(bytes(wav), np.uint8) if not isinstance(wav, np.ndarray) else np.ascontiguousarray(wav, np.uint8)
+        cid = C.c_int32(-1)
+        self._chk(self.lib.clip_create_from_wav(self.ctx, buf.ctypes.data_as(C.c_void_p), buf.size, C.byref(cid)), "clip_create_from_wav")
+        return cid.value
+
+    def add_clip_wav_file(self, path):
+        cid = C.c_int32(-1)
+        self._chk(self.lib.clip_create_from_wav_file(self.ctx, os.fsencode(path), C.byref(cid)), "clip_create_from_wav_file")
+        return cid.value
+
+    def clip_pcm(self, clip, nch, frames):
+        """The clip's sample data as SamplerSynthSound holds it: float32 [nch, frames]."""
+        out = np.zeros((nch, frames), np.float32)
+        ptrs = (C.POINTER(C.c_float) * nch)(*[_fp(out[i]) for i in range(nch)])
+        self._chk(self.lib.clip_read_pcm(self.ctx, clip, ptrs, nch, frames), "clip_read_pcm")
+        return out
+
+    def wav_encode(self, left, right=None, rate=48000.0, bits=16):
+        """Host floats -> the bytes of the WAV file the reference's writer would produce (16 or 24 bit)."""
+        left = np.ascontiguousarray(left, np.float32)
+        right = None if right is None else np.ascontiguousarray(right, np.float32)
+        size = C.c_uint64(0)
+        cap = 104 + left.size * (2 if right is not None else 1) * (bits // 8) + 1
+        out = np.zeros(cap, np.uint8)
+        self._chk(self.lib.wav_encode(self.ctx, _fp(left), _fp(right) if right is not None else None, left.size, float(rate), bits,
+                                      out.ctypes.data_as(C.c_void_p), cap, C.byref(size)), "wav_encode")
+        return out[:size.value].copy()
+
+    def bounce_wav(self, session=0, bus=-1, which=0, bits=16):
+        """The last render of one stereo port (bus < 0: the session's master) as a WAV file image."""
+        size = C.c_uint64(0)
+        self.lib.bounce_wav(self.ctx, session, bus, which, bits, None, 0, C.byref(size))
+        if size.value == 0:
+            self._chk(K.ZL_ERR_STATE, "bounce_wav")
+        out = np.zeros(size.value, np.uint8)
+        self._chk(self.lib.bounce_wav(self.ctx, session, bus, which, bits, out.ctypes.data_as(C.c_void_p), out.size, C.byref(size)), "bounce_wav")
+        return out
 
     def add_clip_device(self, dptr, nch, frames, rate=48000.0):
         cid = C.c_int32(-1)

@@ -58,4 +58,8 @@ def load_juceref():
     d.ref_wav_roundtrip.restype = C.c_longlong
     d.ref_wav_roundtrip.argtypes = [C.POINTER(f32p), C.c_int, C.c_longlong, C.c_double, C.c_int, C.POINTER(C.c_ubyte),
                                     C.c_longlong, C.POINTER(C.c_longlong), C.POINTER(f32p)]
+    if hasattr(d, "ref_wav_read"):
+        d.ref_wav_read.restype = C.c_longlong
+        d.ref_wav_read.argtypes = [C.POINTER(C.c_ubyte), C.c_longlong, C.c_longlong, C.POINTER(f32p), C.POINTER(C.c_double),
+                                   C.POINTER(C.c_longlong)]
     return d

@@ -7,6 +7,7 @@
 #include <juce_audio_basics/juce_audio_basics.h>
 #include <juce_audio_formats/juce_audio_formats.h>
 
+#include <algorithm>
 #include <cstring>
 #include <memory>
 
@@ -125,6 +126,25 @@ long long ref_wav_roundtrip(const float* const* planar, int nch, long long len, 
     if (!r) return -2;
     r->read(back, nch, 0, (int) len);
     return r->lengthInSamples;
+}
+
+// Any WAV image through the reference's reader the way SamplerSynthSound::loadSoundData does it
+// (lib/SamplerSynthSound.cpp:40-46): createReaderFor, AudioBuffer<float>(min(2, numChannels), length), read(&buffer, 0,
+// length, 0, true, true).  info = {numChannels, bitsPerSample, usesFloatingPointData, lengthInSamples}; back = 2 rows of
+// cap floats.  Returns the frames copied out, -2 when the reader refuses the image.
+long long ref_wav_read(const unsigned char* wav, long long size, long long cap, float* const* back, double* rate, long long* info) {
+    juce::WavAudioFormat fmt;
+    std::unique_ptr<juce::AudioFormatReader> r(fmt.createReaderFor(new juce::MemoryInputStream(wav, (size_t) size, false), true));
+    if (!r) return -2;
+    if (rate) *rate = r->sampleRate;
+    if (info) { info[0] = r->numChannels; info[1] = r->bitsPerSample; info[2] = r->usesFloatingPointData ? 1 : 0; info[3] = r->lengthInSamples; }
+    if (!(r->sampleRate > 0 && r->lengthInSamples > 0)) return 0;
+    const int length = (int) r->lengthInSamples;
+    juce::AudioBuffer<float> data(juce::jmin(2, (int) r->numChannels), length);
+    r->read(&data, 0, length, 0, true, true);
+    const long long n = std::min<long long>(cap, length);
+    for (int ch = 0; ch < data.getNumChannels(); ++ch) std::memcpy(back[ch], data.getReadPointer(ch), (size_t) n * sizeof(float));
+    return n;
 }
 
 } // extern "C"

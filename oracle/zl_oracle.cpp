@@ -27,6 +27,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <limits>
 #include <string>
 #include <thread>
 #include <vector>
@@ -1006,6 +1007,189 @@ int zlo_levels_scan(zl_ctx*, const float* l, const float* r, int64_t n, int32_t*
     if (sa) *sa = sumSquares(l, (size_t) n);
     if (sb) *sb = sumSquares(r, (size_t) n);
     return ZL_OK;
+}
+
+// ---- rows n1 / n3: WAV in, WAV out — restated from the reference's reader and writer ----------------
+// Reader: juce::WavAudioFormatReader ctor (juce_WavAudioFormat.cpp:933-1190) walks the chunks; readSamples/copySampleData
+// (:1195-1245) left-justify into int32 (juce_AudioDataConverters.h:134,159,184,209); AudioFormatReader::read(AudioBuffer*)
+// (juce_AudioFormatReader.cpp:139-183) scales with (float) i * (1.0f / 0x7fffffff); SamplerSynthSound keeps min(2, nch)
+// channels (lib/SamplerSynthSound.cpp:40-46).  PINNED: tests/golden wav*_bytes / wav*_back come from the reference's own
+// compiled reader and writer (oracle/ref/juce_ref.cpp ref_wav_roundtrip / ref_wav_read).
+namespace {
+struct WavIn {
+    const unsigned char* p; uint64_t n; uint64_t at = 0;
+    int byteAt(uint64_t i) const { return i < n ? p[i] : 0; }                  // InputStream reads past the end give zeros
+    int64_t readLE(int bytes) { uint64_t v = 0; for (int i = 0; i < bytes; ++i) v |= (uint64_t) byteAt(at + (uint64_t) i) << (8 * i); at += (uint64_t) bytes; return (int64_t) v; }
+    bool is(const char* fourcc, uint32_t v) const { return v == ((uint32_t) (unsigned char) fourcc[0] | ((uint32_t) (unsigned char) fourcc[1] << 8) | ((uint32_t) (unsigned char) fourcc[2] << 16) | ((uint32_t) (unsigned char) fourcc[3] << 24)); }
+};
+}  // namespace
+int zlo_wav_probe(const void* wav, uint64_t nbytes, zl_wav_format* out) {
+    if (!wav || !out) return ZL_ERR_INVALID;
+    memset(out, 0, sizeof *out);
+    WavIn in{static_cast<const unsigned char*>(wav), nbytes};
+    uint64_t riffEnd = 0, dataLength = 0;
+    bool isRF64 = false;
+    const uint32_t first = (uint32_t) in.readLE(4);
+    if (in.is("RF64", first)) { in.at += 4; isRF64 = true; }
+    else if (in.is("RIFF", first)) { const uint64_t len = (uint32_t) in.readLE(4); riffEnd = len + in.at; }
+    else return ZL_ERR_INVALID;
+    const uint64_t startOfRIFFChunk = in.at;
+    if (!in.is("WAVE", (uint32_t) in.readLE(4))) return ZL_ERR_INVALID;
+    if (isRF64 && in.is("ds64", (uint32_t) in.readLE(4))) {
+        const uint32_t length = (uint32_t) in.readLE(4);
+        if (length < 28) return ZL_ERR_INVALID;
+        const uint64_t chunkEnd = in.at + length + (length & 1);
+        riffEnd = (uint64_t) in.readLE(8) + startOfRIFFChunk;
+        dataLength = (uint64_t) in.readLE(8);
+        in.at = chunkEnd;
+    }
+    unsigned numChannels = 0, bitsPerSample = 0;
+    int bytesPerFrame = 0;
+    double sampleRate = 0;
+    bool usesFloat = false;
+    int64_t lengthInSamples = 0;
+    while (in.at < riffEnd && in.at < in.n) {
+        const uint32_t chunkType = (uint32_t) in.readLE(4);
+        const uint32_t length = (uint32_t) in.readLE(4);
+        uint64_t chunkEnd = in.at + length + (length & 1);
+        if (in.is("fmt ", chunkType)) {
+            const unsigned format = (unsigned short) in.readLE(2);
+            numChannels = (unsigned) (int) (short) in.readLE(2);
+            sampleRate = (double) (int) in.readLE(4);
+            const int bytesPerSec = (int) in.readLE(4);
+            in.at += 2;
+            bitsPerSample = (unsigned) (int) (short) in.readLE(2);
+            if (bitsPerSample > 64 && (int) sampleRate != 0) {
+                bytesPerFrame = bytesPerSec / (int) sampleRate;
+                if (numChannels != 0) bitsPerSample = 8 * (unsigned) bytesPerFrame / numChannels;
+            } else bytesPerFrame = (int) (numChannels * bitsPerSample / 8);
+            usesFloat = false;
+            if (format == 3) usesFloat = true;
+            else if (format == 0xfffe) {
+                if (length < 40) bytesPerFrame = 0;
+                else {
+                    in.at += 4;                                                  // size and bitsPerSample
+                    in.at += 4;                                                  // channel mask
+                    unsigned char guid[16];
+                    for (int i = 0; i < 16; ++i) guid[i] = (unsigned char) in.readLE(1);
+                    static const unsigned char pcm[16] = {1, 0, 0, 0, 0, 0, 0x10, 0, 0x80, 0, 0, 0xaa, 0, 0x38, 0x9b, 0x71};
+                    static const unsigned char flt[16] = {3, 0, 0, 0, 0, 0, 0x10, 0, 0x80, 0, 0, 0xaa, 0, 0x38, 0x9b, 0x71};
+                    static const unsigned char amb[16] = {1, 0, 0, 0, 0x21, 0x07, 0xd3, 0x11, 0x86, 0x44, 0xc8, 0xc1, 0xca, 0, 0, 0};
+                    if (!memcmp(guid, flt, 16)) usesFloat = true;
+                    else if (memcmp(guid, pcm, 16) && memcmp(guid, amb, 16)) bytesPerFrame = 0;
+                }
+            } else if (format == 0x674f || format == 0x6750 || format == 0x6751 || format == 0x676f || format == 0x6770 || format == 0x6771) return ZL_ERR_INVALID;
+            else if (format != 1) bytesPerFrame = 0;
+        } else if (in.is("data", chunkType)) {
+            if (isRF64) { if (dataLength > 0) chunkEnd = in.at + dataLength + (dataLength & 1); }
+            else dataLength = length;
+            out->data_offset = in.at; out->data_bytes = dataLength;
+            lengthInSamples = bytesPerFrame > 0 ? (int64_t) (dataLength / (uint64_t) bytesPerFrame) : 0;
+        } else {
+            static const char* const known[] = {"bext", "smpl", "inst", "INST", "cue ", "axml", "LIST", "acid", "Trkn"};
+            bool isKnown = false;
+            for (const char* k : known) isKnown = isKnown || in.is(k, chunkType);
+            if (!isKnown && chunkEnd <= in.at) break;
+        }
+        in.at = chunkEnd;
+    }
+    out->channels = (int32_t) numChannels; out->bits_per_sample = (int32_t) bitsPerSample; out->is_float = usesFloat ? 1 : 0;
+    out->bytes_per_frame = bytesPerFrame; out->sample_rate = sampleRate; out->frames = lengthInSamples;
+    // WavAudioFormat::createReaderFor :1718-1731, then the formats copySampleData knows :1232-1245
+    if (!(sampleRate > 0) || (int) numChannels <= 0 || bytesPerFrame <= 0 || bitsPerSample > 32) return ZL_ERR_INVALID;
+    if (!(bitsPerSample == 8 || bitsPerSample == 16 || bitsPerSample == 24 || bitsPerSample == 32) || (usesFloat && bitsPerSample != 32)) return ZL_ERR_INVALID;
+    if ((int) (numChannels * (bitsPerSample / 8)) > bytesPerFrame) return ZL_ERR_INVALID;
+    return ZL_OK;
+}
+int zlo_clip_create_from_wav(zl_ctx* ctx, const void* wav, uint64_t nbytes, int32_t* clip_id) {
+    zl_wav_format f;
+    if (!ctx || !wav || !clip_id || zlo_wav_probe(wav, nbytes, &f) != ZL_OK) return ZL_ERR_INVALID;
+    if (f.frames < 1 || f.frames > 2147483647LL - 8) return ZL_ERR_INVALID;
+    const int keep = std::min(2, (int) f.channels), bps = f.bits_per_sample / 8;
+    std::vector<std::vector<float>> pcm((size_t) keep, std::vector<float>((size_t) f.frames));
+    WavIn in{static_cast<const unsigned char*>(wav), nbytes};
+    const float scale = 1.0f / static_cast<float>(0x7fffffff);                  // juce_AudioFormatReader.cpp:41
+    for (int64_t fr = 0; fr < f.frames; ++fr)
+        for (int ch = 0; ch < keep; ++ch) {
+            const uint64_t q = f.data_offset + (uint64_t) fr * (uint64_t) f.bytes_per_frame + (uint64_t) (ch * bps);
+            uint32_t raw = 0;
+            for (int i = 0; i < bps; ++i) raw |= (uint32_t) in.byteAt(q + (uint64_t) i) << (8 * i);
+            float v;
+            if (f.is_float) memcpy(&v, &raw, 4);
+            else {
+                int32_t fixed;
+                if (bps == 1) fixed = (int32_t) ((raw - 128u) << 24);           // UInt8::getAsInt32LE
+                else if (bps == 2) fixed = (int32_t) (raw << 16);               // Int16
+                else if (bps == 3) fixed = (int32_t) (raw << 8);                // Int24
+                else fixed = (int32_t) raw;
+                v = (float) fixed * scale;
+            }
+            pcm[(size_t) ch][(size_t) fr] = v;
+        }
+    const float* planar[2] = {pcm[0].data(), keep > 1 ? pcm[1].data() : nullptr};
+    return zlo_clip_create_from_pcm(ctx, planar, keep, f.frames, f.sample_rate, clip_id);
+}
+int zlo_clip_create_from_wav_file(zl_ctx* ctx, const char* path, int32_t* clip_id) {
+    if (!ctx || !path || !clip_id) return ZL_ERR_INVALID;
+    FILE* fp = fopen(path, "rb");
+    if (!fp) return ZL_ERR_INVALID;
+    std::vector<unsigned char> bytes;
+    unsigned char buf[65536];
+    size_t got;
+    while ((got = fread(buf, 1, sizeof buf, fp)) > 0) bytes.insert(bytes.end(), buf, buf + got);
+    fclose(fp);
+    return zlo_clip_create_from_wav(ctx, bytes.data(), bytes.size(), clip_id);
+}
+int zlo_clip_read_pcm(zl_ctx* ctx, int32_t id, float* const* planar, int32_t nch, int64_t length) {
+    Clip* c = ctx ? findClip(ctx, id) : nullptr;
+    if (!c || !planar || nch != c->nch || length != c->length) return ZL_ERR_INVALID;
+    for (int ch = 0; ch < nch; ++ch) memcpy(planar[ch], c->data[ch].data(), (size_t) length * 4);
+    return ZL_OK;
+}
+// Writer: AudioFormatWriter::writeFromFloatArrays -> convertFloatsToInts (juce_AudioFormatWriter.cpp:64-79,160-185), then
+// WavAudioFormatWriter::write keeps the top bits (juce_WavAudioFormat.cpp:1336-1369) behind writeHeader's layout (:1391-1500).
+static int wavEncode(const float* l, const float* r, size_t N, double rate, int bits, void* out, uint64_t cap, uint64_t* size) {
+    const int nch = r ? 2 : 1, bytesPerSample = bits / 8, bytesPerFrame = nch * bytesPerSample;
+    const uint64_t audioDataSize = (uint64_t) bytesPerFrame * N;
+    const uint64_t total = 104 + audioDataSize + (audioDataSize & 1);
+    *size = total;
+    if (!out || cap < total) return ZL_ERR_STATE;
+    unsigned char* o = static_cast<unsigned char*>(out);
+    size_t at = 0;
+    auto put = [&](uint64_t v, int bytes) { for (int i = 0; i < bytes; ++i) o[at++] = (unsigned char) (v >> (8 * i)); };
+    auto fourcc = [&](const char* t) { memcpy(o + at, t, 4); at += 4; };
+    int64_t riffChunkSize = (int64_t) (4 + 8 + 40 + 8 + audioDataSize + (audioDataSize & 1) + (8 + 28));
+    riffChunkSize += (riffChunkSize & 1);
+    fourcc("RIFF"); put((uint64_t) riffChunkSize, 4); fourcc("WAVE");
+    fourcc("JUNK"); put(28 + 24, 4); for (int i = 0; i < 28 + 24; ++i) o[at++] = 0;
+    fourcc("fmt "); put(16, 4); put(1, 2); put((uint64_t) nch, 2); put((uint64_t) (int) rate, 4);
+    put((uint64_t) (int) ((double) bytesPerFrame * rate), 4); put((uint64_t) bytesPerFrame, 2); put((uint64_t) bits, 2);
+    fourcc("data"); put(audioDataSize, 4);
+    for (size_t j = 0; j < N; ++j)
+        for (int ch = 0; ch < nch; ++ch) {
+            const double samp = (ch ? r : l)[j];
+            int fixed;
+            if (samp <= -1.0) fixed = std::numeric_limits<int>::min();
+            else if (samp >= 1.0) fixed = std::numeric_limits<int>::max();
+            else fixed = roundToInt(std::numeric_limits<int>::max() * samp);
+            put((uint64_t) (uint32_t) (fixed >> (32 - bits)), bytesPerSample);
+        }
+    if (audioDataSize & 1) o[at++] = 0;
+    return ZL_OK;
+}
+int zlo_wav_encode(zl_ctx* ctx, const float* l, const float* r, int64_t n, double rate, int32_t bits, void* out, uint64_t cap, uint64_t* size) {
+    if (!ctx || !l || n < 1 || !(rate > 0) || (bits != 16 && bits != 24) || !size) return ZL_ERR_INVALID;
+    return wavEncode(l, r, (size_t) n, rate, bits, out, cap, size);
+}
+int zlo_bounce_wav(zl_ctx* ctx, int32_t s, int32_t b, int32_t which, int32_t bits, void* out, uint64_t cap, uint64_t* size) {
+    if (!ctx || !size || (bits != 16 && bits != 24) || s < 0 || s >= ctx->cfg.n_sessions || b >= ctx->cfg.buses_per_session || (b >= 0 && (which < 0 || which > 3)))
+        return ZL_ERR_INVALID;
+    const size_t N = (size_t) ctx->nblocks * (size_t) ctx->nframes;
+    const float* l = nullptr;
+    if (b < 0) { if ((ctx->cfg.outputs & ZL_OUT_MASTER) && !ctx->master.empty()) l = ctx->master.data() + (size_t) s * 2 * N; }
+    else if ((ctx->cfg.outputs & (ZL_OUT_RAW << which)) && !ctx->bus[which].empty()) l = ctx->bus[which].data() + ((size_t) s * (size_t) ctx->cfg.buses_per_session + (size_t) b) * 2 * N;
+    if (!l || N < 1) return ZL_ERR_STATE;
+    return wavEncode(l, l + N, N, ctx->cfg.sample_rate, bits, out, cap, size);
 }
 
 int zlo_host_alloc(void** p, size_t bytes) { if (!p) return ZL_ERR_INVALID; *p = malloc(bytes ? bytes : 1); return *p ? ZL_OK : ZL_ERR_NOMEM; }

@@ -107,6 +107,82 @@ def main():
         out[f"wav{bits}_back"] = back
     out["wav_src"] = wpcm
 
+    # --- row n1: WAV images through the reference's reader the way SamplerSynthSound::loadSoundData reads them
+    # (ref_wav_read); the first four are written by the reference's own writer, the rest are hand-built to reach the
+    # reader's other branches (int32 PCM, WAVE_FORMAT_EXTENSIBLE, chunks before data, a data chunk longer than the file,
+    # odd-sized chunks, float specials).  Images the reader refuses are kept too (wavbad_*).
+    import struct
+
+    def juce_written(pcm, bits):
+        nch, n = pcm.shape
+        back = np.zeros((nch, n), np.float32)
+        bp = (f32p * nch)(*[fp(back[i]) for i in range(nch)])
+        cap = 1 << 18
+        wav = np.zeros(cap, np.uint8)
+        size = C.c_longlong()
+        got = ref.ref_wav_roundtrip(planar_ptrs(pcm), nch, n, 44100.0, bits, wav.ctypes.data_as(C.POINTER(C.c_ubyte)), cap, C.byref(size), bp)
+        assert got == n, got
+        return wav[:size.value].copy()
+
+    def riff(chunks):
+        body = b"WAVE" + b"".join(t + struct.pack("<I", len(d) if ln is None else ln) + d + (b"\0" if len(d) & 1 else b"") for t, d, ln in chunks)
+        return np.frombuffer(b"RIFF" + struct.pack("<I", len(body)) + body, np.uint8).copy()
+
+    def fmt_chunk(tag, nch, rate, bits, ext_sub=None):
+        bpf = nch * bits // 8
+        d = struct.pack("<HHIIHH", tag, nch, rate, bpf * rate, bpf, bits)
+        if ext_sub is not None:
+            d += struct.pack("<HHI", 22, bits, 0) + ext_sub
+        return d
+
+    pcm_guid = bytes([1, 0, 0, 0, 0, 0, 0x10, 0, 0x80, 0, 0, 0xaa, 0, 0x38, 0x9b, 0x71])
+    flt_guid = bytes([3]) + pcm_guid[1:]
+    i32 = rng.integers(-2**31, 2**31, (700, 2), dtype=np.int64).astype(np.int32)
+    i32[0] = (-2**31, 2**31 - 1); i32[1] = (1, -1); i32[2] = (0x7fffff7f, 0x01000001); i32[3] = (-0x7fffff81, 0x00ffffff)
+    s16 = rng.integers(-32768, 32768, (1000, 2)).astype(np.int16)
+    s16[0] = (-32768, 32767)
+    f32 = rng.uniform(-1.5, 1.5, 300).astype(np.float32)
+    f32[:8] = np.array([np.nan, np.inf, -np.inf, -0.0, 1e-42, -1e-45, 3.4e38, 1.0], np.float32)
+    s24 = rng.integers(0, 256, 3 * 501).astype(np.uint8)
+    s24[:6] = (0, 0, 0x80, 0xff, 0xff, 0x7f)
+    images = [
+        juce_written(rng.uniform(-1, 1, (2, 900)).astype(np.float32), 8),
+        juce_written(rng.uniform(-1, 1, (1, 777)).astype(np.float32), 16),
+        juce_written(rng.uniform(-1, 1, (3, 640)).astype(np.float32), 24),
+        juce_written(rng.uniform(-2, 2, (2, 512)).astype(np.float32), -32),
+        riff([(b"fmt ", fmt_chunk(1, 2, 48000, 32), None), (b"data", i32.tobytes(), None)]),
+        riff([(b"fmt ", fmt_chunk(1, 2, 22050, 16), None), (b"LIST", b"INFOISFT\x05\0\0\0zl_b\0\0", None),
+              (b"data", s16[:601].tobytes()[:-2], 4000)]),                      # promises 1000 frames, holds 600.5
+        riff([(b"fmt ", fmt_chunk(0xfffe, 1, 96000, 32, flt_guid), None), (b"data", f32.tobytes(), None)]),
+        riff([(b"fmt ", fmt_chunk(0xfffe, 1, 48000, 24, pcm_guid), None), (b"data", s24.tobytes(), None), (b"junk", b"abc", None)]),
+        riff([(b"JUNK", bytes(28), None), (b"fmt ", fmt_chunk(3, 2, 48000, 32), None), (b"data", f32[:298].tobytes(), None)]),
+    ]
+    out["wavc_count"] = np.array([len(images)], np.int32)
+    for i, img in enumerate(images):
+        back = np.zeros((2, 4096), np.float32)
+        bp = (f32p * 2)(fp(back[0]), fp(back[1]))
+        rate = C.c_double()
+        info = (C.c_longlong * 4)()
+        n = ref.ref_wav_read(img.ctypes.data_as(C.POINTER(C.c_ubyte)), len(img), 4096, bp, C.byref(rate), info)
+        assert n > 0, (i, n)
+        keep = min(2, info[0])
+        out[f"wavc_{i}_bytes"] = img
+        out[f"wavc_{i}_back"] = back[:keep, :n].copy()
+        out[f"wavc_{i}_info"] = np.array([info[0], info[1], info[2], info[3], rate.value], np.float64)
+    bad = [
+        riff([(b"fmt ", fmt_chunk(2, 2, 48000, 4), None), (b"data", bytes(64), None)]),       # ADPCM
+        riff([(b"fmt ", fmt_chunk(3, 1, 48000, 64), None), (b"data", bytes(64), None)]),      # float64
+        np.frombuffer(b"RIFX" + bytes(60), np.uint8).copy(),
+        riff([(b"data", bytes(64), None)]),                                                    # no fmt chunk
+    ]
+    out["wavbad_count"] = np.array([len(bad)], np.int32)
+    for i, img in enumerate(bad):
+        back = np.zeros((2, 64), np.float32)
+        bp = (f32p * 2)(fp(back[0]), fp(back[1]))
+        n = ref.ref_wav_read(img.ctypes.data_as(C.POINTER(C.c_ubyte)), len(img), 64, bp, None, None)
+        assert n == -2, (i, n)
+        out[f"wavbad_{i}_bytes"] = img
+
     path = os.path.join(HERE, "juce_golden.npz")
     np.savez_compressed(path, **out)
     print("wrote", path, os.path.getsize(path), "bytes,", len(out), "arrays")
