@@ -456,6 +456,47 @@ def thumbnail_probe(local_rank, peak):
             "pixel_checksum": int(px.astype(np.int64).sum()), "mask_on": int(mask.sum()) if mask is not None else None}
 
 
+def wav_io_probe(local_rank):
+    """Rows n1 / n3: a 16-bit stereo WAV image in pinned host memory -> HBM clip (H2D of the file bytes + device decode),
+    and host floats -> 16-bit WAV image (H2D + device convert + D2H).  End-to-end times through the C ABI; the kernels'
+    own durations are in profiles/ (ncu launch list)."""
+    import libzl_b200
+    from libzl_b200 import _capi as K
+    from libzl_b200.engine import Engine
+    frames = 1 << 25                                          # 128 MB of file, 256 MB of clip
+    e = Engine(lib=libzl_b200.load(), n_sessions=1, buses_per_session=1, voices_per_bus=1, max_clips=8, outputs=K.ZL_OUT_RAW, device=local_rank)
+    nbytes = 44 + frames * 4
+    hp = C.c_void_p()
+    e._chk(e.lib.host_alloc(C.byref(hp), nbytes), "host_alloc")
+    img = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(nbytes,))
+    import struct
+    img[:44] = np.frombuffer(b"RIFF" + struct.pack("<I", nbytes - 8) + b"WAVEfmt " + struct.pack("<IHHIIHH", 16, 1, 2, 48000, 192000, 4, 16)
+                             + b"data" + struct.pack("<I", frames * 4), np.uint8)
+    rng = np.random.default_rng(11)
+    img[44:] = rng.integers(0, 256, frames * 4, dtype=np.uint8)
+    ms = []
+    for _ in range(4):
+        cid = C.c_int32(-1)
+        t0 = time.perf_counter()
+        e._chk(e.lib.clip_create_from_wav(e.ctx, hp, nbytes, C.byref(cid)), "clip_create_from_wav")
+        ms.append((time.perf_counter() - t0) * 1e3)
+        e._chk(e.lib.clip_destroy(e.ctx, cid.value), "clip_destroy")
+    ingest = min(ms[1:])
+    n = 1 << 24
+    x = rng.uniform(-1, 1, (2, n)).astype(np.float32)
+    t_enc = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        out = e.wav_encode(x[0], x[1], rate=48000.0, bits=16)
+        t_enc.append((time.perf_counter() - t0) * 1e3)
+    e.lib.host_free(hp)
+    e.close()
+    return {"what": "n1: 2^25-frame 16-bit stereo WAV image (pinned host) -> HBM clip, zl_clip_create_from_wav incl. allocation, H2D and device decode; "
+                    "n3: 2^24 stereo frames of host floats -> 16-bit WAV image, zl_wav_encode incl. H2D, device convert, D2H",
+            "ingest_ms": round(ingest, 3), "ingest_file_GBps": nbytes / (ingest * 1e-3) / 1e9,
+            "encode_ms": round(min(t_enc[1:]), 3), "encode_checksum": int(out[104:104 + 4096].astype(np.int64).sum())}
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -539,6 +580,10 @@ def main():
                 line["thumbnail"] = thumbnail_probe(local_rank, peak)
             except Exception as ex:   # noqa: BLE001
                 line["thumbnail"] = {"error": str(ex)}
+            try:
+                line["wav_io"] = wav_io_probe(local_rank)
+            except Exception as ex:   # noqa: BLE001
+                line["wav_io"] = {"error": str(ex)}
         if world == 1 and not args.no_cpu_baseline:
             sessions = cpu_sample_size(args)
             cvf, cdt, th = run_cpu(args, sessions, 2, 1)

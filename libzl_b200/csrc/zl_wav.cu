@@ -149,8 +149,54 @@ __global__ void __launch_bounds__(256) wav_decode_kernel(const unsigned char* __
     }
 }
 
+// The layouts nearly every file has - 16-bit or 32-bit samples, all of the file's channels kept - are one flat array of
+// samples: thread = 16 input bytes (8 x s16 or 4 x 32-bit) -> 8 or 4 floats, vector loads and stores, no staging.
+// total = samples to decode, outTotal = floats to write (the rest is the zero padding).
+template <int FMT>
+__global__ void __launch_bounds__(256) wav_decode_flat_kernel(const uint4* __restrict__ raw, long long total, long long outTotal, float* __restrict__ out) {
+    constexpr int PER = FMT == kS16 ? 8 : 4;
+    const long long v = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    const long long k0 = v * PER;
+    if (k0 >= outTotal) return;
+    float f[PER];
+    if (k0 < total) {                                      // raw is readable (zero-filled) to the end of this vector
+        const uint4 w = __ldcs(raw + v);
+        const uint32_t u[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (FMT == kS16) {
+                f[2 * i] = __fmul_rn(__int2float_rn((int32_t) (u[i] << 16)), 4.656612873077393e-10f);
+                f[2 * i + 1] = __fmul_rn(__int2float_rn((int32_t) (u[i] & 0xffff0000u)), 4.656612873077393e-10f);
+            } else if (FMT == kS32) f[i] = __fmul_rn(__int2float_rn((int32_t) u[i]), 4.656612873077393e-10f);
+            else f[i] = __uint_as_float(u[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < PER; ++i) if (k0 + i >= total) f[i] = 0.0f;
+    } else {
+#pragma unroll
+        for (int i = 0; i < PER; ++i) f[i] = 0.0f;
+    }
+    if (k0 + PER <= outTotal) {
+#pragma unroll
+        for (int i = 0; i < PER; i += 4) __stcs(reinterpret_cast<float4*>(out + k0 + i), make_float4(f[i], f[i + 1], f[i + 2], f[i + 3]));
+    } else {
+        for (int i = 0; i < PER && k0 + i < outTotal; ++i) out[k0 + i] = f[i];
+    }
+}
+
 cudaError_t launch_wav_decode(const unsigned char* raw, const zl_wav_format& f, int nchOut, long long padded, float* out, cudaStream_t st) {
     const int fmt = f.is_float ? kF32 : (f.bits_per_sample == 8 ? kU8 : (f.bits_per_sample == 16 ? kS16 : (f.bits_per_sample == 24 ? kS24 : kS32)));
+    const int bps = f.bits_per_sample / 8;
+    if ((fmt == kS16 || fmt == kS32 || fmt == kF32) && f.bytes_per_frame == nchOut * bps) {
+        const long long total = (long long) f.frames * nchOut, outTotal = padded * nchOut;
+        const int per = fmt == kS16 ? 8 : 4;
+        const unsigned g = (unsigned) (((outTotal + per - 1) / per + 255) / 256);
+        const uint4* r4 = reinterpret_cast<const uint4*>(raw);
+        if (fmt == kS16) wav_decode_flat_kernel<kS16><<<g, 256, 0, st>>>(r4, total, outTotal, out);
+        else if (fmt == kS32) wav_decode_flat_kernel<kS32><<<g, 256, 0, st>>>(r4, total, outTotal, out);
+        else wav_decode_flat_kernel<kF32><<<g, 256, 0, st>>>(r4, total, outTotal, out);
+        return cudaGetLastError();
+    }
     int framesPerCta = 40960 / f.bytes_per_frame;
     if (framesPerCta > 2048) framesPerCta = 2048;
     if (framesPerCta < 1) return cudaErrorInvalidValue;                          // > 40 KB per frame: not a sampler clip
@@ -208,8 +254,45 @@ __global__ void __launch_bounds__(256) wav_encode_kernel(const float* __restrict
     }
 }
 
+// Stereo, rows 16-byte aligned: thread = 4 frames -> 16 (16-bit) or 24 (24-bit) packed bytes, vector loads and stores.
+template <int BYTES>
+__global__ void __launch_bounds__(256) wav_encode4_kernel(const float4* __restrict__ l, const float4* __restrict__ r, long long n4, unsigned char* __restrict__ out) {
+    const long long j = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n4) return;
+    const float4 a = __ldcs(l + j), b = __ldcs(r + j);
+    const int32_t v[8] = {float_to_fixed(a.x), float_to_fixed(b.x), float_to_fixed(a.y), float_to_fixed(b.y),
+                          float_to_fixed(a.z), float_to_fixed(b.z), float_to_fixed(a.w), float_to_fixed(b.w)};
+    if (BYTES == 2) {
+        uint4 w;
+        w.x = ((uint32_t) v[0] >> 16) | ((uint32_t) v[1] & 0xffff0000u); w.y = ((uint32_t) v[2] >> 16) | ((uint32_t) v[3] & 0xffff0000u);
+        w.z = ((uint32_t) v[4] >> 16) | ((uint32_t) v[5] & 0xffff0000u); w.w = ((uint32_t) v[6] >> 16) | ((uint32_t) v[7] & 0xffff0000u);
+        __stcs(reinterpret_cast<uint4*>(out) + j, w);
+    } else {
+        uint32_t t[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t[i] = (uint32_t) v[i] >> 8;                        // 24 significant bits, little endian
+        uint2 w0, w1, w2;
+        w0.x = t[0] | (t[1] << 24); w0.y = (t[1] >> 8) | (t[2] << 16);
+        w1.x = (t[2] >> 16) | (t[3] << 8); w1.y = t[4] | (t[5] << 24);
+        w2.x = (t[5] >> 8) | (t[6] << 16); w2.y = (t[6] >> 16) | (t[7] << 8);
+        uint2* o = reinterpret_cast<uint2*>(out) + j * 3;
+        __stcs(o, w0); __stcs(o + 1, w1); __stcs(o + 2, w2);
+    }
+}
+
 cudaError_t launch_wav_encode(const float* l, const float* r, long long n, int bits, unsigned char* out, cudaStream_t st) {
     if (n <= 0) return cudaSuccess;
+    if (bits != 16 && bits != 24) return cudaErrorInvalidValue;
+    long long done = 0;
+    if (r && ((reinterpret_cast<uintptr_t>(l) | reinterpret_cast<uintptr_t>(r)) & 15) == 0 && n >= 4) {
+        const long long n4 = n / 4;
+        const unsigned g4 = (unsigned) ((n4 + 255) / 256);
+        if (bits == 16) wav_encode4_kernel<2><<<g4, 256, 0, st>>>(reinterpret_cast<const float4*>(l), reinterpret_cast<const float4*>(r), n4, out);
+        else wav_encode4_kernel<3><<<g4, 256, 0, st>>>(reinterpret_cast<const float4*>(l), reinterpret_cast<const float4*>(r), n4, out);
+        done = n4 * 4;
+        if (done == n) return cudaGetLastError();
+        l += done; r += done; out += (size_t) done * 2 * (bits / 8); n -= done;      // the last 1-3 frames: scalar kernel
+    }
     const unsigned grid = (unsigned) ((n + 255) / 256);
     if (bits == 16) wav_encode_kernel<2><<<grid, 256, 0, st>>>(l, r, n, out);
     else if (bits == 24) wav_encode_kernel<3><<<grid, 256, 0, st>>>(l, r, n, out);
