@@ -310,6 +310,16 @@ ZL_EXPORT int ZL_FN(thumb_build)(zl_ctx* ctx, int32_t clip_id, int32_t samples_p
 ZL_EXPORT int ZL_FN(thumb_size)(zl_ctx* ctx, int32_t clip_id, int32_t* n_thumb, int32_t* nch);
 /* out: [nch][n_thumb][2] int8 */
 ZL_EXPORT int ZL_FN(thumb_read_level0)(zl_ctx* ctx, int32_t clip_id, int8_t* out);
+/* n4: the thumbnail in JUCE's `jatm` stream format - AudioThumbnail::saveTo / loadFrom
+ * (JUCE/juce_audio_utils/gui/juce_AudioThumbnail.cpp:593-639), what AudioThumbnailCache::storeThumb keeps per file hash:
+ * "jatm", samplesPerThumbSample i32, totalSamples i64, numSamplesFinished i64 (= whole thumb blocks read, :735-743),
+ * numThumbnailSamples i32, numChannels i32, sampleRate i32, 16 reserved bytes, then [thumb sample][channel](min, max) int8.
+ * save: the device level-0 table is transposed on the device into that order (builds it at 512 samples per thumb
+ * sample if the clip has none, lib/WaveFormItem.cpp:22); out == NULL or cap too small: *size set, ZL_ERR_STATE.
+ * load: replaces the clip's level-0 table (no pass over the PCM); the stream must describe this clip (channels and
+ * 1 + length / samplesPerThumbSample entries), anything else is ZL_ERR_INVALID. */
+ZL_EXPORT int ZL_FN(thumb_save_jatm)(zl_ctx* ctx, int32_t clip_id, void* out, uint64_t cap, uint64_t* size);
+ZL_EXPORT int ZL_FN(thumb_load_jatm)(zl_ctx* ctx, int32_t clip_id, const void* jatm, uint64_t nbytes);
 /* CachedWindow::refillCache (juce_AudioThumbnail.cpp:430-521) for all channels:
  * out [nch][width][2] int8 (min,max).  Returns ZL_ERR_INVALID where the reference returns false. */
 ZL_EXPORT int ZL_FN(thumb_pixels)(zl_ctx* ctx, int32_t clip_id, double t0, double t1,

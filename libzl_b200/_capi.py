@@ -86,6 +86,8 @@ SIGNATURES = {
     "clip_read_pcm": (C.c_int, [_ctx, C.c_int32, _P(_f32p), C.c_int32, C.c_int64]),
     "wav_encode": (C.c_int, [_ctx, _f32p, _f32p, C.c_int64, C.c_double, C.c_int32, C.c_void_p, C.c_uint64, _P(C.c_uint64)]),
     "bounce_wav": (C.c_int, [_ctx, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint64, _P(C.c_uint64)]),
+    "thumb_save_jatm": (C.c_int, [_ctx, C.c_int32, C.c_void_p, C.c_uint64, _P(C.c_uint64)]),
+    "thumb_load_jatm": (C.c_int, [_ctx, C.c_int32, C.c_void_p, C.c_uint64]),
     "clip_destroy": (C.c_int, [_ctx, C.c_int32]),
     "clip_params_default": (C.c_int, [_ctx, C.c_int32, _P(zl_clip_params)]),
     "clip_set_params": (C.c_int, [_ctx, C.c_int32, _P(zl_clip_params)]),

@@ -39,6 +39,7 @@ int wav_parse(const void* bytes, uint64_t n, zl_wav_format* f);
 cudaError_t launch_wav_decode(const unsigned char* raw, const zl_wav_format& f, int nchOut, long long padded, float* out, cudaStream_t st);
 cudaError_t launch_wav_encode(const float* l, const float* r, long long n, int bits, unsigned char* out, cudaStream_t st);
 int wav_header(unsigned char* h, int nch, double rate, int bits, uint64_t dataBytes);
+cudaError_t launch_jatm_transpose(const void* in, int nch, int n, int toJatm, void* out, cudaStream_t st);
 }  // namespace zl
 
 using namespace zl;
@@ -1187,6 +1188,61 @@ int zl_thumb_read_level0(zl_ctx* ctx, int32_t id, int8_t* out) {
     if (!c || !c->nThumb || !out) { ctx->err = "thumb_read_level0: no thumbnail built"; return ZL_ERR_STATE; }
     CK(cudaMemcpyAsync(out, c->d_thumb, (size_t) c->nch * c->nThumb * 2, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    return ZL_OK;
+}
+
+// ---- n4: jatm stream (AudioThumbnail::saveTo / loadFrom, juce_AudioThumbnail.cpp:593-639) ----------------------------
+static void put_le(unsigned char* o, uint64_t v, int bytes) { for (int i = 0; i < bytes; ++i) o[i] = (unsigned char) (v >> (8 * i)); }
+static uint64_t get_le(const unsigned char* p, int bytes) { uint64_t v = 0; for (int i = 0; i < bytes; ++i) v |= (uint64_t) p[i] << (8 * i); return v; }
+
+int zl_thumb_save_jatm(zl_ctx* ctx, int32_t id, void* out, uint64_t cap, uint64_t* size) {
+    BIND();
+    ClipHost* c = find_clip(ctx, id);
+    if (!c || !size) return invalid(ctx, "thumb_save_jatm: bad argument");
+    if (!c->nThumb) { int rc = build_thumb(ctx, c, 512); if (rc != ZL_OK) return rc; }
+    const uint64_t body = (uint64_t) c->nThumb * c->nch * 2, total = 52 + body;
+    *size = total;
+    if (!out || cap < total) { ctx->err = "thumb_save_jatm: output buffer too small (size returned)"; return ZL_ERR_STATE; }
+    unsigned char* o = static_cast<unsigned char*>(out);
+    memcpy(o, "jatm", 4);
+    put_le(o + 4, (uint32_t) c->thumbSpt, 4);
+    put_le(o + 8, (uint64_t) c->length, 8);                                              // totalSamples
+    put_le(o + 16, (uint64_t) (c->length / c->thumbSpt) * (uint64_t) c->thumbSpt, 8);    // numSamplesFinished: the last setLevels' end
+    put_le(o + 24, (uint32_t) c->nThumb, 4);
+    put_le(o + 28, (uint32_t) c->nch, 4);
+    put_le(o + 32, (uint32_t) (int) c->rate, 4);
+    memset(o + 36, 0, 16);
+    void* d_t = nullptr;
+    CK(cudaMalloc(&d_t, (size_t) body));
+    cudaError_t e = launch_jatm_transpose(c->d_thumb, c->nch, c->nThumb, 1, d_t, ctx->stream);
+    ctx->launches++;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(o + 52, d_t, (size_t) body, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_t);
+    if (e != cudaSuccess) return fail(ctx, e, "thumb_save_jatm");
+    return ZL_OK;
+}
+
+int zl_thumb_load_jatm(zl_ctx* ctx, int32_t id, const void* jatm, uint64_t nbytes) {
+    BIND();
+    ClipHost* c = find_clip(ctx, id);
+    const unsigned char* p = static_cast<const unsigned char*>(jatm);
+    if (!c || !p || nbytes < 52 || memcmp(p, "jatm", 4) != 0) return invalid(ctx, "thumb_load_jatm: not a jatm stream");
+    const int spt = (int) (int32_t) get_le(p + 4, 4), n = (int) (int32_t) get_le(p + 24, 4), nch = (int) (int32_t) get_le(p + 28, 4);
+    if (spt < 1 || nch != c->nch || n != 1 + c->length / spt || (int64_t) get_le(p + 8, 8) != c->length || nbytes < 52 + (uint64_t) n * nch * 2)
+        return invalid(ctx, "thumb_load_jatm: the stream does not describe this clip");
+    const size_t body = (size_t) n * nch * 2;
+    if (c->d_thumb) { CK(cudaStreamSynchronize(ctx->stream)); cudaFree(c->d_thumb); c->d_thumb = nullptr; c->nThumb = 0; }
+    void* d_t = nullptr;
+    CK(cudaMalloc(&d_t, body));
+    cudaError_t e = cudaMalloc((void**) &c->d_thumb, body);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_t, p + 52, body, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = launch_jatm_transpose(d_t, nch, n, 0, c->d_thumb, ctx->stream);
+    ctx->launches++;
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_t);
+    if (e != cudaSuccess) { if (c->d_thumb) cudaFree(c->d_thumb); c->d_thumb = nullptr; return fail(ctx, e, "thumb_load_jatm"); }
+    c->thumbSpt = spt; c->nThumb = n;
     return ZL_OK;
 }
 

@@ -728,7 +728,8 @@ void render_bind_scratch(RenderParams& P, void* scratch, int nVoices, int nframe
 cudaError_t launch_plan(RenderParams& P, cudaStream_t stream) {
     const int V = P.V, nBuses = P.nSessions * P.B;
     if (V < 1 || V > 1024) return cudaErrorInvalidValue;
-    P.planBusesPerCta = V >= 128 ? 1 : 128 / V;
+    static const int planThreadsWanted = [] { const char* e = getenv("ZL_B200_PLAN_THREADS"); const int v = e ? atoi(e) : 64; return v == 32 || v == 128 ? v : 64; }();
+    P.planBusesPerCta = V >= planThreadsWanted ? 1 : planThreadsWanted / V;
     const int planThreads = ((P.planBusesPerCta * V + 31) / 32) * 32;
     P.planGroups = (nBuses + P.planBusesPerCta - 1) / P.planBusesPerCta;
     const int planGrid = P.planCtaCap > 0 ? min(P.planGroups, P.planCtaCap) : P.planGroups;

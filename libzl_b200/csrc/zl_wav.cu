@@ -226,6 +226,21 @@ cudaError_t launch_deinterleave(const float* in, int nch, long long len, float* 
     return cudaGetLastError();
 }
 
+// n4: level-0 table [nch][n](min,max) <-> jatm order [n][nch](min,max); one 2-byte pair per thread element, nch <= 2
+__global__ void __launch_bounds__(256) jatm_transpose_kernel(const uint16_t* __restrict__ in, int nch, int n, int toJatm, uint16_t* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    for (int ch = 0; ch < nch; ++ch) {
+        if (toJatm) out[(size_t) i * nch + ch] = in[(size_t) ch * n + i];
+        else out[(size_t) ch * n + i] = in[(size_t) i * nch + ch];
+    }
+}
+cudaError_t launch_jatm_transpose(const void* in, int nch, int n, int toJatm, void* out, cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    jatm_transpose_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(static_cast<const uint16_t*>(in), nch, n, toJatm, static_cast<uint16_t*>(out));
+    return cudaGetLastError();
+}
+
 // ---- device: encode -----------------------------------------------------------------------------------------------
 // convertFloatsToInts (juce_AudioFormatWriter.cpp:64-79); roundToInt of a double = round half to even (juce_MathsFunctions.h:471-485)
 __device__ __forceinline__ int32_t float_to_fixed(float x) {

@@ -143,6 +143,20 @@ class Engine:
         self._chk(self.lib.bounce_wav(self.ctx, session, bus, which, bits, out.ctypes.data_as(C.c_void_p), out.size, C.byref(size)), "bounce_wav")
         return out
 
+    def thumb_save_jatm(self, clip):
+        """The clip's thumbnail as a JUCE `jatm` stream (AudioThumbnail::saveTo)."""
+        size = C.c_uint64(0)
+        self.lib.thumb_save_jatm(self.ctx, clip, None, 0, C.byref(size))
+        if size.value == 0:
+            self._chk(K.ZL_ERR_STATE, "thumb_save_jatm")
+        out = np.zeros(size.value, np.uint8)
+        self._chk(self.lib.thumb_save_jatm(self.ctx, clip, out.ctypes.data_as(C.c_void_p), out.size, C.byref(size)), "thumb_save_jatm")
+        return out
+
+    def thumb_load_jatm(self, clip, jatm):
+        buf = np.ascontiguousarray(jatm, np.uint8)
+        self._chk(self.lib.thumb_load_jatm(self.ctx, clip, buf.ctypes.data_as(C.c_void_p), buf.size), "thumb_load_jatm")
+
     def add_clip_device(self, dptr, nch, frames, rate=48000.0):
         cid = C.c_int32(-1)
         self._chk(self.lib.clip_create_from_device(self.ctx, C.c_void_p(dptr), nch, frames, float(rate), C.byref(cid)),

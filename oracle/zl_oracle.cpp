@@ -961,6 +961,42 @@ int zlo_thumb_read_level0(zl_ctx* ctx, int32_t id, int8_t* out) {
     for (int ch = 0; ch < c->nch; ++ch) memcpy(out + (size_t) ch * (size_t) c->nThumb * 2, c->thumb[ch].data(), (size_t) c->nThumb * 2);
     return ZL_OK;
 }
+// AudioThumbnail::saveTo / loadFrom  juce_AudioThumbnail.cpp:593-639 (MinMaxValue::read/write :75-84: two raw bytes).
+// juce_audio_utils does not build here, so this row is restated from the source lines only: parity unpinned.
+int zlo_thumb_save_jatm(zl_ctx* ctx, int32_t id, void* out, uint64_t cap, uint64_t* size) {
+    Clip* c = ctx ? findClip(ctx, id) : nullptr; if (!c || !size) return ZL_ERR_INVALID;
+    if (!c->nThumb) buildThumb(c, 512);
+    std::vector<unsigned char> o;
+    auto writeInt = [&](int32_t v) { for (int i = 0; i < 4; ++i) o.push_back((unsigned char) ((uint32_t) v >> (8 * i))); };
+    auto writeInt64 = [&](int64_t v) { for (int i = 0; i < 8; ++i) o.push_back((unsigned char) ((uint64_t) v >> (8 * i))); };
+    o.insert(o.end(), {'j', 'a', 't', 'm'});
+    writeInt(c->thumbSamples);
+    writeInt64(c->length);                                                     // totalSamples
+    writeInt64((int64_t) (c->length / c->thumbSamples) * c->thumbSamples);     // numSamplesFinished after the last setLevels (:735-743)
+    writeInt(c->nThumb); writeInt(c->nch); writeInt((int) c->rate);
+    writeInt64(0); writeInt64(0);
+    for (int i = 0; i < c->nThumb; ++i)
+        for (int ch = 0; ch < c->nch; ++ch) { o.push_back((unsigned char) c->thumb[ch][(size_t) i * 2]); o.push_back((unsigned char) c->thumb[ch][(size_t) i * 2 + 1]); }
+    *size = o.size();
+    if (!out || cap < o.size()) return ZL_ERR_STATE;
+    memcpy(out, o.data(), o.size());
+    return ZL_OK;
+}
+int zlo_thumb_load_jatm(zl_ctx* ctx, int32_t id, const void* jatm, uint64_t nbytes) {
+    Clip* c = ctx ? findClip(ctx, id) : nullptr;
+    const unsigned char* p = static_cast<const unsigned char*>(jatm);
+    if (!c || !p || nbytes < 52 || p[0] != 'j' || p[1] != 'a' || p[2] != 't' || p[3] != 'm') return ZL_ERR_INVALID;
+    auto readInt = [&](size_t at) { uint32_t v = 0; for (int i = 0; i < 4; ++i) v |= (uint32_t) p[at + (size_t) i] << (8 * i); return (int32_t) v; };
+    auto readInt64 = [&](size_t at) { uint64_t v = 0; for (int i = 0; i < 8; ++i) v |= (uint64_t) p[at + (size_t) i] << (8 * i); return (int64_t) v; };
+    const int spt = readInt(4), n = readInt(24), nch = readInt(28);
+    if (spt < 1 || nch != c->nch || n != 1 + c->length / spt || readInt64(8) != c->length || nbytes < 52 + (uint64_t) n * (uint64_t) nch * 2) return ZL_ERR_INVALID;
+    c->thumbSamples = spt; c->nThumb = n;
+    for (int ch = 0; ch < nch; ++ch) c->thumb[ch].assign((size_t) n * 2, 0);
+    size_t at = 52;
+    for (int i = 0; i < n; ++i)
+        for (int ch = 0; ch < nch; ++ch) { c->thumb[ch][(size_t) i * 2] = (int8_t) p[at++]; c->thumb[ch][(size_t) i * 2 + 1] = (int8_t) p[at++]; }
+    return ZL_OK;
+}
 int zlo_thumb_pixels(zl_ctx* ctx, int32_t id, double t0, double t1, int32_t width, int8_t* out) {
     Clip* c = ctx ? findClip(ctx, id) : nullptr; if (!c || !out) return ZL_ERR_INVALID;
     if (!c->nThumb) buildThumb(c, 512);                                      // lib/WaveFormItem.cpp:22
