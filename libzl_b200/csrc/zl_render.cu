@@ -452,19 +452,23 @@ constexpr int kStageV = 16;          // voices per bus whose descriptors are sta
 // v + 2 - contiguous, 16 bytes per lane per instruction, so every 128-byte line crosses the L1 data pipe once - into
 // shared-memory slots while the arithmetic of voice-tile v runs on a slot that has already landed.  No registers are
 // held by loads in flight, and the taps themselves are then two LDS.64 per lane-frame.
-__device__ __forceinline__ void cp_async16(uint32_t saddr, const void* gptr) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(saddr), "l"(gptr) : "memory");
+template <int OFF> __device__ __forceinline__ void cp_async16(uint32_t saddr, const void* gptr) {   // same immediate offset on both sides
+    asm volatile("cp.async.cg.shared.global [%0 + %2], [%1 + %2], 16;" :: "r"(saddr), "l"(gptr), "n"(OFF) : "memory");
 }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
-__device__ __forceinline__ void stage_window(const TileDesc& d, int lane, unsigned char* slot) {
-    const unsigned char* src = reinterpret_cast<const unsigned char*>((uintptr_t) __double_as_longlong(d.p0b)) + lane * 16;
-    const int rows = __double2loint(d.Rb) >> 9;                          // whole 512-byte rows (warp-uniform)
-    const uint32_t sa = (uint32_t) __cvta_generic_to_shared(slot) + lane * 16;
-#pragma unroll
-    for (int k = 0; k < kSlotBytes / 512; ++k)
-        if (k < rows) cp_async16(sa + k * 512, src + k * 512);
-    asm volatile("cp.async.commit_group;" ::: "memory");
+// Issues the copies of one window into the slot at shared address `slot`; the caller commits the group.
+__device__ __forceinline__ void stage_window(const TileDesc& d, int lane16, uint32_t slot) {
+    const unsigned char* src = reinterpret_cast<const unsigned char*>((uintptr_t) __double_as_longlong(d.p0b)) + lane16;
+    const int rows = __double2loint(d.Rb) >> 9;                          // whole 512-byte rows (warp-uniform), >= 1
+    const uint32_t sa = slot + lane16;
+    static_assert(kSlotBytes == 5 * 512, "stage_window copies up to five rows");
+    cp_async16<0>(sa, src);
+    if (rows > 1) cp_async16<512>(sa, src);
+    if (rows > 2) cp_async16<1024>(sa, src);
+    if (rows > 3) cp_async16<1536>(sa, src);
+    if (rows > 4) cp_async16<2048>(sa, src);
 }
 
 template <bool JMODE, bool Q1>
@@ -492,6 +496,8 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
     __shared__ __align__(16) unsigned char sWin[STAGED ? W : 1][kSlots][kSlotBytes];
     int lane = threadIdx.x & 31, warp = STAGED ? (threadIdx.x >> 5) : 0;
     asm volatile("" : "+r"(lane), "+r"(warp));            // opaque: keeps ptxas from re-deriving them from S2R inside the voice loop
+    const int lane16 = lane * 16;
+    const uint32_t slot0 = (uint32_t) __cvta_generic_to_shared(&sWin[warp][0][0]);
     const int gbw = blockIdx.x * W + (threadIdx.x >> 5);      // global bus
     if (gbw >= P.nSessions * P.B) return;
     const unsigned FULL = 0xffffffffu;
@@ -544,34 +550,44 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
                     atomicMax(reinterpret_cast<int*>(&P.voices[v0 + vs].posGain), __float_as_int(__fmul_rn(__int_as_float(pk), 0.5f)));
             }
         };
-        // STAGED: the tile's staged voice-tiles, in slot order, form a queue through the kSlots window slots: two windows
-        // are in flight behind the one being computed.  toStage = voices not yet staged; si / sd = next slot to stage / to read.
-        unsigned toStage = 0;
-        int si = 0, sd = 0, inFlight = 0;
+        // STAGED: the tile's window-staged voice-tiles, in slot order, form a queue through the kSlots slots: two windows
+        // are in flight behind the one being computed.  Exactly one cp.async group is committed per queue position
+        // (an empty one when nothing is left to stage), so "all but the newest two groups have landed" is always the
+        // window about to be read.  act = voices that sound in this tile, toStage = of those, not yet staged.
+        unsigned act = 0, toStage = 0;
+        uint32_t wrSlot = slot0;
+        int rdOff = 0, vs = -1;
         if (STAGED) {
-            toStage = __ballot_sync(FULL, lane < V && (sDesc[warp][lane < V ? lane : 0].nrend & kRingBit) != 0);
+            const int fl = lane < V ? sDesc[warp][lane].nrend : 0;
+            act = __ballot_sync(FULL, (fl & kCountMask) != 0);
+            toStage = __ballot_sync(FULL, (fl & kCountMask) != 0 && (fl & kRingBit) != 0);
 #pragma unroll
-            for (int k = 0; k < kSlots - 1; ++k)
+            for (int k = 0; k < kSlots - 1; ++k) {
                 if (toStage) {
-                    stage_window(sDesc[warp][__ffs(toStage) - 1], lane, sWin[warp][si]);
-                    toStage &= toStage - 1; si = si + 1 == kSlots ? 0 : si + 1; ++inFlight;
+                    stage_window(sDesc[warp][__ffs(toStage) - 1], lane16, wrSlot);
+                    toStage &= toStage - 1; wrSlot = wrSlot == slot0 + (kSlots - 1) * kSlotBytes ? slot0 : wrSlot + kSlotBytes;
                 }
+                cp_async_commit();
+            }
         }
-        for (int vs = 0; vs < V; ++vs) {
+        for (;;) {
+            if (STAGED) { if (!act) break; vs = __ffs(act) - 1; act &= act - 1; }   // silent voices are never visited
+            else if (++vs >= V) break;
             const TileDesc d = STAGED ? sDesc[warp][vs] : load_desc(dp + vs);
             const int nr = d.nrend & kCountMask;              // warp-uniform
-            if (nr == 0) continue;
+            if (!STAGED && nr == 0) continue;
             const VoiceGather g = STAGED ? sVg[warp][vs] : load_vg(P.vgs + v0 + vs);
             if (STAGED && (d.nrend & kRingBit)) {
                 if (toStage) {                                // keep the queue full: the slot read last time is free
-                    stage_window(sDesc[warp][__ffs(toStage) - 1], lane, sWin[warp][si]);
-                    toStage &= toStage - 1; si = si + 1 == kSlots ? 0 : si + 1; ++inFlight;
+                    stage_window(sDesc[warp][__ffs(toStage) - 1], lane16, wrSlot);
+                    toStage &= toStage - 1; wrSlot = wrSlot == slot0 + (kSlots - 1) * kSlotBytes ? slot0 : wrSlot + kSlotBytes;
                 }
-                if (inFlight >= 3) cp_async_wait<2>(); else if (inFlight == 2) cp_async_wait<1>(); else cp_async_wait<0>();
+                cp_async_commit();
+                cp_async_wait<kSlots - 1>();
                 __syncwarp();                                 // the window was copied by all lanes
-                take_peak(gather_finish_ring<JMODE, Q1>(d, g, sWin[warp][sd], laneD, laneF, nz, acc), vs, g.nch);
+                take_peak(gather_finish_ring<JMODE, Q1>(d, g, sWin[warp][0] + rdOff, laneD, laneF, nz, acc), vs, g.nch);
                 __syncwarp();                                 // every lane is done with the slot before it is staged again
-                sd = sd + 1 == kSlots ? 0 : sd + 1; --inFlight;
+                rdOff = rdOff == (kSlots - 1) * kSlotBytes ? 0 : rdOff + kSlotBytes;
                 continue;
             }
             Taps tp;
