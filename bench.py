@@ -270,8 +270,10 @@ def run_cuda(args, rank, world, local_rank):
     barrier()
     # gather_kernel alone (no planner beside it): one extra untimed step on one stream, per-launch events
     e._chk(e.lib.ctx_set_overlap(e.ctx, 0), "ctx_set_overlap")
+    step(2 * total_steps)                                     # one step to settle into the single-stream schedule
+    barrier()
     e._chk(e.lib.kernel_timing(e.ctx, 2), "kernel_timing")
-    step(2 * total_steps)
+    step(2 * total_steps + 1)
     barrier()
     kms0, kn0 = C.c_double(), C.c_uint64()
     e._chk(e.lib.kernel_time(e.ctx, C.byref(kms0), C.byref(kn0)), "kernel_time")
