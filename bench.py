@@ -329,7 +329,7 @@ def run_cuda(args, rank, world, local_rank):
     h2d = wl.steps[0][3].nbytes + wl.steps[0][0].nbytes * 2 + wl.steps[0][2].nbytes + NB * 40
     d2h = S * 2 * n_per_step * 4
     # the last step's masters really are on the host: compare a few sessions with a synchronous read-back
-    chk = np.ctypeslib.as_array(host_master[(args.steps - 1) & 1], shape=(S, 2, n_per_step))[:4].copy()
+    chk = np.ctypeslib.as_array(host_master[0 if master_t is not None else (args.steps - 1) & 1], shape=(S, 2, n_per_step))[:4].copy()
     ref = np.zeros((2, n_per_step), np.float32)
     for sidx in range(min(4, S)):
         l_, r_ = e.master(sidx)
