@@ -402,8 +402,11 @@ __global__ void __launch_bounds__(MAXT, MAXT == 128 ? ZL_PLAN_MINB : 1) plan_ker
 
 // walk_kernel: thread = queued voice (the ones plan_kernel deferred); CTA = one warp, grid-stride over the warps of
 // the two queues (serial walkers first, so the long ones start first).
+#ifndef ZL_WALK_MINB
+#define ZL_WALK_MINB 1      // one-warp CTAs per SM the register allocation is sized for (1: no cap, 128 registers)
+#endif
 template <bool JMODE, bool Q3>
-__global__ void __launch_bounds__(32) walk_kernel(const RenderParams P) {
+__global__ void __launch_bounds__(32, ZL_WALK_MINB) walk_kernel(const RenderParams P) {
     const unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x;
     const int cA = P.walkCount[2 * P.blk], cB = P.walkCount[2 * P.blk + 1];
