@@ -150,6 +150,8 @@ struct zl_ctx {
     bool overlapEnabled = true;
     cudaStream_t planStream = nullptr;                  // high priority: plan/walk of period b + 1 overlap the gather of period b
     cudaEvent_t evStart = nullptr, evPlan[2] = {nullptr, nullptr}, evGather[2] = {nullptr, nullptr};
+    cudaStream_t mixStream = nullptr;                   // low priority: the master mix of period b runs beside the gather of period b + 1
+    cudaEvent_t evMix = nullptr;
     int32_t* d_walkCount = nullptr; int walkCountCap = 0;
     int64_t stride = 0; size_t lvlCap = 0;
     int nblocks = 0, nframes = 0;
@@ -327,6 +329,8 @@ int zl_ctx_destroy(zl_ctx* ctx) {
     for (void* p : frees) if (p) cudaFree(p);
     if (ctx->d_scratch) cudaFree(ctx->d_scratch);
     if (ctx->planStream) { cudaStreamSynchronize(ctx->planStream); cudaStreamDestroy(ctx->planStream); }
+    if (ctx->mixStream) { cudaStreamSynchronize(ctx->mixStream); cudaStreamDestroy(ctx->mixStream); }
+    if (ctx->evMix) cudaEventDestroy(ctx->evMix);
     if (ctx->evStart) cudaEventDestroy(ctx->evStart);
     for (int k = 0; k < 2; ++k) { if (ctx->evPlan[k]) cudaEventDestroy(ctx->evPlan[k]); if (ctx->evGather[k]) cudaEventDestroy(ctx->evGather[k]); }
     if (ctx->copyStream) { cudaStreamSynchronize(ctx->copyStream); cudaStreamDestroy(ctx->copyStream); }
@@ -757,6 +761,16 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         }
     }
     cudaStream_t ps = overlap ? ctx->planStream : st;
+    // The port mix re-reads the raw planes at DRAM speed; sliced by period on a third, low-priority stream it runs in the DRAM
+    // headroom of the following gather (same kernel, same arithmetic).  Needs float4 rows: nframes and stride multiples of 4.
+    static const bool mixOverlapWanted = env_int("ZL_B200_MIX_OVERLAP", 1) != 0;
+    const bool mixPerBlock = overlap && ctx->d_master && mixOverlapWanted && (nframes & 3) == 0 && (ctx->stride & 3) == 0;
+    if (mixPerBlock && !ctx->mixStream) {
+        int lo = 0, hi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CK(cudaStreamCreateWithPriority(&ctx->mixStream, cudaStreamNonBlocking, lo));
+        CK(cudaEventCreateWithFlags(&ctx->evMix, cudaEventDisableTiming));
+    }
     // timing 1: one event pair around the whole plan/walk/gather sequence of this call; 2: one pair per gather_kernel launch
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->timing == 1) {
@@ -805,12 +819,22 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         CK(launch_gather(P, st, g0, g1));
         if (overlap) CK(cudaEventRecord(ctx->evGather[par], st));
         ctx->launches += 3;
+        if (mixPerBlock) {                          // this period's slice of the JACK port mix: a DRAM stream beside the next gather
+            const int64_t off = (int64_t) blk * nframes;
+            CK(cudaStreamWaitEvent(ctx->mixStream, ctx->evGather[par], 0));
+            CK(launch_master_mix(ctx->d_out[0] + off, ctx->d_buses, ctx->d_master + off, ctx->cfg.n_sessions, ctx->cfg.buses_per_session,
+                                 ctx->stride, nframes, ctx->mixStream));
+            ctx->launches++;
+        }
     }
     if (ctx->timing == 1) {
         CK(cudaEventRecord(e1, st));
         ctx->tev.push_back(e0); ctx->tev.push_back(e1);
     }
-    if (ctx->d_master) {
+    if (mixPerBlock) {                              // everything later on the context stream comes after the last slice
+        CK(cudaEventRecord(ctx->evMix, ctx->mixStream));
+        CK(cudaStreamWaitEvent(st, ctx->evMix, 0));
+    } else if (ctx->d_master) {
         CK(launch_master_mix(ctx->d_out[0], ctx->d_buses, ctx->d_master, ctx->cfg.n_sessions, ctx->cfg.buses_per_session,
                              ctx->stride, (int64_t) nblocks * nframes, st));
         ctx->launches++;
