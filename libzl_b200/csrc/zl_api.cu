@@ -721,9 +721,7 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         }
     }
     ctx->pending.clear();
-    CK(cudaMemcpyAsync(ds, hs, slotBytes, cudaMemcpyHostToDevice, st));
     auto hp3 = std::chrono::steady_clock::now();
-    CK(cudaMemsetAsync(ctx->d_counters, 0, 2 * sizeof(unsigned long long), st));
     const zl_block_clock* dck = reinterpret_cast<const zl_block_clock*>(ds);
 
     RenderParams P{};
@@ -743,7 +741,6 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         CK(cudaMalloc((void**) &ctx->d_walkCount, sizeof(int32_t) * 2 * (size_t) nblocks));
         ctx->walkCountCap = nblocks;
     }
-    CK(cudaMemsetAsync(ctx->d_walkCount, 0, sizeof(int32_t) * 2 * (size_t) nblocks, st));
     P.walkCount = ctx->d_walkCount;
     // Two streams: plan/walk of period b + 1 (high priority) run beside the gather of period b.  The positions-model gain
     // is then written by the gather alone (V <= 32); with more voices per bus it needs the planner's reset first -> one stream.
@@ -771,6 +768,11 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         CK(cudaStreamCreateWithPriority(&ctx->mixStream, cudaStreamNonBlocking, lo));
         CK(cudaEventCreateWithFlags(&ctx->evMix, cudaEventDisableTiming));
     }
+    // The command upload and the counter resets are the planner's inputs only: queued on its stream they run beside the tail
+    // of the previous render instead of between two renders (one stream: the same order as ever).
+    CK(cudaMemcpyAsync(ds, hs, slotBytes, cudaMemcpyHostToDevice, ps));
+    CK(cudaMemsetAsync(ctx->d_counters, 0, 2 * sizeof(unsigned long long), ps));
+    CK(cudaMemsetAsync(ctx->d_walkCount, 0, sizeof(int32_t) * 2 * (size_t) nblocks, ps));
     // timing 1: one event pair around the whole plan/walk/gather sequence of this call; 2: one pair per gather_kernel launch
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->timing == 1) {
