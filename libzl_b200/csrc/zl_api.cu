@@ -150,6 +150,8 @@ struct zl_ctx {
     bool overlapEnabled = true;
     cudaStream_t planStream = nullptr;                  // high priority: plan/walk of period b + 1 overlap the gather of period b
     cudaEvent_t evStart = nullptr, evPlan[2] = {nullptr, nullptr}, evGather[2] = {nullptr, nullptr};
+    size_t chainScratchBytes = 0;
+    bool planChained = false;                           // the previous zl_render ran two-stream: its evGather records order the next planner
     cudaStream_t mixStream = nullptr;                   // low priority: the master mix of period b runs beside the gather of period b + 1
     cudaEvent_t evMix = nullptr;
     int32_t* d_walkCount = nullptr; int walkCountCap = 0;
@@ -358,6 +360,7 @@ int zl_ctx_set_overlap(zl_ctx* ctx, int32_t enable) {
 int zl_ctx_set_stream(zl_ctx* ctx, void* s) {
     if (!ctx) return ZL_ERR_INVALID;
     ctx->stream = s ? (cudaStream_t) s : ctx->own;
+    ctx->planChained = false;
     return ZL_OK;
 }
 
@@ -779,10 +782,19 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
         CK(cudaEventRecord(e0, st));
     }
-    if (overlap) {                                  // everything queued on st so far (tables, commands, counters) precedes the planner
+    // Across renders the planner of period 0 stands to the previous render's last gather as plan(b + 1) to gather(b) inside
+    // a render: it needs the planner before it (same stream) and the hand-over buffer of its parity (evGather, below), nothing
+    // else - every other producer of its inputs (clip and bus tables, voice reads) is host-synchronous.  Only the first
+    // two-stream render after a one-stream one (or a stream change) orders itself after everything queued on st.
+    size_t soff[5];
+    const size_t scratchBytes = render_scratch_bytes((int) (NB * ctx->cfg.voices_per_bus), nframes, soff);
+    const bool chained = overlap && ctx->planChained && scratchBytes == ctx->chainScratchBytes;   // same two hand-over buffers as last time
+    ctx->chainScratchBytes = scratchBytes;
+    if (overlap && !chained) {
         CK(cudaEventRecord(ctx->evStart, st));
         CK(cudaStreamWaitEvent(ps, ctx->evStart, 0));
     }
+    ctx->planChained = overlap;
     const char* tl = ctx->timing == 2 ? nullptr : getenv("ZL_B200_TIMELINE");
     std::vector<cudaEvent_t> tlev;
     static cudaEvent_t tlBase = nullptr;
@@ -792,13 +804,11 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     }
     static const int planCap = env_int("ZL_B200_PLAN_CTAS", ZL_PLAN_CTAS_PER_SM) * ctx_sm_count();
     static const int walkCap = env_int("ZL_B200_WALK_CTAS", ZL_WALK_CTAS_PER_SM) * ctx_sm_count();
-    size_t soff[5];
-    const size_t scratchBytes = render_scratch_bytes((int) (NB * ctx->cfg.voices_per_bus), nframes, soff);
     for (int blk = 0; blk < nblocks; ++blk) {      // one JACK period = plan_kernel + walk_kernel + gather_kernel
         const int par = blk & 1;
         P.blk = blk;
         render_bind_scratch(P, static_cast<unsigned char*>(ctx->d_scratch) + (size_t) par * scratchBytes, (int) (NB * ctx->cfg.voices_per_bus), nframes);
-        if (overlap && blk >= 2) CK(cudaStreamWaitEvent(ps, ctx->evGather[par], 0));   // gather(blk - 2) has released this hand-over buffer
+        if (overlap && (blk >= 2 || chained)) CK(cudaStreamWaitEvent(ps, ctx->evGather[par], 0));   // gather(blk - 2) (or the previous render's of this parity) has released this hand-over buffer
         // beside a running gather the planner gets a few CTAs per SM only: it has the whole gather to finish in, and
         // a full-size high-priority grid would push the gather off the SMs while it waits on its own latencies
         P.planCtaCap = overlap && blk >= 1 ? planCap : 0;
