@@ -231,3 +231,38 @@ def test_high_pitch_ratios_bypass_the_window_staging(product, oracle):
     for (m0, r0, p0, v0), (m1, r1, p1, v1) in zip(run(product), run(oracle)):
         assert np.array_equal(m0, m1) and np.array_equal(r0, r1) and np.array_equal(p0, p1) and v0 == v1
         assert np.abs(m0).max() > 0.05
+
+
+def test_stream_schedules_agree_render_after_render(product, oracle):
+    """The two-stream schedule (planner of the next period beside the gather, planner of period 0 chained to the previous
+    render, master mix sliced by period on a third stream, uploads on the planner stream) must give bit for bit what the
+    one-stream schedule and the oracle give - across renders with commands in between, a change of period size (the
+    hand-over buffers move: the chain must fall back) and a one-period render in the middle."""
+    def run(lib, overlap):
+        rng = np.random.default_rng(21)
+        e = Engine(lib=lib, n_sessions=2, buses_per_session=3, voices_per_bus=4, max_frames=512, max_blocks=8)
+        if lib is product:
+            e._chk(lib.ctx_set_overlap(e.ctx, 1 if overlap else 0), "ctx_set_overlap")
+        clips = [e.add_clip(rng.uniform(-1, 1, (2, 9000 + 1000 * k)).astype(np.float32)) for k in range(3)]
+        for c in clips:
+            e.set_clip_params(c, attack=0.003, decay=0.01, sustain=0.7, release=0.02, pan=0.3, length_beats=0.75)
+        for s in range(2):
+            for k in range(6):
+                e.play(clips[k % 3], loop=bool(k % 2), midi_channel=k % 3 - 2, note=55 + 2 * k + s, volume=0.8, session=s)
+        acc = {}
+        first = 0
+        for step, (nb, nf) in enumerate([(4, 256), (4, 256), (3, 256), (1, 256), (5, 128), (5, 128), (2, 512), (4, 256)]):
+            if step in (2, 5):
+                for s in range(2):
+                    e.stop(clips[step % 3], midi_channel=-2, note=55 + s, session=s, block=1 % nb)
+                    e.play(clips[(step + 1) % 3], midi_channel=-1, note=64, volume=0.5, session=s, block=nb - 1)
+            e.render(nb, nf, e.make_clocks(nb, nf, 48000.0, first_block=first))
+            first += nb
+            S.append(acc, S.collect(e))
+        e.close()
+        return S.finish(acc)
+
+    two, one, ref = run(product, True), run(product, False), run(oracle, False)
+    assert np.abs(two["master"]).max() > 0.05
+    assert not S.compare(two, one, exact_audio=True)
+    assert not S.compare(two, ref, exact_audio=True)
