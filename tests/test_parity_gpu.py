@@ -266,3 +266,37 @@ def test_stream_schedules_agree_render_after_render(product, oracle):
     assert np.abs(two["master"]).max() > 0.05
     assert not S.compare(two, one, exact_audio=True)
     assert not S.compare(two, ref, exact_audio=True)
+
+
+def test_command_ring_overflow_and_late_commands_are_dropped_like_the_reference(product, oracle):
+    """lib/SamplerSynth.cpp:32,332-334: the per-bus command ring holds 256 commands per period; what does not fit is
+    dropped, and so are commands addressed to a bus that does not exist or to a period this render does not have.
+    A burst of 300 commands on one bus in one period takes the library's sorted slow path; the same burst split over
+    two periods (150 + 150) must lose nothing on the fast path."""
+    def run(lib, split):
+        rng = np.random.default_rng(5)
+        e = Engine(lib=lib, n_sessions=2, buses_per_session=3, voices_per_bus=8)
+        c = e.add_clip(rng.uniform(-1, 1, (2, 20000)).astype(np.float32))
+        e.set_clip_params(c, attack=0.0, decay=0.0, sustain=1.0, release=0.01)
+        for k in range(300):                         # start / stop pairs and volume updates on session 1, bus 0
+            blk = (k // 150) if split else 0
+            if k % 3 == 0:
+                e.play(c, midi_channel=-2, note=48 + (k // 3) % 24, volume=0.3 + 0.002 * k, session=1, block=blk)
+            elif k % 3 == 1:
+                e.stop(c, midi_channel=-2, note=48 + (k // 3) % 24, session=1, block=blk)
+            else:
+                e.play(c, midi_channel=-2, note=72, volume=0.5, session=1, block=blk)
+        e.play(c, midi_channel=-1, note=60, session=0, block=2)          # survives: another bus, another period
+        e.play(c, midi_channel=-2, note=61, session=0, block=3)          # period 3 of a 3-period render: dropped
+        e.play(c, midi_channel=5, note=62, session=0, block=0)           # bus 7 of 3: dropped on arrival
+        e.render(3, 256, e.make_clocks(3, 256))
+        out = S.collect(e)
+        out["dropped"] = np.array([e.dropped_commands()])
+        e.close()
+        return out
+
+    for split in (False, True):
+        a, b = run(product, split), run(oracle, split)
+        assert not S.compare(a, b, exact_audio=True)
+        assert int(a["dropped"][0]) == (300 - 256 + 2 if not split else 2)
+        assert np.abs(a["raw"]).max() > 0.01
