@@ -28,11 +28,15 @@ namespace zl {
 #ifndef ZL_KT
 #define ZL_KT 128
 #endif
+// gather_kernel CTA = ONE warp = one bus: buses differ in how many voices sound, and a warp that is done hands its
+// registers and shared memory to the next bus at once instead of waiting for three CTA-mates (4-warp CTAs: 0.75 ms per
+// launch, 1-warp CTAs at the same 20 warps per SM: 0.65 ms; sized for 21 per SM ptxas settles on 78 registers and 22
+// fit beside their 9 KB of shared memory: 0.60 ms).
 #ifndef ZL_GATHER_THREADS
-#define ZL_GATHER_THREADS 128
+#define ZL_GATHER_THREADS 32
 #endif
 #ifndef ZL_GATHER_MINB
-#define ZL_GATHER_MINB 5
+#define ZL_GATHER_MINB 21
 #endif
 constexpr int kT = ZL_KT;            // frames per tile (multiple of 32)
 constexpr int kNC = kT / 32;         // 32-frame chunks per tile
@@ -42,7 +46,10 @@ constexpr int kSimpleBit = 1 << 29;   // one position segment, one envelope segm
 constexpr int kRingBit = 1 << 28;     // simple, full tile, and the source window fits one staging slot: p0b = window address, Rb = (first frame, bytes)
 constexpr int kCountMask = (1 << 20) - 1;
 constexpr int kSlotBytes = 2560;      // one staged source window: 128 frames x ratio 2.4 x 8 B + halo, copied in 512-byte rows
-constexpr int kSlots = 3;             // staging slots per warp: two windows in flight behind the one being gathered
+#ifndef ZL_SLOTS
+#define ZL_SLOTS 3
+#endif
+constexpr int kSlots = ZL_SLOTS;             // staging slots per warp: two windows in flight behind the one being gathered
 constexpr int kWantPeak = 1 << 8;     // VoiceGather.nch flag: the positions model takes this block's peak  :265-267
 
 // The gather of one voice x one tile is split in two so all of the tile's loads are in flight together:
