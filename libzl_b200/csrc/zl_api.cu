@@ -12,6 +12,11 @@
 #include <vector>
 #include <chrono>
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include "zl_device.cuh"
 
 namespace zl {
@@ -25,6 +30,7 @@ cudaError_t launch_plan(RenderParams& P, cudaStream_t stream);
 cudaError_t launch_gather(RenderParams& P, cudaStream_t stream, cudaEvent_t gatherBegin, cudaEvent_t gatherEnd);
 size_t render_scratch_bytes(int nVoices, int nframes, size_t off[5]);
 void render_bind_scratch(RenderParams& P, void* scratch, int nVoices, int nframes);
+cudaError_t launch_stop_clip_voices(VoiceDev* voices, int n, int clipId, cudaStream_t stream);
 cudaError_t launch_master_mix(const float* raw, const BusDev* buses, float* master, int nSessions, int B, int64_t stride, int64_t n, cudaStream_t stream);
 cudaError_t launch_thumb_level0(const float*, int, int, int, int, int8_t*, cudaStream_t);
 cudaError_t launch_thumb_bounds(double, double, double, int, int*, cudaStream_t);
@@ -323,7 +329,8 @@ int zl_ctx_create(const zl_config* cfg, zl_ctx** out) {
 int zl_ctx_destroy(zl_ctx* ctx) {
     if (!ctx) return ZL_ERR_INVALID;
     cudaSetDevice(ctx->device);
-    if (ctx->own) cudaStreamSynchronize(ctx->own);
+    for (cudaStream_t s : {ctx->stream, ctx->own, ctx->planStream, ctx->mixStream, ctx->copyStream})   // nothing may still run on a buffer freed below
+        if (s) cudaStreamSynchronize(s);
     for (ClipHost& c : ctx->clips) { if (c.owned && c.d_data) cudaFree(c.d_data); if (c.d_thumb) cudaFree(c.d_thumb); }
     void* frees[] = {ctx->d_clips, ctx->d_slice, ctx->d_voices, ctx->d_buses, ctx->d_cmds, ctx->d_clocks, ctx->d_pow2,
                      ctx->d_counters, ctx->d_bnd, ctx->d_px, ctx->d_mask, ctx->d_tmp, ctx->d_out[0], ctx->d_out[1],
@@ -462,18 +469,17 @@ int zl_clip_create_from_wav(zl_ctx* ctx, const void* wav, uint64_t nbytes, int32
 
 int zl_clip_create_from_wav_file(zl_ctx* ctx, const char* path, int32_t* clip_id) {
     if (!ctx || !path || !clip_id) return invalid(ctx, "clip_create_from_wav_file: null argument");
-    FILE* fp = fopen(path, "rb");
-    if (!fp) return invalid(ctx, "clip_create_from_wav_file: cannot open the file");
-    fseek(fp, 0, SEEK_END);
-    const long long n = ftell(fp);
-    fseek(fp, 0, SEEK_SET);
-    void* pinned = nullptr;                                    // page-locked: the H2D copy of the data chunk runs at PCIe rate
-    int rc = ZL_OK;
-    if (n <= 0 || cudaMallocHost(&pinned, (size_t) n) != cudaSuccess) rc = invalid(ctx, "clip_create_from_wav_file: empty file or no pinned memory");
-    else if (fread(pinned, 1, (size_t) n, fp) != (size_t) n) rc = invalid(ctx, "clip_create_from_wav_file: short read");
-    fclose(fp);
-    if (rc == ZL_OK) rc = zl_clip_create_from_wav(ctx, pinned, (uint64_t) n, clip_id);
-    if (pinned) cudaFreeHost(pinned);
+    // The file is mapped, not read into a pinned copy of itself (an hour-long recording is gigabytes): the chunk walk touches a
+    // few header pages, and the data chunk goes to the device through the driver's own bounded staging of a pageable source.
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) return invalid(ctx, "clip_create_from_wav_file: cannot open the file");
+    struct stat sb;
+    if (fstat(fd, &sb) != 0 || !S_ISREG(sb.st_mode) || sb.st_size <= 0) { close(fd); return invalid(ctx, "clip_create_from_wav_file: not a regular, non-empty file"); }
+    void* map = mmap(nullptr, (size_t) sb.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+    close(fd);
+    if (map == MAP_FAILED) return invalid(ctx, "clip_create_from_wav_file: cannot map the file");
+    const int rc = zl_clip_create_from_wav(ctx, map, (uint64_t) sb.st_size, clip_id);
+    munmap(map, (size_t) sb.st_size);
     return rc;
 }
 
@@ -497,6 +503,12 @@ int zl_clip_destroy(zl_ctx* ctx, int32_t id) {
     BIND();
     ClipHost* c = find_clip(ctx, id);
     if (!c) return invalid(ctx, "clip_destroy: unknown clip");
+    // every stream a render may still be running on, then the voices still on this clip end as by stopNote(0, false)
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->planStream) CK(cudaStreamSynchronize(ctx->planStream));
+    if (ctx->mixStream) CK(cudaStreamSynchronize(ctx->mixStream));
+    CK(launch_stop_clip_voices(ctx->d_voices, ctx->nvoices(), id, ctx->stream));
+    ctx->launches++;
     CK(cudaStreamSynchronize(ctx->stream));
     if (c->owned && c->d_data) cudaFree(c->d_data);
     if (c->d_thumb) cudaFree(c->d_thumb);
@@ -771,11 +783,6 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         CK(cudaStreamCreateWithPriority(&ctx->mixStream, cudaStreamNonBlocking, lo));
         CK(cudaEventCreateWithFlags(&ctx->evMix, cudaEventDisableTiming));
     }
-    // The command upload and the counter resets are the planner's inputs only: queued on its stream they run beside the tail
-    // of the previous render instead of between two renders (one stream: the same order as ever).
-    CK(cudaMemcpyAsync(ds, hs, slotBytes, cudaMemcpyHostToDevice, ps));
-    CK(cudaMemsetAsync(ctx->d_counters, 0, 2 * sizeof(unsigned long long), ps));
-    CK(cudaMemsetAsync(ctx->d_walkCount, 0, sizeof(int32_t) * 2 * (size_t) nblocks, ps));
     // timing 1: one event pair around the whole plan/walk/gather sequence of this call; 2: one pair per gather_kernel launch
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->timing == 1) {
@@ -795,6 +802,13 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         CK(cudaStreamWaitEvent(ps, ctx->evStart, 0));
     }
     ctx->planChained = overlap;
+    // The command upload and the counter resets are the planner's inputs only: queued on its stream they run beside the tail
+    // of the previous render instead of between two renders (one stream: the same order as ever).  They come AFTER the
+    // wait above: d_counters and d_walkCount are shared across renders, so a first two-stream render must not reset them
+    // under a one-stream render still running on the context stream.
+    CK(cudaMemcpyAsync(ds, hs, slotBytes, cudaMemcpyHostToDevice, ps));
+    CK(cudaMemsetAsync(ctx->d_counters, 0, 2 * sizeof(unsigned long long), ps));
+    CK(cudaMemsetAsync(ctx->d_walkCount, 0, sizeof(int32_t) * 2 * (size_t) nblocks, ps));
     const char* tl = ctx->timing == 2 ? nullptr : getenv("ZL_B200_TIMELINE");
     std::vector<cudaEvent_t> tlev;
     static cudaEvent_t tlBase = nullptr;

@@ -131,6 +131,7 @@ __device__ __forceinline__ bool voice_block_begin(VoiceHot& h, const RenderParam
                                                   VoiceBlockCtl& b, VoiceGather& g) {
     if (h.sound < 0) return false;
     const ClipDev& snd = P.clips[h.sound];
+    if (!snd.valid) return false;                                             // destroyed clip: zl_clip_destroy stops its voices; belt and braces
     g.data = snd.data; g.nch = snd.nch; g.sampleDuration = snd.length - 1; g.gain = h.gain;
     b.nch = snd.nch; b.clipFrames = snd.length; b.releaseArmed = 0; b.span = 0; b.spanStart = (int) h.p; b.lastPos = b.spanStart;
     if (JMODE) {

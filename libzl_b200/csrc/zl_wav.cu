@@ -62,6 +62,7 @@ int wav_parse(const void* bytes, uint64_t n, zl_wav_format* f) {
     }
     int bytesPerFrame = 0;
     while (in.pos < end && !in.exhausted()) {                                    // :979-1183
+        const uint64_t chunkHeader = in.pos;
         const uint32_t type = in.u32();
         const uint32_t length = in.u32();
         uint64_t chunkEnd = in.pos + length + (length & 1);
@@ -101,6 +102,9 @@ int wav_parse(const void* bytes, uint64_t n, zl_wav_format* f) {
             f->frames = bytesPerFrame > 0 ? (int64_t) (dataLength / (uint64_t) bytesPerFrame) : 0;
         } else if (type != tag("bext") && type != tag("smpl") && type != tag("inst") && type != tag("INST") && type != tag("cue ")
                    && type != tag("axml") && type != tag("LIST") && type != tag("acid") && type != tag("Trkn") && chunkEnd <= in.pos) break;   // :1176-1179
+        // a ds64 data length near 2^64 wraps chunkEnd back into the image (the reference's int64 sum does the same and its walk
+        // never ends on such a file): the walk stops unless the chunk ends after its own header
+        if (chunkEnd <= chunkHeader) break;
         in.pos = chunkEnd;
     }
     f->bytes_per_frame = bytesPerFrame;

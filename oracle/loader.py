@@ -58,6 +58,19 @@ def load_juceref():
     d.ref_wav_roundtrip.restype = C.c_longlong
     d.ref_wav_roundtrip.argtypes = [C.POINTER(f32p), C.c_int, C.c_longlong, C.c_double, C.c_int, C.POINTER(C.c_ubyte),
                                     C.c_longlong, C.POINTER(C.c_longlong), C.POINTER(f32p)]
+    if hasattr(d, "ref_thumb_create"):          # the reference's own juce::AudioThumbnail (oracle/ref/juce_thumb_ref.cpp)
+        u8p, i8p = C.POINTER(C.c_ubyte), C.POINTER(C.c_byte)
+        d.ref_thumb_create.restype, d.ref_thumb_create.argtypes = C.c_void_p, [u8p, C.c_longlong, C.c_int]
+        d.ref_thumb_destroy.restype, d.ref_thumb_destroy.argtypes = None, [C.c_void_p]
+        d.ref_thumb_info.restype = C.c_int
+        d.ref_thumb_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        d.ref_thumb_level0.restype, d.ref_thumb_level0.argtypes = C.c_int, [C.c_void_p, i8p]
+        d.ref_thumb_pixels.restype, d.ref_thumb_pixels.argtypes = C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_int, i8p]
+        d.ref_thumb_draw.restype = C.c_int
+        d.ref_thumb_draw.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int, C.c_int, C.c_float, u8p]
+        d.ref_thumb_save.restype, d.ref_thumb_save.argtypes = C.c_longlong, [C.c_void_p, u8p, C.c_longlong]
+        d.ref_thumb_load.restype = C.c_int
+        d.ref_thumb_load.argtypes = [u8p, C.c_longlong, C.c_int, i8p, C.c_longlong, C.POINTER(C.c_int)]
     if hasattr(d, "ref_wav_read"):
         d.ref_wav_read.restype = C.c_longlong
         d.ref_wav_read.argtypes = [C.POINTER(C.c_ubyte), C.c_longlong, C.c_longlong, C.POINTER(f32p), C.POINTER(C.c_double),

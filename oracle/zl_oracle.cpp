@@ -742,6 +742,11 @@ int zlo_clip_create_from_pcm(zl_ctx* ctx, const float* const* planar, int32_t nc
 int zlo_clip_create_from_device(zl_ctx*, const void*, int32_t, int64_t, double, int32_t*) { return ZL_ERR_INVALID; }
 int zlo_clip_destroy(zl_ctx* ctx, int32_t id) {
     Clip* c = ctx ? findClip(ctx, id) : nullptr; if (!c) return ZL_ERR_INVALID;
+    // ~ClipAudioSource calls stop() and unregisterClip (lib/ClipAudioSource.cpp:207-210), after which a voice still holding the
+    // clip would read freed memory; the boundary defines it instead: voices still on the clip end as by stopNote(0, false).
+    for (Channel& ch : ctx->channels)
+        for (Voice& v : ch.voices)
+            if (v.sound == c || v.clip == c) v.stopNote(false);
     delete c; ctx->clips[(size_t) id] = nullptr; return ZL_OK;
 }
 static void fillParams(const Clip* c, zl_clip_params* p) {
@@ -1085,6 +1090,7 @@ int zlo_wav_probe(const void* wav, uint64_t nbytes, zl_wav_format* out) {
     bool usesFloat = false;
     int64_t lengthInSamples = 0;
     while (in.at < riffEnd && in.at < in.n) {
+        const uint64_t chunkHeader = in.at;
         const uint32_t chunkType = (uint32_t) in.readLE(4);
         const uint32_t length = (uint32_t) in.readLE(4);
         uint64_t chunkEnd = in.at + length + (length & 1);
@@ -1127,6 +1133,9 @@ int zlo_wav_probe(const void* wav, uint64_t nbytes, zl_wav_format* out) {
             for (const char* k : known) isKnown = isKnown || in.is(k, chunkType);
             if (!isKnown && chunkEnd <= in.at) break;
         }
+        // A ds64 data length near 2^64 wraps chunkEnd back into the file (the reference's int64 sum does the same and its walk
+        // never ends); the boundary ends the walk there: a chunk must end after its own header.
+        if (chunkEnd <= chunkHeader) break;
         in.at = chunkEnd;
     }
     out->channels = (int32_t) numChannels; out->bits_per_sample = (int32_t) bitsPerSample; out->is_float = usesFloat ? 1 : 0;

@@ -56,3 +56,16 @@ def product():
         pytest.skip("no CUDA device")
     import libzl_b200
     return libzl_b200.load()
+
+
+@pytest.fixture(scope="session")
+def thumb_golden():
+    """Vectors from the reference's own compiled juce::AudioThumbnail (tests/golden/make_thumb_golden.py)."""
+    return np.load(os.path.join(ROOT, "tests", "golden", "juce_thumb_golden.npz"))
+
+
+@pytest.fixture(scope="session")
+def juceref_optional():
+    """oracle/_ref/libzl_juceref.so when it was built (it travels to the GPU box), else None."""
+    from oracle import loader
+    return loader.load_juceref()
