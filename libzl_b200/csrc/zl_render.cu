@@ -612,11 +612,17 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
         for (int ch = 0; ch < kNC; ++ch) acc[ch] = make_float2(0.0f, 0.0f);
         // block peak of a voice -> positions model gain  :213-216, :265
         auto take_peak = [&](float vmax, int vs, int flags) {
-            if (!JMODE && (flags & kWantPeak)) {
+            if (!JMODE) {
+                // The reduction is NOT put under the kWantPeak test: ptxas 12.9 was seen to predicate the CREDUX of that form
+                // on an unrelated live predicate (the hoisted passthrough test) while its consumers used the right one, so
+                // buses with a non-trivial passthrough took a stale uniform register for the peak.  Unconditional, the
+                // instruction carries no predicate at all; the test only guards the bookkeeping.
                 const int pk = __reduce_max_sync(FULL, __float_as_int(vmax));   // vmax >= +0: int order == float order
-                if (STAGED || V <= 32) { if (lane == vs) vpk = max(vpk, pk); }
-                else if (lane == 0 && pk > 0)
-                    atomicMax(reinterpret_cast<int*>(&P.voices[v0 + vs].posGain), __float_as_int(__fmul_rn(__int_as_float(pk), 0.5f)));
+                if (flags & kWantPeak) {
+                    if (STAGED || V <= 32) { if (lane == vs) vpk = max(vpk, pk); }
+                    else if (lane == 0 && pk > 0)
+                        atomicMax(reinterpret_cast<int*>(&P.voices[v0 + vs].posGain), __float_as_int(__fmul_rn(__int_as_float(pk), 0.5f)));
+                }
             }
         };
         // STAGED: the tile's window-staged voice-tiles, in slot order, form a queue through the kSlots slots: kSlots - 1

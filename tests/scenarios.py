@@ -197,3 +197,40 @@ def compare(a, b, audio_tol=1e-5, exact_audio=False, loose_levels=False):
             if not np.array_equal(x, y):
                 bad.append(f"{k}: integer/state mismatch ({int((x != y).sum())} of {x.size})")
     return bad
+
+
+def adsr_via_voice(lib, sr, a, d, s, r, n_on, n_total, renote=False, period=100):
+    """A juce::ADSR sequence (noteOn at 0, noteOff at frame n_on; renote: noteOff again before every later frame) taken
+    through the VOICE path of `lib`: a DC clip of 1.0 at pitch ratio 1, velocity 1, so the bus carries the envelope itself.
+    Plain sequences run in J-mode (stop command at the period that starts at n_on); renote sequences run in Z-mode with
+    only quirk Q3 on, where the one-shot's release window (lib/SamplerSynthVoice.cpp:253-256) starts after frame n_on - 1
+    and the voice ends at the stop position.  Returns (envelope, frames that are comparable)."""
+    a, d, s, r = (float(np.float32(x)) for x in (a, d, s, r))
+    n_on, n_total = int(n_on), int(n_total)
+    assert n_on % period == 0 and n_total % period == 0
+    nb = n_total // period
+    if not renote:
+        e = Engine(lib=lib, mode=K.ZL_MODE_J, sample_rate=float(sr), max_frames=period, max_blocks=nb)
+        c = e.add_clip(np.ones((2, n_total + 16), np.float32), rate=float(sr))
+        e.set_clip_params(c, attack=a, decay=d, sustain=s, release=r, root_note=60)
+        e.play(c, midi_channel=-2, note=60, volume=1.0)
+        e.stop(c, midi_channel=-2, note=60, block=n_on // period)
+        e.render(nb, period)
+        l, rr = e.bus(0, 0, K.ZL_BUS_RAW)
+        e.close()
+        assert np.array_equal(l, rr)
+        return l, n_total
+    rel_frames = int(np.ceil(np.float64(np.float32(r)) * sr))
+    stop = n_on + rel_frames - 1                     # relStart = stop - release * rate lies in (n_on - 1, n_on]
+    assert stop - np.float64(np.float32(r)) * sr <= n_on and stop - np.float64(np.float32(r)) * sr > n_on - 1
+    e = Engine(lib=lib, mode=K.ZL_MODE_Z, quirks=K.ZL_Q3_RENOTEOFF, sample_rate=float(sr), max_frames=period, max_blocks=nb)
+    c = e.add_clip(np.ones((2, n_total + 16), np.float32), rate=float(sr))
+    e.set_clip_params(c, attack=a, decay=d, sustain=s, release=r, root_note=60, pan=0.0, volume_abs=1.0,
+                      start_s=0.0, length_s=(stop + 0.5) / sr)
+    assert e.slice_bounds(c, -1) == (0, stop)
+    e.play(c, midi_channel=-2, note=60, volume=1.0)
+    e.render(nb, period)
+    l, rr = e.bus(0, 0, K.ZL_BUS_RAW)
+    e.close()
+    assert np.array_equal(l, rr)
+    return l * np.float32(2.0), min(stop, n_total)    # M/S pan at pan 0: l = 0.5 * m + 0 (exact halving)

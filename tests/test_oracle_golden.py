@@ -68,6 +68,46 @@ def test_adsr_properties_of_juce_unit_tests(oracle):
     assert e[1000] == 0.0 and e[1050] == 0.0
 
 
+def check_adsr_golden_through_voice(lib, golden):
+    """Every golden juce::ADSR sequence, replayed through the voice path of `lib` (J-mode; the renote cases through
+    Z-mode quirk Q3)."""
+    import scenarios as S
+    for i, (sr, a, d, s, r, n_on, n_total, ren) in enumerate(golden["adsr_params"]):
+        env, n = S.adsr_via_voice(lib, sr, a, d, s, r, n_on, n_total, renote=bool(ren))
+        assert n > n_on
+        assert np.array_equal(env[:n], golden[f"adsr_{i}"][:n]), f"ADSR case {i} through the voice differs from juce::ADSR"
+
+
+def test_adsr_golden_through_the_oracle_voice(oracle, golden):
+    check_adsr_golden_through_voice(oracle, golden)
+
+
+def check_adsr_properties_through_voice(lib):
+    """The assertions of ADSRTests (juce_ADSR_test.cpp:26-243) on the envelope a voice of `lib` produces."""
+    import scenarios as S
+    sr, a, d, s, r = 44100.0, 0.1, 0.1, 0.5, 0.1
+    na, nd = int(a * sr), int(d * sr)
+    n_on = ((na + nd + 5000) // 100) * 100
+    n_total = ((n_on + int(r * sr) + 300) // 100) * 100
+    env, _ = S.adsr_via_voice(lib, sr, a, d, s, r, n_on, n_total)
+    assert np.all(np.diff(env[:na - 1]) > 0), "attack strictly increasing"
+    assert np.all(np.diff(env[na + 1:na + nd - 1]) < 0), "decay strictly decreasing"
+    sus = env[na + nd + 10:n_on - 10]
+    assert sus.min() == sus.max() == np.float32(s), "sustain exact"
+    assert np.all(np.diff(env[n_on:n_on + int(r * sr) - 2]) < 0), "release strictly decreasing"
+    assert env[-1] == 0.0, "idle after release"
+    e, _ = S.adsr_via_voice(lib, sr, 0.0, d, s, r, 100, 200)
+    assert e[0] < 1.0 and e[0] > 0.99                                   # zero-length attack: decay starts from 1.0
+    e, _ = S.adsr_via_voice(lib, sr, a, 0.0, s, r, ((na + 100) // 100) * 100, ((na + 300) // 100) * 100)
+    assert e[na + 5] == np.float32(s)                                   # zero-length decay: straight to sustain
+    e, _ = S.adsr_via_voice(lib, sr, a, d, s, 0.0, 1000, 1100)
+    assert e[1000] == 0.0 and e[1050] == 0.0                            # zero-length release: idle at once
+
+
+def test_adsr_properties_through_the_oracle_voice(oracle):
+    check_adsr_properties_through_voice(oracle)
+
+
 def _run_jmode(lib, p, pcm):
     nch, n, rate, orate, root, note, vel, att, rel, nb, nf, off = p
     e = Engine(lib=lib, mode=K.ZL_MODE_J, sample_rate=float(orate), max_frames=1024, max_blocks=64)

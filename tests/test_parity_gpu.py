@@ -133,6 +133,79 @@ def test_golden_jmode_vectors_on_gpu(product, golden):
         assert np.array_equal(l, golden[f"j_L_{i}"]) and np.array_equal(r, golden[f"j_R_{i}"]), i
 
 
+def test_golden_adsr_sequences_on_gpu(product, golden):
+    """The committed juce::ADSR vectors (from the reference's own compiled object) replayed through the DEVICE voice:
+    J-mode for the plain sequences, Z-mode quirk Q3 for the re-armed noteOff ones."""
+    from test_oracle_golden import check_adsr_golden_through_voice
+    check_adsr_golden_through_voice(product, golden)
+
+
+def test_adsr_unit_test_properties_on_the_device_envelope(product):
+    """ADSRTests (juce_ADSR_test.cpp:26-243) ported: monotone attack / decay / release, exact sustain, zero-length
+    segments - on the envelope the device voice produces."""
+    from test_oracle_golden import check_adsr_properties_through_voice
+    check_adsr_properties_through_voice(product)
+
+
+def test_unsynced_one_period_render_then_multi_period_render(product, oracle):
+    """A one-stream render (one period) immediately followed - no host sync - by a two-stream render: the second render's
+    counter resets and command upload (planner stream) must wait for the first (context stream)."""
+    def run(lib):
+        rng = np.random.default_rng(33)
+        e = Engine(lib=lib, n_sessions=64, buses_per_session=4, voices_per_bus=8, max_frames=512, max_blocks=8)
+        clips = [e.add_clip(rng.uniform(-1, 1, (2, 30000)).astype(np.float32)) for _ in range(3)]
+        for c in clips:
+            e.set_clip_params(c, attack=0.004, decay=0.02, sustain=0.6, release=0.03, pan=-0.3, length_beats=0.75)
+        for s in range(64):
+            for k in range(16):
+                e.play(clips[k % 3], loop=bool(k % 3 == 0), midi_channel=k % 4 - 2, note=50 + k + s % 7, volume=0.7, session=s)
+        outs = []
+        first = 0
+        for rep in range(6):
+            for s in range(0, 64, 5):
+                e.play(clips[rep % 3], midi_channel=rep % 4 - 2, note=70 + rep, volume=0.5, session=s, block=0)
+            e.render(1, 512, e.make_clocks(1, 512, first_block=first)); first += 1          # one stream
+            m1 = None
+            for s in range(0, 64, 7):
+                e.stop(clips[rep % 3], midi_channel=rep % 4 - 2, note=70 + rep, session=s, block=1)
+            e.render(6, 512, e.make_clocks(6, 512, first_block=first)); first += 6          # two streams, queued right behind
+            outs.append((e.master_all().copy(), e.block_levels()[0].copy(), e.voice_frames()))
+        e.close()
+        return outs
+    for (m0, p0, v0), (m1, p1, v1) in zip(run(product), run(oracle)):
+        assert np.array_equal(m0, m1) and np.array_equal(p0, p1) and v0 == v1
+        assert np.abs(m0).max() > 0.05
+
+
+def test_destroying_a_clip_in_use_stops_its_voices(product, oracle):
+    """zl_clip_destroy while voices still play the clip: they end as by stopNote(0, false) (both modes), the slots are
+    free again, other clips keep sounding, and nothing reads the freed PCM."""
+    for mode in (K.ZL_MODE_Z, K.ZL_MODE_J):
+        def run(lib):
+            rng = np.random.default_rng(8)
+            e = Engine(lib=lib, mode=mode, n_sessions=2, buses_per_session=2, voices_per_bus=4)
+            a = e.add_clip(rng.uniform(-1, 1, (2, 20000)).astype(np.float32))
+            b = e.add_clip(rng.uniform(-1, 1, (2, 20000)).astype(np.float32))
+            for s in range(2):
+                for k in range(4):
+                    e.play(a if k % 2 else b, loop=bool(k == 0), midi_channel=k % 2 - 2, note=60 + k, volume=0.6, session=s)
+            e.render(2, 256)
+            r0 = S.collect(e)
+            lib.clip_destroy(e.ctx, a)
+            e.render(2, 256, e.make_clocks(2, 256, first_block=2))
+            r1 = S.collect(e)
+            for s in range(2):                                   # the freed slots take new voices
+                e.play(b, midi_channel=-1, note=72, volume=0.4, session=s)
+                e.play(b, midi_channel=-1, note=74, volume=0.4, session=s)
+            e.render(2, 256, e.make_clocks(2, 256, first_block=4))
+            r2 = S.collect(e)
+            e.close()
+            return r0, r1, r2
+        for x, y in zip(run(product), run(oracle)):
+            assert not S.compare(x, y, exact_audio=True)
+        assert np.all(run(product)[1]["v_clip"] != 0) and np.any(run(product)[1]["v_clip"] == 1)
+
+
 def test_native_library_is_what_ran(product):
     e = Engine(lib=product)
     c = e.add_clip(S.noise_clip(1, 2000))
