@@ -759,7 +759,8 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     P.walkCount = ctx->d_walkCount;
     // Two streams: plan/walk of period b + 1 (high priority) run beside the gather of period b.  The positions-model gain
     // is then written by the gather alone (V <= 32); with more voices per bus it needs the planner's reset first -> one stream.
-    const bool overlap = ctx->overlapEnabled && ctx->cfg.voices_per_bus <= 32 && nblocks > 1;
+    static const bool noOverlapEnv = env_int("ZL_B200_NO_OVERLAP", 0) != 0;        // experiment knob: everything on one stream
+    const bool overlap = ctx->overlapEnabled && !noOverlapEnv && ctx->cfg.voices_per_bus <= 32 && nblocks > 1;
     if (overlap && !ctx->planStream) {
         int lo = 0, hi = 0;
         CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));

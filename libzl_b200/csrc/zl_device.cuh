@@ -107,6 +107,7 @@ struct RenderParams {
     int32_t* walkCount;      // [nblocks][2] queue lengths: serial walkers (front of the queue), others (back); zeroed per launch
     int32_t nVoices, tilesPerBlock, blk, planBusesPerCta;
     int32_t planGroups, planCtaCap, walkCtaCap;     // bus groups of plan_kernel; grid caps beside a running gather (0 = none)
+    int32_t dbgFlags;                               // profiling aid (ZL_B200_DEBUG_SKIP bit 4): plan_kernel queues nothing, walk_kernel runs empty
 };
 
 // ---------------------------------------------------------------------------------------------

@@ -21,6 +21,8 @@
 //                  stores.  No shared memory, no barriers; small enough to stay in the instruction cache and to run at
 //                  high occupancy, which is what hides the HBM latency of the gather.
 //   master_mix_kernel  the JACK port mix of each session's dry outputs (the only cross-bus step), once per launch.
+#include <cstdlib>
+
 #include "zl_voice.cuh"
 
 namespace zl {
@@ -38,6 +40,8 @@ namespace zl {
 #ifndef ZL_GATHER_MINB
 #define ZL_GATHER_MINB 28
 #endif
+#define ZL_LAUNCH(kernel, grid, block, stream, ...) kernel<<<grid, block, 0, stream>>>(__VA_ARGS__)
+
 constexpr int kT = ZL_KT;            // frames per tile (multiple of 128)
 constexpr int kNC = kT / 32;         // 32-frame chunks per tile
 constexpr int kG = 4;                // chunks gathered together (all their loads in flight at once); a tile is kNG such groups
@@ -251,7 +255,35 @@ __device__ __forceinline__ int plan_voice_block(const RenderParams& P, int vIdx,
     // position, release window) until the end of the block: every tile is one (p0, R) segment with a constant
     // envelope, exactly what the generic planner below would produce tile by tile.
     bool fast = false;
-    if (active && h.adsrState == kSustain) {
+    // The envelope of the whole period as ONE exact-linear run e(c) = e0 + c E (zl_voice.cuh): sustain (E = 0), or an attack
+    // under way / a decay / a plain release that stays inside one f32 binade and short of its next state until the period
+    // ends.  The generic planner would find the same run tile by tile (each tile's first step RN(e + rate) lands on the same
+    // grid), so the descriptors - and the voice's state after the period - are identical.
+    float envE0 = h.sustain, envE = 0.0f, envLast = h.sustain;
+    bool envOk = h.adsrState == kSustain;
+    if (active && !envOk && nframes > 1) {
+        const int st = h.adsrState;
+        if (JMODE && st == kIdle) { envOk = true; envE0 = 0.0f; envLast = h.env; }
+        else if ((st == kAttack && h.env > 0.0f) || st == kDecay || st == kRelease) {
+            VoiceHot hc = h;
+            const float e0 = adsr_next(hc);                        // exact step; may clamp and change state
+            const float step = st == kAttack ? h.aRate : (st == kDecay ? h.dRate : h.rRate);
+            float E, topF, bottomF;
+            if (hc.adsrState == st && binade_step_f(e0, step, E, topF, bottomF)) {
+                const int X = nframes - 1;
+                int x;
+                if (st == kAttack) x = env_run_up(e0, E, fminf(1.0f, topF), X);
+                else {
+                    const float floorUp = __int_as_float(__float_as_int(bottomF) + 1);
+                    const float lim = st == kDecay ? fmaxf(floorUp, __int_as_float(__float_as_int(h.sustain) + 1)) : floorUp;
+                    x = env_run_down(e0, E, lim, X);
+                    E = -E;
+                }
+                if (x == X) { envOk = true; envE0 = e0; envE = E; envLast = __fmaf_rn((float) X, E, e0); }
+            }
+        }
+    }
+    if (active && envOk) {
         double R, top;
         if (binade_step(h.p, h.ratio, R, top)) {
             const double q = __fma_rn((double) nframes, R, h.p);   // position after the block's last increment
@@ -263,7 +295,7 @@ __device__ __forceinline__ int plan_voice_block(const RenderParams& P, int vIdx,
                     const int n = min(kT, nframes - t0);
                     TileDesc d;
                     d.p0a = __fma_rn((double) t0, R, h.p); d.Ra = R; d.p0b = 0.0; d.Rb = 0.0;
-                    d.e0a = h.sustain; d.Ea = 0.0f; d.e0b = 0.0f; d.Eb = 0.0f;
+                    d.e0a = __fmaf_rn((float) t0, envE, envE0); d.Ea = envE; d.e0b = 0.0f; d.Eb = 0.0f;   // exact: the run stays on one grid
                     d.cb = n; d.ce = n; d.ct = INT_MAX;
                     const int lastPos = (int) __fma_rn((double) (t0 + n - 1), R, h.p);
                     d.nrend = n | ((bc.nch == 2 && (JMODE || lastPos < sampleDuration)) ? kSimpleBit : 0);
@@ -271,7 +303,7 @@ __device__ __forceinline__ int plan_voice_block(const RenderParams& P, int vIdx,
                     P.descs[(size_t) t * P.nVoices + vIdx] = d;
                     bc.lastPos = lastPos;
                 }
-                h.p = q; h.env = h.sustain;
+                h.p = q; h.env = envLast;
                 nrendBlock = nframes;
             }
         }
@@ -388,6 +420,7 @@ __global__ void __launch_bounds__(MAXT, MAXT == 128 ? ZL_PLAN_MINB : 1) plan_ker
     if (hasVoice) {
         unsigned long long a = 0, b = 0;
         kind = plan_voice_block<JMODE, Q3, true>(P, vIdx, gb, a, b);
+        if (P.dbgFlags & 4) kind = 0;
         nVoiceFrames += a; nSrcFloats += b;
     }
     // queue the deferred voices of this warp: serial walkers from the front of the queue, the others from its back; one
@@ -537,7 +570,9 @@ __device__ __forceinline__ float gather_finish_ring(const TileDesc& d, const Voi
     return gather_finish<JMODE, Q1, true>(g, t, kG, nz, acc);
 }
 
-template <bool JMODE, bool Q1, bool Q2, bool STAGED>
+// LEAN: only the raw SamplerChannel ports (and what the master mix and the meters need) are materialised - no dry / fx planes,
+// no sum of squares: the per-chunk epilogue then carries none of their tests (the offline-render configuration).
+template <bool JMODE, bool Q1, bool Q2, bool STAGED, bool LEAN>
 __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kernel(const RenderParams P) {
     constexpr int QS = Q2 ? 1 : 0;                            // frame f lands at output index f + QS   :218-221
     constexpr int W = ZL_GATHER_THREADS / 32;
@@ -568,6 +603,8 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
     int pkL = 0, pkR = 0;
     double sqL = 0.0, sqR = 0.0;
     int vpk = 0;                                              // V <= 32: lane vs keeps voice vs's block peak (float bits, >= +0)
+    float* const __restrict__ out0L = P.out[0] ? P.out[0] + rowL + QS : nullptr;   // LEAN: the raw rows of this bus and period
+    float* const __restrict__ out0R = P.out[0] ? P.out[0] + rowR + QS : nullptr;
 #if ZL_TMA
     // staging queue state: slots are written and read round-robin; a slot's barrier phase flips every time it goes round
     const uint32_t bar0 = (uint32_t) __cvta_generic_to_shared(&sBar[warp][0]);
@@ -711,7 +748,14 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
         for (int ch = 0; ch < kNC; ++ch) {
             const int c = ch * 32 + lane;
             const int j = t0 + c + QS;                            // output index in the block
-            if (c < n && j < nframes) {
+            if (LEAN) {
+                if (c < n && j < nframes) {
+                    float dL, dR;
+                    if (out0L) { out0L[t0 + c] = acc[ch].x; out0R[t0 + c] = acc[ch].y; }
+                    passthrough_pair(pt, pt.dry_amount, acc[ch].x, acc[ch].y, dL, dR);
+                    pkL = max(pkL, peak_int(dL)); pkR = max(pkR, peak_int(dR));
+                }
+            } else if (c < n && j < nframes) {
                 float dL, dR;
                 if (P.out[0]) { P.out[0][rowL + j] = acc[ch].x; P.out[0][rowR + j] = acc[ch].y; }
                 passthrough_pair(pt, pt.dry_amount, acc[ch].x, acc[ch].y, dL, dR);
@@ -869,23 +913,24 @@ cudaError_t launch_plan(RenderParams& P, cudaStream_t stream) {
     static const int dbgSkip = [] { const char* e = getenv("ZL_B200_DEBUG_SKIP"); return e ? atoi(e) : 0; }();
     static int dbgCalls = 0;
     const int skip = (dbgSkip && ++dbgCalls > 96) ? dbgSkip : 0;
+    P.dbgFlags = skip & 4;
     if (skip & 1) {
     } else if (planThreads <= 128) {
-        if (P.mode == ZL_MODE_J) plan_kernel<true, false, 128><<<planGrid, planThreads, 0, stream>>>(P);
-        else if (q3) plan_kernel<false, true, 128><<<planGrid, planThreads, 0, stream>>>(P);
-        else plan_kernel<false, false, 128><<<planGrid, planThreads, 0, stream>>>(P);
+        if (P.mode == ZL_MODE_J) ZL_LAUNCH((plan_kernel<true, false, 128>), planGrid, planThreads, stream, P);
+        else if (q3) ZL_LAUNCH((plan_kernel<false, true, 128>), planGrid, planThreads, stream, P);
+        else ZL_LAUNCH((plan_kernel<false, false, 128>), planGrid, planThreads, stream, P);
     } else {
-        if (P.mode == ZL_MODE_J) plan_kernel<true, false, 1024><<<planGrid, planThreads, 0, stream>>>(P);
-        else if (q3) plan_kernel<false, true, 1024><<<planGrid, planThreads, 0, stream>>>(P);
-        else plan_kernel<false, false, 1024><<<planGrid, planThreads, 0, stream>>>(P);
+        if (P.mode == ZL_MODE_J) ZL_LAUNCH((plan_kernel<true, false, 1024>), planGrid, planThreads, stream, P);
+        else if (q3) ZL_LAUNCH((plan_kernel<false, true, 1024>), planGrid, planThreads, stream, P);
+        else ZL_LAUNCH((plan_kernel<false, false, 1024>), planGrid, planThreads, stream, P);
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     const int wGrid = min((P.nVoices + 31) / 32 + 1, P.walkCtaCap > 0 ? P.walkCtaCap : 148 * 16);
     if (skip & 2) return cudaSuccess;
-    if (P.mode == ZL_MODE_J) walk_kernel<true, false><<<wGrid, 32, 0, stream>>>(P);
-    else if (q3) walk_kernel<false, true><<<wGrid, 32, 0, stream>>>(P);
-    else walk_kernel<false, false><<<wGrid, 32, 0, stream>>>(P);
+    if (P.mode == ZL_MODE_J) ZL_LAUNCH((walk_kernel<true, false>), wGrid, 32, stream, P);
+    else if (q3) ZL_LAUNCH((walk_kernel<false, true>), wGrid, 32, stream, P);
+    else ZL_LAUNCH((walk_kernel<false, false>), wGrid, 32, stream, P);
     return cudaGetLastError();
 }
 
@@ -895,10 +940,13 @@ cudaError_t launch_gather(RenderParams& P, cudaStream_t stream, cudaEvent_t gath
     if (gatherBegin && (e = cudaEventRecord(gatherBegin, stream)) != cudaSuccess) return e;
     const int gGrid = (nBuses + ZL_GATHER_THREADS / 32 - 1) / (ZL_GATHER_THREADS / 32);
     const bool q1 = (P.quirks & ZL_Q1_TAP_GAIN) != 0, q2 = (P.quirks & ZL_Q2_PREINC) != 0;
+    const bool lean = !P.out[1] && !P.out[2] && !P.out[3] && !P.sumsq;
 #define ZL_LAUNCH_GATHER(J, A, B2)                                                                          \
     do {                                                                                                   \
-        if (V <= kStageV) gather_kernel<J, A, B2, true><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);       \
-        else gather_kernel<J, A, B2, false><<<gGrid, ZL_GATHER_THREADS, 0, stream>>>(P);                   \
+        if (V <= kStageV) {                                                                                \
+            if (lean) ZL_LAUNCH((gather_kernel<J, A, B2, true, true>), gGrid, ZL_GATHER_THREADS, stream, P);  \
+            else ZL_LAUNCH((gather_kernel<J, A, B2, true, false>), gGrid, ZL_GATHER_THREADS, stream, P);      \
+        } else ZL_LAUNCH((gather_kernel<J, A, B2, false, false>), gGrid, ZL_GATHER_THREADS, stream, P);       \
     } while (0)
     if (P.mode == ZL_MODE_J) ZL_LAUNCH_GATHER(true, false, false);
     else if (q1 && q2) ZL_LAUNCH_GATHER(false, true, true);

@@ -1,0 +1,7 @@
+// shim: lib/JUCEHeaders.h and lib/Helper.h name these tracktion_engine types in declarations only
+#pragma once
+#include <juce_core/juce_core.h>
+namespace tracktion_engine {
+class Engine; class Edit; class AudioTrack; class AudioFile; class AudioFileInfo;
+class WaveAudioClip : public juce::ReferenceCountedObject { public: using Ptr = juce::ReferenceCountedObjectPtr<WaveAudioClip>; };
+}

@@ -1,0 +1,20 @@
+#!/bin/bash
+cd "$GRAFT_REPO_ROOT" || exit 1
+O=gpurun_out; mkdir -p $O
+B="python bench.py --steps 8 --warmup 3 --no-cpu-baseline --no-latency --no-thumb"
+sum() { python - "$1" "$2" <<'PY'
+import json,sys
+try:
+    j=json.loads(open(sys.argv[2]).read().strip().splitlines()[-1]); r=j["roofline"]
+    print(f'{sys.argv[1]:28s} ms/step {j["ms_per_step"]:.3f} vf/s {j["value"]:.4g} e2e {j["e2e"]["value"]:.4g} gather_live {r["kernel_ms"]:.4f} alone {r["kernel_alone_ms"]:.4f} frac {r["frac"]:.3f} whole {r["whole_step_frac"]:.3f}')
+except Exception as ex:
+    print(sys.argv[1], "FAILED", ex)
+PY
+}
+: > $O/b7_summary.txt
+timeout 300 $B > $O/b7_default.json 2> $O/b7_default.err; sum "same carveout" $O/b7_default.json >> $O/b7_summary.txt
+ZL_B200_SAME_CARVEOUT=0 timeout 300 $B > $O/b7_off.json 2> $O/b7_off.err; sum "default carveouts" $O/b7_off.json >> $O/b7_summary.txt
+ZL_B200_PLAN_PRIORITY=low timeout 300 $B > $O/b7_low.json 2> $O/b7_low.err; sum "same carveout, planner low" $O/b7_low.json >> $O/b7_summary.txt
+ZL_B200_NO_OVERLAP=1 timeout 300 $B > $O/b7_noovl.json 2> $O/b7_noovl.err; sum "same carveout, one stream" $O/b7_noovl.json >> $O/b7_summary.txt
+timeout 600 ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum --clock-control none -k regex:"plan_kernel|walk_kernel|gather_kernel|master_mix" -s 64 -c 64 --csv --log-file $O/b7_launches.csv python bench.py --steps 1 --warmup 2 --no-cpu-baseline --no-latency --no-thumb > $O/b7_ncu.log 2>&1
+cat $O/b7_summary.txt

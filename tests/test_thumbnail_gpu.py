@@ -105,7 +105,8 @@ def test_cfg4_full_size_one_hour_clip_bit_exact(product, oracle, juceref_optiona
     assert got[0].shape == (2, 337501, 2) and np.all(got[0][:, -1] == 0)
     for k, (x, y) in enumerate(zip(got, exp)):
         assert x.shape == y.shape and np.array_equal(x, y), f"product vs oracle: item {k}"
-    assert got[0].min() == -128 and got[0].max() == 127 and got[-1].sum() > 100000
+    assert got[0].min() == -127 and got[0].max() == 127      # a 16-bit file reaches -1.0 = -127 and +32767/32768 = 127; -128 needs a float file (golden case b)
+    assert got[-1].sum() > 100000
     if juceref_optional is not None and hasattr(juceref_optional, "ref_thumb_create"):
         th = T.RefThumb(juceref_optional, img, 512)
         ref = [th.level0()] + [th.pixels(a, b, w) for a, b, w in windows] + [th.raster(0, 0.0, dur, 4096, 400, 1.0)]
