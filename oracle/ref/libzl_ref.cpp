@@ -36,6 +36,7 @@
 
 #include <cstdarg>
 #include <cstring>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -46,7 +47,8 @@ extern "C" long long zl_ref_shim_now_msecs = 1000000;
 struct _jack_port {
     std::string name; unsigned long flags = 0; bool midi = false;
     std::vector<float> buf;              // nframes + 1: quirk Q2 writes index nframes (lib/SamplerSynthVoice.cpp:218-221)
-    _jack_port* source = nullptr;        // an input port reads its source's buffer
+    _jack_port* source = nullptr;        // an input port with one connection reads its source's buffer
+    std::vector<_jack_port*> mix;        // more than one: the sum of the sources in connection order (what jackd's mixdown does)
 };
 struct _jack_client {
     std::string name; JackProcessCallback cb = nullptr; void* arg = nullptr; bool active = false;
@@ -97,7 +99,17 @@ int jack_connect(jack_client_t*, const char* src, const char* dst) {
     d->source = s; return 0;
 }
 int jack_disconnect(jack_client_t*, const char*, const char* dst) { if (_jack_port* d = findPort(dst)) d->source = nullptr; return 0; }
-void* jack_port_get_buffer(jack_port_t* p, jack_nframes_t) { return (p->source ? p->source : p)->buf.data(); }
+void* jack_port_get_buffer(jack_port_t* p, jack_nframes_t nframes) {
+    if (!p->mix.empty()) {
+        for (jack_nframes_t f = 0; f < nframes; ++f) {
+            float acc = p->mix[0]->buf[f];
+            for (size_t k = 1; k < p->mix.size(); ++k) acc += p->mix[k]->buf[f];
+            p->buf[f] = acc;
+        }
+        return p->buf.data();
+    }
+    return (p->source ? p->source : p)->buf.data();
+}
 const char* jack_port_name(const jack_port_t* p) { return p->name.c_str(); }
 int jack_port_flags(const jack_port_t* p) { return (int) p->flags; }
 jack_port_t* jack_port_by_id(jack_client_t*, jack_port_id_t) { return nullptr; }
@@ -131,7 +143,8 @@ public:
     static void handle(ClipCommand* c, quint64 tick) { SamplerSynth::instance()->handleClipCommand(c, tick); }
     static void enable(int channel, bool en) { SamplerSynth::instance()->setChannelEnabled(channel, en); }
 };
-SyncTimer::SyncTimer(QObject* parent) : QObject(parent), d(new SyncTimerPrivate) {}
+namespace { SyncTimerPrivate* gTimerPrivate = nullptr; }
+SyncTimer::SyncTimer(QObject* parent) : QObject(parent), d(new SyncTimerPrivate) { gTimerPrivate = d; }
 SyncTimer::~SyncTimer() { delete d; }
 float SyncTimer::subbeatCountToSeconds(quint64 bpm, quint64 beats) const { return (float) ((beats * 60.0) / (bpm * 96.0)); }   // unused by process()
 int SyncTimer::getMultiplier() { return 96; }                                 // BeatSubdivisions  lib/SyncTimer.cpp:95,946-948
@@ -145,8 +158,8 @@ extern "C" QObject* SyncTimer_instance() { return SyncTimer::instance(); }
 
 // ---------------------------------------------------------------------------------------------------------------------
 // ClipAudioSource: the class lib/ClipAudioSource.h declares, as the parameter holder the voice and the sound query
-class ClipAudioSource::Private {
-public:
+namespace {
+struct ClipData {
     std::vector<std::vector<float>> pcm;       // the "file": planar channels
     double rate = 48000.0;
     float startPositionInSeconds = 0.0f, lengthInSeconds = -1.0f, lengthInBeats = -1.0f, volumeAbsolute = -1.0f, pan = 0.0f;
@@ -156,10 +169,14 @@ public:
     ClipAudioSourcePositionsModel* positionsModel = nullptr;
     std::string path = "memory";
 };
+std::map<const ClipAudioSource*, ClipData*> gClipData;     // the class keeps its d pointer private; the driver goes through this
+}  // namespace
+class ClipAudioSource::Private : public ClipData {};
 ClipAudioSource::ClipAudioSource(tracktion_engine::Engine*, SyncTimer*, const char*, bool, QObject* parent) : QObject(parent), d(new Private) {
     d->positionsModel = new ClipAudioSourcePositionsModel(this);
+    gClipData[this] = d;
 }
-ClipAudioSource::~ClipAudioSource() { delete d->positionsModel; delete d; }
+ClipAudioSource::~ClipAudioSource() { gClipData.erase(this); delete d->positionsModel; delete d; }
 float ClipAudioSource::getStartPosition(int slice) const {                    // lib/ClipAudioSource.cpp:261-268
     if (slice > -1 && slice < d->slicePositionsCache.length()) return d->startPositionInSeconds + (d->lengthInSeconds * d->slicePositionsCache[slice]);
     return d->startPositionInSeconds;
@@ -186,10 +203,10 @@ public:
     double sourceSampleRate = 0.0;
     ClipAudioSource* clip = nullptr;
 };
-namespace { ClipAudioSource::Private* gLastClipPrivate = nullptr; }
+namespace { ClipData* gLastClipPrivate = nullptr; }
 SamplerSynthSound::SamplerSynthSound(ClipAudioSource* clip) : juce::SynthesiserSound(), d(new SamplerSynthSoundPrivate) {
     d->clip = clip;
-    ClipAudioSource::Private* cp = gLastClipPrivate;                           // loadSoundData  lib/SamplerSynthSound.cpp:28-59
+    ClipData* cp = gLastClipPrivate;                                           // loadSoundData  lib/SamplerSynthSound.cpp:28-59
     d->sourceSampleRate = cp->rate;
     if (d->sourceSampleRate > 0 && !cp->pcm.empty() && !cp->pcm[0].empty()) {
         d->length = (int) cp->pcm[0].size();
@@ -263,8 +280,7 @@ ZLREF int zlref_init(double sample_rate, int max_frames) {
 // ClipAudioSource_new + SamplerSynth::registerClip over in-memory PCM; returns the clip index
 ZLREF int zlref_clip_new(const float* const* planar, int nch, long long n, double rate) {
     auto* clip = new ClipAudioSource(nullptr, SyncTimer::instance(), "memory");
-    ClipAudioSource::Private* d = *reinterpret_cast<ClipAudioSource::Private**>(reinterpret_cast<char*>(clip) + sizeof(QObject));
-    // (the d pointer is the first data member after the QObject base - see lib/ClipAudioSource.h:233-235)
+    ClipData* d = gClipData[clip];
     d->pcm.resize((size_t) nch);
     for (int ch = 0; ch < nch; ++ch) d->pcm[(size_t) ch].assign(planar[ch], planar[ch] + n);
     d->rate = rate;
@@ -283,7 +299,7 @@ ZLREF int zlref_clip_new(const float* const* planar, int nch, long long n, doubl
 ZLREF int zlref_clip_set(int clip, float start_s, float length_s, float length_beats, float pan, float volume_abs,
                          float attack, float decay, float sustain, float release, int root_note, const double* slices, int n_slices) {
     if (clip < 0 || clip >= (int) gWorld.clips.size()) return -1;
-    ClipAudioSource::Private* d = *reinterpret_cast<ClipAudioSource::Private**>(reinterpret_cast<char*>(gWorld.clips[(size_t) clip]) + sizeof(QObject));
+    ClipData* d = gClipData[gWorld.clips[(size_t) clip]];
     d->startPositionInSeconds = start_s; d->lengthInSeconds = length_s; d->lengthInBeats = length_beats; d->pan = pan;
     d->volumeAbsolute = volume_abs; d->rootNote = root_note;
     d->adsr.setParameters(juce::ADSR::Parameters(attack, decay, sustain, release));
@@ -316,10 +332,12 @@ ZLREF int zlref_process(int nframes, unsigned long long current_usecs, unsigned 
                         unsigned long long playhead_usecs, unsigned long long subbeat_usecs) {
     if (!gWorld.ready || nframes > gWorld.nframesMax) return -1;
     gJack.currentUsecs = current_usecs; gJack.nextUsecs = next_usecs; gJack.periodUsecs = (float) (next_usecs - current_usecs);
-    SyncTimerPrivate* st = *reinterpret_cast<SyncTimerPrivate**>(reinterpret_cast<char*>(SyncTimer::instance()) + sizeof(QObject));
+    SyncTimer::instance();
+    SyncTimerPrivate* st = gTimerPrivate;
     st->jackPlayhead = playhead; st->jackPlayheadUsecs = playhead_usecs; st->jackSubbeatLengthInMicroseconds = subbeat_usecs;
     for (int b = 0; b < 12; ++b) { _jack_client* c = channelClient(b); if (c && c->cb) c->cb((jack_nframes_t) nframes, c->arg); }
     for (int b = 0; b < 12; ++b) { _jack_client* c = passthroughClient(b); if (c && c->cb) c->cb((jack_nframes_t) nframes, c->arg); }
+    for (auto* c : gJack.clients) if (c->name.rfind("AudioLevels-", 0) == 0 && c->cb) c->cb((jack_nframes_t) nframes, c->arg);
     gJack.currentFrames += (jack_nframes_t) nframes;
     zl_ref_shim_now_msecs += 1;                     // the positions model only compares against "a second ago"
     return 0;
@@ -348,5 +366,13 @@ ZLREF int zlref_clip_positions(int clip, long long* ids, float* gains, float* pr
     return n;
 }
 ZLREF void zlref_set_clock_msecs(long long t) { zl_ref_shim_now_msecs = t; }
+// jack_connect by full port names; a destination with several sources gets their sum in connection order
+ZLREF int zlref_connect(const char* src, const char* dst) {
+    _jack_port* s = findPort(src); _jack_port* d = findPort(dst);
+    if (!s || !d) return -1;
+    if (d->source && d->mix.empty()) d->mix.push_back(d->source);
+    if (!d->mix.empty()) d->mix.push_back(s); else d->source = s;
+    return 0;
+}
 
 }  // extern "C"

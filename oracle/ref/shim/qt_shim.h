@@ -44,6 +44,7 @@ namespace Qt {
 enum ItemDataRole { DisplayRole = 0, UserRole = 0x0100 };
 enum ConnectionType { AutoConnection, DirectConnection, QueuedConnection, BlockingQueuedConnection };
 enum TimerType { PreciseTimer, CoarseTimer };
+enum DateFormat { TextDate, ISODate };
 }
 
 template <typename T> inline const T& qMin(const T& a, const T& b) { return (a < b) ? a : b; }
@@ -105,6 +106,11 @@ public:
     QString& operator+=(const QString& o) { s_ += o.s_; return *this; }
     bool startsWith(const QString& p) const { return s_.compare(0, p.s_.size(), p.s_) == 0; }
     bool endsWith(const QString& p) const { return s_.size() >= p.s_.size() && s_.compare(s_.size() - p.s_.size(), p.s_.size(), p.s_) == 0; }
+    QString left(int n) const { return n < 0 ? *this : QString(s_.substr(0, (size_t) n)); }
+    QString mid(int pos, int n = -1) const { return QString(n < 0 ? s_.substr((size_t) pos) : s_.substr((size_t) pos, (size_t) n)); }
+    int lastIndexOf(char c) const { const size_t p = s_.rfind(c); return p == std::string::npos ? -1 : (int) p; }
+    int indexOf(char c) const { const size_t p = s_.find(c); return p == std::string::npos ? -1 : (int) p; }
+    bool contains(const QString& o) const { return s_.find(o.s_) != std::string::npos; }
     const std::string& str() const { return s_; }
 private:
     std::string s_;
@@ -300,6 +306,14 @@ extern "C" long long zl_ref_shim_now_msecs;
 class QDateTime {
 public:
     static qint64 currentMSecsSinceEpoch() { return zl_ref_shim_now_msecs; }
+    static QDateTime currentDateTime() { return QDateTime(); }
+    QString toString(Qt::DateFormat = Qt::TextDate) const { return QString("1970-01-01T00:00:00"); }
+};
+class QDir {
+public:
+    QDir() {}
+    bool exists(const QString& path) const;          // oracle/ref/libzl_ref.cpp (std::filesystem)
+    bool mkpath(const QString& path) const;
 };
 
 class QModelIndex {

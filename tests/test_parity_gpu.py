@@ -206,6 +206,22 @@ def test_destroying_a_clip_in_use_stops_its_voices(product, oracle):
         assert np.all(run(product)[1]["v_clip"] != 0) and np.any(run(product)[1]["v_clip"] == 1)
 
 
+@pytest.mark.parametrize("name", ["single_one_shot", "single_position_loop", "polyphonic_seed2", "polyphonic_seed7_ragged",
+                                  "sketch_beat_aligned", "sketch_position_loops"])
+def test_device_matches_the_reference_compiled_hot_path(product, name):
+    """The product against the reference's OWN compiled SamplerSynthVoice / SamplerChannel / JackPassthrough / positions model
+    / AudioLevels (oracle/ref/libzl_ref.cpp): through the committed digests of the reference's outputs and, where oracle/_ref
+    travelled to this box, against the reference run live - bit for bit (audio planes, integer meter peaks, positions)."""
+    import json, os
+    import libref as R
+    golden = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "libzl_digests.json")))
+    ops = R.SCENARIOS[name]()
+    got = R.run_engine(product, ops)
+    if R.available():
+        assert not R.compare(R.run_reference(ops), got, skip_buses=R.disabled_buses(ops))
+    assert R.digest(got, R.disabled_buses(ops)) == golden[name]
+
+
 def test_native_library_is_what_ran(product):
     e = Engine(lib=product)
     c = e.add_clip(S.noise_clip(1, 2000))
