@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--cpu-sessions", type=int, default=0, help="sessions of the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle replay of four sessions after the timed regions")
     ap.add_argument("--no-kernel-events", action="store_true", help="experiment: no per-launch event pairs in the timed region")
     ap.add_argument("--rms", action="store_true", help="also produce the per-bus f64 sum of squares (getRMSLevel extension; libzl's AudioLevels has peaks only)")
     ap.add_argument("--no-thumb", action="store_true", help="skip the WaveFormItem thumbnail probe (BASELINE configs[3])")
@@ -110,11 +111,22 @@ class Workload:
                 out[i, :CLIP_FRAMES, 1] = g * np.sin(ph + np.pi / 2)
         return out
 
-    def configure_clip(self, e, cid):
+    def configure_clip(self, e, cid, as_id=None):
         p = self.clip_params
-        e.set_clip_params(cid, attack=float(p["attack"][cid]), decay=float(p["decay"][cid]), sustain=float(p["sustain"][cid]),
-                          release=float(p["release"][cid]), pan=float(p["pan"][cid]), volume_abs=float(p["volume"][cid]),
-                          length_beats=1.5, root_note=60)
+        e.set_clip_params(cid if as_id is None else as_id, attack=float(p["attack"][cid]), decay=float(p["decay"][cid]),
+                          sustain=float(p["sustain"][cid]), release=float(p["release"][cid]), pan=float(p["pan"][cid]),
+                          volume_abs=float(p["volume"][cid]), length_beats=1.5, root_note=60)
+
+    def subset(self, batch, sessions):
+        """The commands of `batch` = (sessions, blocks, ticks, cmds) that belong to the given global sessions, renumbered to
+        local sessions 0.. and local clip ids (a session's 8 clips are private to it)."""
+        sess, blocks, ticks, c = batch
+        local = {int(g): i for i, g in enumerate(sessions)}
+        keep = np.isin(sess, list(local))
+        s2 = np.array([local[int(x)] for x in sess[keep]], np.int32)
+        c2 = c[keep].copy()
+        c2["clip"] = s2 * CLIPS_PER_SESSION + (c2["clip"] - sess[keep] * CLIPS_PER_SESSION)
+        return s2, blocks[keep], ticks[keep], c2
 
 
 def clocks_for(e, step, blocks):
@@ -168,11 +180,15 @@ def S_BUS_BYTES(args):
     return args.sessions * BUSES * 2 * args.blocks * FRAMES * 4      # raw bus planes of one step on one GPU
 
 
+TRAFFIC_FILE = os.path.join("profiles", "r02_traffic.json")
+
+
 def ncu_traffic():
-    """dram__bytes_read.sum + dram__bytes_write.sum of one gather_kernel launch of this workload, from the committed
-    ncu --set full capture (profiles/r01_final_traffic.json); None when the file is missing or the workload differs."""
+    """dram__bytes_read.sum + dram__bytes_write.sum of one gather_kernel launch of this workload.  NOT measured by this run:
+    read from the committed summary of a builder-run `ncu --set full` capture of the same command (roofline.traffic_source
+    says so); None when the file is missing or the workload differs."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_final_traffic.json")) as f:
+        with open(os.path.join(ROOT, TRAFFIC_FILE)) as f:
             t = json.load(f)["gather"]
         return t["dram_bytes_read"] + t["dram_bytes_write"]
     except Exception:
@@ -237,24 +253,30 @@ def run_cuda(args, rank, world, local_rank):
 
     # --span-mix G: groups of G ranks share one stereo mix per session index -> NCCL sum of the master planes, in place on
     # the library's own device buffer, inside the timed region (the only collective on the path)
-    mix_group, master_t = None, None
+    # --span-mix G: groups of G ranks share one stereo mix per session index -> the library's own collective
+    # (zl_comm_init / zl_mix_reduce: ncclReduce of the master planes to the group's first rank, in place, on the context
+    # stream), inside the timed region (the only collective on the path).  Only the group's root reads the mix back.
+    span, mix_root = False, True
     if args.span_mix > 1 and dist is not None:
         from libzl_b200 import shard
         for ranks in shard.mix_groups(world, args.span_mix):
             gobj = dist.new_group(ranks=ranks)
             if rank in ranks:
-                mix_group = gobj
-        e.render(NB, FRAMES, clocks_for(e, 0, NB))          # allocates the output planes
-        mp_, ms_ = C.c_void_p(), C.c_int64()
-        e._chk(e.lib.device_master_ptr(e.ctx, C.byref(mp_), C.byref(ms_)), "device_master_ptr")
-        master_t = torch.as_tensor(shard.DeviceArray(mp_.value, (S, 2, ms_.value)), device=dev)
+                idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+                if rank == ranks[0]:
+                    buf = (C.c_ubyte * 128)()
+                    e._chk(e.lib.comm_unique_id(buf), "comm_unique_id")
+                    idt.copy_(torch.tensor(list(bytes(buf)), dtype=torch.uint8))
+                dist.broadcast(idt, src=ranks[0], group=gobj)
+                buf = (C.c_ubyte * 128)(*idt.cpu().tolist())
+                e._chk(e.lib.comm_init(e.ctx, buf, ranks.index(rank), len(ranks)), "comm_init")
+                span, mix_root = True, rank == ranks[0]
 
     def step(i, read_back=None):
         e.command_batch(*wl.steps[i])
         e.render(NB, FRAMES, clocks_for(e, i, NB))
-        if master_t is not None:
-            with torch.cuda.stream(stream):
-                shard.reduce_mix(master_t, group=mix_group)
+        if span:
+            e._chk(e.lib.mix_reduce(e.ctx, 0), "mix_reduce")
         if read_back is not None:
             e._chk(e.lib.read_master_all(e.ctx, read_back, n_per_step), "read_master_all")
 
@@ -285,13 +307,17 @@ def run_cuda(args, rank, world, local_rank):
     vf0, src0 = e.total_counters()
     e._chk(e.lib.kernel_timing(e.ctx, 0 if args.no_kernel_events else 2), "kernel_timing")    # CUDA events around each gather_kernel launch, same stream
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    e.lib.host_profile(e.ctx, None, None, None)                         # clear the host-time sums
     ev[0].record(stream)
     th0 = time.perf_counter()
     for k in range(args.steps):
         step(args.warmup + k)
         ev[k + 1].record(stream)
-    host_submit_ms = (time.perf_counter() - th0) * 1e3 / args.steps      # host time to queue one step (commands + launches)
+    host_loop_ms = (time.perf_counter() - th0) * 1e3 / args.steps        # wall time of the submitting loop (includes back-pressure)
     barrier()
+    hs, hw, hn = C.c_double(), C.c_double(), C.c_uint64()
+    e._chk(e.lib.host_profile(e.ctx, C.byref(hs), C.byref(hw), C.byref(hn)), "host_profile")
+    host_submit_ms = (hs.value - hw.value) / max(1, hn.value)           # host work inside zl_render per step, without the wait for a free command slot
     elapsed_ms = ev[0].elapsed_time(ev[-1])
     kernel_launches = e.launch_count() - launches0
     kms, kn = C.c_double(), C.c_uint64()
@@ -316,33 +342,88 @@ def run_cuda(args, rank, world, local_rank):
         i = total_steps + k
         e.command_batch(*wl.steps[i])
         e.render(NB, FRAMES, clocks_for(e, i, NB))
-        if master_t is not None:
-            with torch.cuda.stream(stream):
-                shard.reduce_mix(master_t, group=mix_group)
-            e._chk(e.lib.read_master_all(e.ctx, host_master[0], n_per_step), "read_master_all")   # in-place reduce: no ping-pong
-        else:
+        if span:
+            e._chk(e.lib.mix_reduce(e.ctx, 0), "mix_reduce")
+        if mix_root:                                           # a spanned mix lives on its group's root only
             e._chk(e.lib.read_master_all_async(e.ctx, host_master[k & 1], n_per_step), "read_master_all_async")
     e._chk(e.lib.read_wait(e.ctx), "read_wait")
     barrier()
     e2e_s = time.perf_counter() - t0
     e2e_vf = e.total_counters()[0] - vf1
     h2d = wl.steps[0][3].nbytes + wl.steps[0][0].nbytes * 2 + wl.steps[0][2].nbytes + NB * 40
-    d2h = S * 2 * n_per_step * 4
+    d2h = S * 2 * n_per_step * 4 if mix_root else 0
     # the last step's masters really are on the host: compare a few sessions with a synchronous read-back
-    chk = np.ctypeslib.as_array(host_master[0 if master_t is not None else (args.steps - 1) & 1], shape=(S, 2, n_per_step))[:4].copy()
-    ref = np.zeros((2, n_per_step), np.float32)
-    for sidx in range(min(4, S)):
-        l_, r_ = e.master(sidx)
-        assert np.array_equal(chk[sidx, 0], l_) and np.array_equal(chk[sidx, 1], r_), "pipelined read-back differs from the synchronous one"
-    del ref
+    if mix_root:
+        chk = np.ctypeslib.as_array(host_master[(args.steps - 1) & 1], shape=(S, 2, n_per_step))[:4].copy()
+        for sidx in range(min(4, S)):
+            l_, r_ = e.master(sidx)
+            assert np.array_equal(chk[sidx, 0], l_) and np.array_equal(chk[sidx, 1], r_), "pipelined read-back differs from the synchronous one"
+    # ---- parity at the benchmarked size: four of the S sessions replayed through the CPU oracle (outside every timed region)
+    parity = None
+    if not span and not args.no_parity:
+        try:
+            order = list(range(args.warmup)) + [2 * total_steps, 2 * total_steps + 1] + list(range(args.warmup, total_steps)) \
+                + list(range(total_steps, total_steps + args.steps))
+            sel = sorted({0, S // 3, (2 * S) // 3, S - 1})
+            last = np.ctypeslib.as_array(host_master[(args.steps - 1) & 1], shape=(S, 2, n_per_step))[sel].copy()
+            pk_all, _ = e.block_levels()
+            vinfo = e.voices()
+            clips_host = [pcm[s_ * CLIPS_PER_SESSION:(s_ + 1) * CLIPS_PER_SESSION, :CLIP_FRAMES].cpu().numpy() for s_ in sel]
+            parity = parity_at_size(args, wl, sel, order, clips_host, last, pk_all, vinfo)
+        except Exception as ex:   # noqa: BLE001
+            parity = {"error": repr(ex)}
     for hp in hostp:
         e.lib.host_free(hp)
-    return dict(e=e, host_submit_ms=host_submit_ms, kernel_ms=kernel_ms, gather_ms_per_step=gather_ms_per_step, gather_alone_ms=gather_alone_ms, elapsed_ms=elapsed_ms, step_ms=step_ms, timed_vf=timed_vf, timed_src=timed_src, launches=kernel_launches,
+    return dict(e=e, parity=parity, host_loop_ms=host_loop_ms, host_submit_ms=host_submit_ms, kernel_ms=kernel_ms, gather_ms_per_step=gather_ms_per_step, gather_alone_ms=gather_alone_ms, elapsed_ms=elapsed_ms, step_ms=step_ms, timed_vf=timed_vf, timed_src=timed_src, launches=kernel_launches,
                 clocks=clocks, e2e_s=e2e_s, e2e_vf=e2e_vf, h2d=h2d, d2h=d2h, out_bytes=out_bytes, state_bytes=state_bytes,
                 dist=dist, dev=dev, wl=wl, keep=pcm)
 
 
 # ------------------------------------------------------------------------------------------------
+def parity_at_size(args, wl, sel, order, clips_host, last_master, peaks_all, voices):
+    """The sessions `sel` of the benchmarked workload, replayed through the exact CPU oracle (oracle/liboracle.so,
+    -ffp-contract=off) over every step the device ran, in the same order; the LAST step's masters (as they arrived on the
+    host through the pipelined read-back), its per-period integer peaks and the voice table must be bit-equal."""
+    from oracle import loader
+    from libzl_b200 import _capi as K
+    from libzl_b200.engine import Engine
+    t0 = time.perf_counter()
+    NB = args.blocks
+    o = Engine(lib=loader.load_oracle(), n_sessions=len(sel), buses_per_session=BUSES, voices_per_bus=VOICES,
+               max_clips=len(sel) * CLIPS_PER_SESSION, max_frames=FRAMES, max_blocks=NB,
+               outputs=K.ZL_OUT_RAW | K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS, quirks=args.quirks)
+    for i, s_ in enumerate(sel):
+        for k in range(CLIPS_PER_SESSION):
+            cid = o.add_clip(np.ascontiguousarray(clips_host[i][k].T), RATE)
+            wl.configure_clip(o, s_ * CLIPS_PER_SESSION + k, as_id=cid)
+    o.command_batch(*wl.subset(wl.init, sel))
+    vf = 0
+    for i in order:
+        o.command_batch(*wl.subset(wl.steps[i], sel))
+        o.render(NB, FRAMES, clocks_for(o, i, NB))
+        vf += o.voice_frames()
+    m = o.master_all()
+    pk, _ = o.block_levels()
+    ov = o.voices()
+    o.close()
+    masters_ok = bool(np.array_equal(m, last_master))
+    peaks_ok = all(np.array_equal(pk[:, i * BUSES:(i + 1) * BUSES], peaks_all[:, s_ * BUSES:(s_ + 1) * BUSES]) for i, s_ in enumerate(sel))
+    nv = BUSES * VOICES
+    voices_ok = True
+    for i, s_ in enumerate(sel):
+        for k in range(nv):
+            a, b = ov[i * nv + k], voices[s_ * nv + k]
+            if (a.position, a.playing, a.envelope, a.adsr_state, a.pos_gain) != (b.position, b.playing, b.envelope, b.adsr_state, b.pos_gain):
+                voices_ok = False
+    res = {"sessions_checked": [int(x) for x in sel], "steps_replayed": len(order), "oracle_voice_frames": int(vf),
+           "masters_bit_equal": masters_ok, "peaks_bit_equal": bool(peaks_ok), "voice_table_bit_equal": bool(voices_ok),
+           "max_abs_master_diff": float(np.abs(m - last_master).max()), "peak_master": float(np.abs(m).max()),
+           "oracle_s": round(time.perf_counter() - t0, 2),
+           "what": "exact CPU oracle (-ffp-contract=off) over every step of this run for these sessions, vs the last step's masters on the host, its per-period peaks and the device voice table"}
+    assert masters_ok and peaks_ok and voices_ok, f"parity at size FAILED: {res}"
+    return res
+
+
 def run_cpu(args, sessions, steps, warmup, threads=None):
     """The reference's CPU implementation of the path (oracle port of lib/SamplerSynthVoice.cpp::process etc.,
     built like the reference with contraction on: oracle/liboracle_fma.so) on a bounded sample of the workload."""
@@ -411,6 +492,37 @@ def latency_probe(local_rank, iters=1500):
     ts = sorted(ts[20:])
     return {"p50_us": round(1e6 * ts[len(ts) // 2], 2), "p99_us": round(1e6 * ts[int(len(ts) * 0.99)], 2),
             "what": "one 512-frame period of one 128-voice session: zl_render + zl_read_master_all to pinned host"}
+
+
+def cpu_latency_probe(iters=300):
+    """The same single period of one 128-voice session on ONE host thread with the oracle port (contraction on, as the
+    reference is built): the CPU figure that stands beside the device latency."""
+    from oracle import loader
+    from libzl_b200 import _capi as K
+    from libzl_b200.engine import Engine
+    wl = Workload(1, 1, iters + 20, 99, 0)
+    lib = loader.load_oracle(fma=True)
+    e = Engine(lib=lib, n_sessions=1, buses_per_session=BUSES, voices_per_bus=VOICES, max_clips=8, max_frames=FRAMES, max_blocks=1,
+               outputs=K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS)
+    lib.dll.zlo_set_threads(e.ctx, 1)
+    pcm = wl.clip_pcm_numpy(0, CLIPS_PER_SESSION)
+    for i in range(CLIPS_PER_SESSION):
+        cid = e.add_clip(np.ascontiguousarray(pcm[i, :CLIP_FRAMES].T), RATE)
+        wl.configure_clip(e, cid)
+    e.command_batch(*wl.init)
+    out = np.zeros((1, 2, FRAMES), np.float32)
+    outp = out.ctypes.data_as(C.POINTER(C.c_float))
+    ts = []
+    for i in range(iters + 20):
+        clk = clocks_for(e, i, 1)
+        t0 = time.perf_counter()
+        e.lib.render(e.ctx, 1, FRAMES, clk)
+        e.lib.read_master_all(e.ctx, outp, FRAMES)
+        ts.append(time.perf_counter() - t0)
+    e.close()
+    ts = sorted(ts[20:])
+    return {"p50_us": round(1e6 * ts[len(ts) // 2], 2), "p99_us": round(1e6 * ts[int(len(ts) * 0.99)], 2), "threads": 1,
+            "what": "the same period on one host thread: oracle port (-O3 -mfma), render + master copy"}
 
 
 def thumbnail_probe(local_rank, peak):
@@ -515,7 +627,7 @@ def main():
               "frames": FRAMES, "blocks_per_step": args.blocks, "mode": "Z (libzl process(), quirks faithful)",
               "outputs": "raw bus + master + peak meters" + (" + RMS sums" if args.rms else " (RMS, an extension over libzl's peak-only AudioLevels: --rms)"), "quirks": args.quirks,
               "kernels_per_period": "plan_kernel + walk_kernel + gather_kernel (+ one master_mix_kernel per step)", "parallelism": (f"sessions sharded over {args.gpus} GPU(s), no collective" if args.span_mix <= 1 else
-                              f"sessions sharded over {args.gpus} GPU(s); groups of {args.span_mix} GPUs share one mix: NCCL all-reduce of the master planes per step"),
+                              f"sessions sharded over {args.gpus} GPU(s); groups of {args.span_mix} GPUs share one mix: zl_mix_reduce (ncclReduce of the master planes to the group's first rank) per step, the root alone reads the mix back"),
               "l2": "inputs (clip PCM 3 MB/session) larger than L2; no flush needed"}
 
     if args.impl == "reference":
@@ -524,8 +636,17 @@ def main():
         sessions = cpu_sample_size(args)
         vf, dt, th = run_cpu(args, sessions, args.steps, min(args.warmup, 1))
         v = vf / dt
+        # this arm renders a bounded SAMPLE of the workload (same per-session shape, fewer sessions): the line says so, and
+        # ms_per_step is the sample's own; the throughput in voice-frames/s is what compares (it does not depend on the count)
+        config = dict(config, sessions_per_gpu=sessions,
+                      workload=f"cfg2x{sessions} (CPU sample of cfg2x{args.sessions}: {sessions} of the {args.sessions} sessions per GPU, same 128-voice "
+                               f"session shape, {args.blocks} periods x {FRAMES} frames per step)",
+                      full_workload_sessions_per_gpu=args.sessions, parallelism=f"{th} host threads, sessions split across them",
+                      kernels_per_period="n/a (CPU)")
         line = {"impl": "reference", "metric": "voice_frames_per_s", "value": v, "unit": "voice-frames/s", "n_gpus": args.gpus,
-                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+                "ms_per_step_is_for": f"the {sessions}-session sample; the full {args.sessions}-session step would take {1e3 * dt / args.steps * args.sessions / sessions:.0f} ms at this rate",
+                "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32 (f64 positions)", "data": "synthetic", "config": config,
                 "cpu_baseline": {"value": v, "unit": "voice-frames/s", "cores": th, "kind": "port",
                                  "sample": f"{sessions} sessions x {args.blocks} periods x {FRAMES} frames per step, {args.steps} steps "
@@ -561,6 +682,7 @@ def main():
                         "d2h_bytes_per_step": r["d2h"], "what": "per step: zl_command_batch (H2D) + zl_render + zl_read_master_all_async (master of every session D2H to pinned host, overlapping the next step's render); zl_read_wait before the clock stops"},
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                              "traffic": (ncu_traffic() if (args.sessions, args.blocks, args.quirks) == (4096, 16, 7) else None),
+                             "traffic_source": f"{TRAFFIC_FILE} (ncu --set full, builder-run capture of this command; NOT measured by this run)",
                              "peak_source": peak_src, "frac_of_nominal_8TBs": ach / 8000.0,
                              "algorithmic_bytes_per_launch": alg_bytes,
                              "bytes_per_voice_frame": step_alg_bytes / (r["timed_vf"] / args.steps),
@@ -570,10 +692,14 @@ def main():
                              "kernel_alone_ms": r["gather_alone_ms"], "frac_alone": alg_bytes / (r["gather_alone_ms"] * 1e-3) / 1e9 / peak,
                              "whole_step_frac": step_alg_bytes / (el_ms / args.steps * 1e-3) / 1e9 / peak,
                              "whole_step_note": "all algorithmic bytes of a step (source + voice state + raw planes + master + peaks) / ms_per_step: plan, walk, gather and master mix together"},
-                "voice_frames_per_step": vf / args.steps / world, "host_submit_ms_per_step": r["host_submit_ms"]}
+                "voice_frames_per_step": vf / args.steps / world, "host_submit_ms_per_step": r["host_submit_ms"],
+                "host_submit_note": "host time inside zl_render per step (commands, launches), without the wait for a free command slot; "
+                                    f"the submitting loop itself took {r['host_loop_ms']:.2f} ms per step because it runs ahead of the device and is held back",
+                "parity_at_size": r["parity"]}
         if world == 1 and not args.no_latency:
             try:
                 line["latency"] = latency_probe(local_rank)
+                line["cpu_latency"] = cpu_latency_probe()
             except Exception as ex:   # noqa: BLE001
                 line["latency"] = {"error": str(ex)}
         if world == 1 and not args.no_thumb:

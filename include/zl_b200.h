@@ -284,6 +284,13 @@ ZL_EXPORT int ZL_FN(read_voices)(zl_ctx* ctx, zl_voice_info* out, int32_t capaci
  * (lib/ClipAudioSourcePositionsModel.cpp:160-173, before hysteresis) + up to 32 (gain,progress). */
 ZL_EXPORT int ZL_FN(read_positions)(zl_ctx* ctx, int32_t clip_id, float* gains, float* progress,
                                     int32_t capacity, int32_t* count);
+/* ClipAudioSourcePositionsModel::peakGain (lib/ClipAudioSourcePositionsModel.cpp:160-173) as ClipAudioSource::syncAudioLevel
+ * reads it (lib/ClipAudioSource.cpp:88-113): the maximum gain over the clip's live positions - the first 32 playing voices of
+ * the clip in voice-table order (POSITION_COUNT, :5; createPositionID hands out slots in start order, :78-100, so the two
+ * agree whenever at most 32 voices play one clip) - taken over only when it moved by more than 0.01 from the value last
+ * reported (the model's hysteresis; the state lives in the context, one per clip).  first_progress: firstProgress() (:175-185),
+ * -1 when nothing plays; may be NULL. */
+ZL_EXPORT int ZL_FN(clip_peak_gain)(zl_ctx* ctx, int32_t clip_id, float* peak_gain, double* first_progress);
 /* Source PCM floats spanned by the voices of the last render (unique samples incl. the +1 tap, summed per
  * voice per block; the algorithmic read traffic of SURVEY.md 8d is 4x this). */
 ZL_EXPORT int ZL_FN(last_source_floats)(zl_ctx* ctx, uint64_t* n);
@@ -299,6 +306,9 @@ ZL_EXPORT int ZL_FN(dropped_commands)(zl_ctx* ctx, uint64_t* n);
  * (the dominant kernel); 0: off.  zl_kernel_time returns and clears the sum (ms) and the number of pairs. */
 ZL_EXPORT int ZL_FN(kernel_timing)(zl_ctx* ctx, int32_t mode);
 ZL_EXPORT int ZL_FN(kernel_time)(zl_ctx* ctx, double* total_ms, uint64_t* launches);
+/* Host time spent inside zl_render since the last call (ms), the part of it blocked waiting for the device to release a
+ * command slot (back-pressure, not host work), and the number of renders; clears the sums. */
+ZL_EXPORT int ZL_FN(host_profile)(zl_ctx* ctx, double* submit_ms, double* wait_ms, uint64_t* renders);
 /* Kernel launches issued by this context so far (bench `gpu_launches`). */
 ZL_EXPORT int ZL_FN(launch_count)(zl_ctx* ctx, uint64_t* n);
 
@@ -353,6 +363,23 @@ ZL_EXPORT int ZL_FN(wav_encode)(zl_ctx* ctx, const float* l, const float* r, int
                                 void* out, uint64_t cap, uint64_t* size);
 ZL_EXPORT int ZL_FN(bounce_wav)(zl_ctx* ctx, int32_t session, int32_t bus, int32_t which, int32_t bits,
                                 void* out, uint64_t cap, uint64_t* size);
+
+/* ---- one mix spanning GPUs ------------------------------------- */
+/* The only exchange step on the path: when the dry ports of buses rendered on different GPUs feed ONE stereo pair (what JACK
+ * does when every track's dryOut is connected to the same system:playback ports, lib/JackPassthrough.cpp:94-101), the
+ * per-rank master planes are summed over NCCL (NVLink / NVSwitch).  One process per GPU; the NCCL C API is taken from the
+ * libnccl.so.2 already in the process or on the loader path (ZL_B200_NCCL_LIB overrides), never linked at build time.
+ * zl_comm_unique_id: rank 0 of a mix group fills 128 bytes (ncclUniqueId) and hands them to the others out of band.
+ * zl_comm_init: joins the group (collective: every rank of the group calls it).
+ * zl_mix_reduce: float32 sum of the master planes [n_sessions][2][stride] of the LAST render, in place on the context stream
+ *   (so zl_read_master* / zl_bounce_wav that follow see the spanned mix); root >= 0: ncclReduce, only that rank holds the sum
+ *   (the others keep their own partial mix); root < 0: ncclAllReduce.  The summation order differs from the serial
+ *   reference: results agree to float reassociation (1e-5 of full scale), not bit for bit; per-bus planes and meters are
+ *   untouched (a meter of the spanned mix must be taken after the reduce: zl_levels_scan). */
+ZL_EXPORT int ZL_FN(comm_unique_id)(void* id128);
+ZL_EXPORT int ZL_FN(comm_init)(zl_ctx* ctx, const void* nccl_unique_id, int32_t rank, int32_t nranks);
+ZL_EXPORT int ZL_FN(mix_reduce)(zl_ctx* ctx, int32_t root);
+ZL_EXPORT int ZL_FN(comm_destroy)(zl_ctx* ctx);
 
 /* ---- pinned host memory ------------------------------------------------------------- */
 /* Page-locked host buffers for callers that want full-rate PCIe transfers on zl_read_* / clip upload

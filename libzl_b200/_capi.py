@@ -113,6 +113,12 @@ SIGNATURES = {
     "levels_tick": (C.c_int, [_ctx, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P(zl_levels)]),
     "read_voices": (C.c_int, [_ctx, _P(zl_voice_info), C.c_int32]),
     "read_positions": (C.c_int, [_ctx, C.c_int32, _f32p, _f32p, C.c_int32, _P(C.c_int32)]),
+    "clip_peak_gain": (C.c_int, [_ctx, C.c_int32, _P(C.c_float), _P(C.c_double)]),
+    "host_profile": (C.c_int, [_ctx, _P(C.c_double), _P(C.c_double), _P(C.c_uint64)]),
+    "comm_unique_id": (C.c_int, [C.c_void_p]),
+    "comm_init": (C.c_int, [_ctx, C.c_void_p, C.c_int32, C.c_int32]),
+    "mix_reduce": (C.c_int, [_ctx, C.c_int32]),
+    "comm_destroy": (C.c_int, [_ctx]),
     "last_voice_frames": (C.c_int, [_ctx, _P(C.c_uint64)]),
     "dropped_commands": (C.c_int, [_ctx, _P(C.c_uint64)]),
     "launch_count": (C.c_int, [_ctx, _P(C.c_uint64)]),

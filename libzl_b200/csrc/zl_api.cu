@@ -12,6 +12,7 @@
 #include <vector>
 #include <chrono>
 
+#include <dlfcn.h>
 #include <fcntl.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
@@ -70,6 +71,7 @@ struct ClipHost {
     // thumbnail
     int8_t* d_thumb = nullptr;
     int thumbSpt = 0, nThumb = 0;
+    float peakGain = 0.0f;                    // ClipAudioSourcePositionsModelPrivate::peakGain (the hysteresis state)
 
     float duration() const { return (float) ((double) length / rate); }
     float startPosition(int slice) const {                                   // lib/ClipAudioSource.cpp:261-268
@@ -144,6 +146,8 @@ struct zl_ctx {
     void* h_slot[2] = {nullptr, nullptr}; void* d_slot[2] = {nullptr, nullptr}; size_t slotCap[2] = {0, 0};
     // optional kernel timing (bench roofline): event pairs around each render_kernel launch
     int timing = 0; std::vector<cudaEvent_t> tev; double timedMs = 0.0; uint64_t timedLaunches = 0;
+    std::vector<cudaEvent_t> evPool;      // timing events are recycled: none is created inside a timed region once the pool is warm
+    double hostSubmitMs = 0.0, hostWaitMs = 0.0; uint64_t hostRenders = 0;   // zl_host_profile: time spent inside zl_render, and of it blocked on the device
     // outputs of the last render
     float* d_out[4] = {nullptr, nullptr, nullptr, nullptr};
     float* d_master = nullptr;            // the master planes of the last render (= d_masterBuf[masterCur])
@@ -166,6 +170,7 @@ struct zl_ctx {
     std::vector<int32_t> h_peaks; std::vector<double> h_sumsq; bool lvlCached = false;
     uint64_t voiceFrames = 0, dropped = 0, launches = 0;
     bool vfCached = true;
+    void* comm = nullptr; int commRank = 0, commSize = 0;   // ncclComm_t of the mix group this context belongs to (zl_comm_init)
 
     int nbus() const { return cfg.n_sessions * cfg.buses_per_session; }
     int nvoices() const { return nbus() * cfg.voices_per_bus; }
@@ -185,6 +190,11 @@ int fail(zl_ctx* c, cudaError_t e, const char* what) {
 #define BIND() do { if (!ctx) return ZL_ERR_INVALID; cudaError_t e_ = cudaSetDevice(ctx->device); if (e_ != cudaSuccess) return fail(ctx, e_, "cudaSetDevice"); } while (0)
 
 int invalid(zl_ctx* c, const char* what) { if (c) c->err = what; return ZL_ERR_INVALID; }
+
+cudaError_t pool_event(zl_ctx* ctx, cudaEvent_t* e) {
+    if (!ctx->evPool.empty()) { *e = ctx->evPool.back(); ctx->evPool.pop_back(); return cudaSuccess; }
+    return cudaEventCreate(e);
+}
 
 ClipHost* find_clip(zl_ctx* ctx, int id) {
     if (!ctx || id < 0 || id >= (int) ctx->clips.size() || !ctx->clips[(size_t) id].live) return nullptr;
@@ -258,6 +268,7 @@ int new_clip_slot(zl_ctx* ctx) {
 
 }  // namespace
 
+static void nccl_destroy_comm(void* comm);
 // =============================================================================================
 extern "C" {
 
@@ -331,6 +342,7 @@ int zl_ctx_destroy(zl_ctx* ctx) {
     cudaSetDevice(ctx->device);
     for (cudaStream_t s : {ctx->stream, ctx->own, ctx->planStream, ctx->mixStream, ctx->copyStream})   // nothing may still run on a buffer freed below
         if (s) cudaStreamSynchronize(s);
+    if (ctx->comm) { nccl_destroy_comm(ctx->comm); ctx->comm = nullptr; }
     for (ClipHost& c : ctx->clips) { if (c.owned && c.d_data) cudaFree(c.d_data); if (c.d_thumb) cudaFree(c.d_thumb); }
     void* frees[] = {ctx->d_clips, ctx->d_slice, ctx->d_voices, ctx->d_buses, ctx->d_cmds, ctx->d_clocks, ctx->d_pow2,
                      ctx->d_counters, ctx->d_bnd, ctx->d_px, ctx->d_mask, ctx->d_tmp, ctx->d_out[0], ctx->d_out[1],
@@ -350,6 +362,7 @@ int zl_ctx_destroy(zl_ctx* ctx) {
     if (ctx->h_clocks) cudaFreeHost(ctx->h_clocks);
     for (int k = 0; k < 2; ++k) { if (ctx->h_slot[k]) cudaFreeHost(ctx->h_slot[k]); if (ctx->d_slot[k]) cudaFree(ctx->d_slot[k]); }
     for (cudaEvent_t e : ctx->tev) cudaEventDestroy(e);
+    for (cudaEvent_t e : ctx->evPool) cudaEventDestroy(e);
     for (cudaEvent_t e : ctx->clkEv) if (e) cudaEventDestroy(e);
     if (ctx->own) cudaStreamDestroy(ctx->own);
     delete ctx;
@@ -787,7 +800,7 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     // timing 1: one event pair around the whole plan/walk/gather sequence of this call; 2: one pair per gather_kernel launch
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->timing == 1) {
-        CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+        CK(pool_event(ctx, &e0)); CK(pool_event(ctx, &e1));
         CK(cudaEventRecord(e0, st));
     }
     // Across renders the planner of period 0 stands to the previous render's last gather as plan(b + 1) to gather(b) inside
@@ -837,7 +850,7 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
         }
         cudaEvent_t g0 = nullptr, g1 = nullptr;
         if (ctx->timing == 2) {
-            CK(cudaEventCreate(&g0)); CK(cudaEventCreate(&g1));
+            CK(pool_event(ctx, &g0)); CK(pool_event(ctx, &g1));
             ctx->tev.push_back(g0); ctx->tev.push_back(g1);
         } else if (tl) {
             CK(cudaEventCreate(&g0)); CK(cudaEventCreate(&g1));
@@ -869,6 +882,12 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     ctx->nblocks = nblocks; ctx->nframes = nframes;
     ctx->lvlCached = false; ctx->vfCached = false;
     CK(cudaEventRecord(ctx->clkEv[slot], st));
+    {
+        const auto hpEnd = std::chrono::steady_clock::now();
+        ctx->hostSubmitMs += std::chrono::duration<double, std::milli>(hpEnd - hp0).count();
+        ctx->hostWaitMs += std::chrono::duration<double, std::milli>(hp2 - hp1).count();
+        ctx->hostRenders++;
+    }
     if (getenv("ZL_B200_HOSTPROF")) {
         auto hp4 = std::chrono::steady_clock::now();
         auto us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
@@ -983,14 +1002,20 @@ int zl_bounce_wav(zl_ctx* ctx, int32_t s, int32_t b, int32_t which, int32_t bits
     return wav_encode_rows(ctx, l, l + ctx->stride, N, ctx->cfg.sample_rate, bits, out, cap, size);
 }
 
+// every session's master rows [n_sessions * 2][N] to the host: one flat copy when the rows are contiguous (stride == N)
+static cudaError_t copy_master_rows(zl_ctx* ctx, float* out, int64_t N, cudaStream_t st) {
+    const size_t rows = (size_t) ctx->cfg.n_sessions * 2;
+    if (ctx->stride == N) return cudaMemcpyAsync(out, ctx->d_master, sizeof(float) * rows * (size_t) N, cudaMemcpyDeviceToHost, st);
+    return cudaMemcpy2DAsync(out, sizeof(float) * (size_t) N, ctx->d_master, sizeof(float) * (size_t) ctx->stride,
+                             sizeof(float) * (size_t) N, rows, cudaMemcpyDeviceToHost, st);
+}
+
 int zl_read_master_all(zl_ctx* ctx, float* out, int64_t n) {
     BIND();
     if (!out) return invalid(ctx, "read_master_all: null");
     const int64_t N = (int64_t) ctx->nblocks * ctx->nframes;
     if (n != N || !ctx->d_master) { ctx->err = "read_master_all: size mismatch or master not enabled"; return ZL_ERR_STATE; }
-    const size_t rows = (size_t) ctx->cfg.n_sessions * 2;
-    CK(cudaMemcpy2DAsync(out, sizeof(float) * (size_t) N, ctx->d_master, sizeof(float) * (size_t) ctx->stride,
-                         sizeof(float) * (size_t) N, rows, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(copy_master_rows(ctx, out, N, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return ZL_OK;
 }
@@ -1011,9 +1036,7 @@ int zl_read_master_all_async(zl_ctx* ctx, float* out, int64_t n) {
     ctx->pipelined = true;
     CK(cudaEventRecord(ctx->renderDone, ctx->stream));
     CK(cudaStreamWaitEvent(ctx->copyStream, ctx->renderDone, 0));
-    const size_t rows = (size_t) ctx->cfg.n_sessions * 2;
-    CK(cudaMemcpy2DAsync(out, sizeof(float) * (size_t) N, ctx->d_master, sizeof(float) * (size_t) ctx->stride,
-                         sizeof(float) * (size_t) N, rows, cudaMemcpyDeviceToHost, ctx->copyStream));
+    CK(copy_master_rows(ctx, out, N, ctx->copyStream));
     CK(cudaEventRecord(ctx->copyDone[ctx->masterCur], ctx->copyStream));
     ctx->copyPending[ctx->masterCur] = true;
     return ZL_OK;
@@ -1149,6 +1172,28 @@ int zl_read_positions(zl_ctx* ctx, int32_t clip, float* gains, float* progress, 
     return ZL_OK;
 }
 
+int zl_clip_peak_gain(zl_ctx* ctx, int32_t clip, float* peak, double* firstProgress) {
+    BIND();
+    ClipHost* c = find_clip(ctx, clip);
+    if (!c || !peak) return invalid(ctx, "clip_peak_gain: unknown clip or null output");
+    std::vector<VoiceDev> hv;
+    int rc = fetch_voices(ctx, hv);
+    if (rc != ZL_OK) return rc;
+    float mx = 0.0f;                                                         // lib/ClipAudioSourcePositionsModel.cpp:162-166
+    double first = -1.0f;
+    int n = 0;
+    for (const VoiceDev& v : hv)
+        if ((v.flags & VF_PLAYING) && v.clip == clip && (v.flags & VF_HAS_POSID) && n < 32) {
+            mx = std::max(mx, v.posGain);
+            if (n == 0) first = v.posProgress;
+            ++n;
+        }
+    if (std::abs(c->peakGain - mx) > 0.01) c->peakGain = mx;                  // :167-169
+    *peak = c->peakGain;
+    if (firstProgress) *firstProgress = first;
+    return ZL_OK;
+}
+
 int zl_last_voice_frames(zl_ctx* ctx, uint64_t* vf) {
     BIND();
     if (!vf) return invalid(ctx, "last_voice_frames: null");
@@ -1195,12 +1240,20 @@ int zl_kernel_time(zl_ctx* ctx, double* total_ms, uint64_t* launches) {
         float ms = 0.0f;
         CK(cudaEventElapsedTime(&ms, ctx->tev[i], ctx->tev[i + 1]));
         ctx->timedMs += ms; ctx->timedLaunches++;
-        cudaEventDestroy(ctx->tev[i]); cudaEventDestroy(ctx->tev[i + 1]);
+        ctx->evPool.push_back(ctx->tev[i]); ctx->evPool.push_back(ctx->tev[i + 1]);
     }
     ctx->tev.clear();
     if (total_ms) *total_ms = ctx->timedMs;
     if (launches) *launches = ctx->timedLaunches;
     ctx->timedMs = 0.0; ctx->timedLaunches = 0;
+    return ZL_OK;
+}
+int zl_host_profile(zl_ctx* ctx, double* submit_ms, double* wait_ms, uint64_t* renders) {
+    if (!ctx) return ZL_ERR_INVALID;
+    if (submit_ms) *submit_ms = ctx->hostSubmitMs;
+    if (wait_ms) *wait_ms = ctx->hostWaitMs;
+    if (renders) *renders = ctx->hostRenders;
+    ctx->hostSubmitMs = 0.0; ctx->hostWaitMs = 0.0; ctx->hostRenders = 0;
     return ZL_OK;
 }
 int zl_launch_count(zl_ctx* ctx, uint64_t* n) { if (!ctx || !n) return ZL_ERR_INVALID; *n = ctx->launches; return ZL_OK; }
@@ -1390,6 +1443,89 @@ int zl_levels_scan(zl_ctx* ctx, const float* l, const float* r, int64_t n, int32
     if (pb) *pb = res.pk[1];
     if (sa) *sa = res.sq[0];
     if (sb) *sb = res.sq[1];
+    return ZL_OK;
+}
+
+// ---- one mix spanning GPUs: NCCL through its C API, resolved at run time ---------------------------------------------
+namespace {
+struct NcclApi {
+    typedef struct { char internal[128]; } UniqueId;
+    int (*GetUniqueId)(UniqueId*) = nullptr;
+    int (*CommInitRank)(void**, int, UniqueId, int) = nullptr;
+    int (*Reduce)(const void*, void*, size_t, int, int, int, void*, cudaStream_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool ok = false;
+};
+NcclApi& nccl() {
+    static NcclApi api = [] {
+        NcclApi a;
+        const char* names[] = {getenv("ZL_B200_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+        void* h = nullptr;
+        for (const char* n : names) if (n && *n && (h = dlopen(n, RTLD_NOW | RTLD_GLOBAL))) break;
+        if (!h) return a;
+        a.GetUniqueId = (int (*)(NcclApi::UniqueId*)) dlsym(h, "ncclGetUniqueId");
+        a.CommInitRank = (int (*)(void**, int, NcclApi::UniqueId, int)) dlsym(h, "ncclCommInitRank");
+        a.Reduce = (int (*)(const void*, void*, size_t, int, int, int, void*, cudaStream_t)) dlsym(h, "ncclReduce");
+        a.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t)) dlsym(h, "ncclAllReduce");
+        a.CommDestroy = (int (*)(void*)) dlsym(h, "ncclCommDestroy");
+        a.GetErrorString = (const char* (*)(int)) dlsym(h, "ncclGetErrorString");
+        a.ok = a.GetUniqueId && a.CommInitRank && a.Reduce && a.AllReduce && a.CommDestroy;
+        return a;
+    }();
+    return api;
+}
+int nccl_fail(zl_ctx* ctx, int rc, const char* what) {
+    char buf[256];
+    snprintf(buf, sizeof buf, "%s: NCCL error %d (%s)", what, rc, nccl().GetErrorString ? nccl().GetErrorString(rc) : "?");
+    if (ctx) ctx->err = buf;
+    return ZL_ERR_CUDA;
+}
+constexpr int kNcclFloat32 = 7, kNcclSum = 0;        // ncclDataType_t / ncclRedOp_t values of the stable C API
+}  // namespace
+
+}  // extern "C"
+static void nccl_destroy_comm(void* comm) { if (nccl().ok && comm) nccl().CommDestroy(comm); }
+extern "C" {
+int zl_comm_unique_id(void* id128) {
+    if (!id128) return ZL_ERR_INVALID;
+    if (!nccl().ok) return ZL_ERR_STATE;
+    NcclApi::UniqueId id;
+    if (nccl().GetUniqueId(&id) != 0) return ZL_ERR_CUDA;
+    memcpy(id128, id.internal, 128);
+    return ZL_OK;
+}
+
+int zl_comm_init(zl_ctx* ctx, const void* id128, int32_t rank, int32_t nranks) {
+    BIND();
+    if (!id128 || nranks < 1 || rank < 0 || rank >= nranks) return invalid(ctx, "comm_init: bad argument");
+    if (!nccl().ok) { ctx->err = "comm_init: libnccl.so.2 not found (set ZL_B200_NCCL_LIB)"; return ZL_ERR_STATE; }
+    if (ctx->comm) { nccl().CommDestroy(ctx->comm); ctx->comm = nullptr; }
+    NcclApi::UniqueId id;
+    memcpy(id.internal, id128, 128);
+    const int rc = nccl().CommInitRank(&ctx->comm, nranks, id, rank);
+    if (rc != 0) { ctx->comm = nullptr; return nccl_fail(ctx, rc, "ncclCommInitRank"); }
+    ctx->commRank = rank; ctx->commSize = nranks;
+    return ZL_OK;
+}
+
+int zl_mix_reduce(zl_ctx* ctx, int32_t root) {
+    BIND();
+    if (!ctx->comm) { ctx->err = "mix_reduce: zl_comm_init first"; return ZL_ERR_STATE; }
+    if (!ctx->d_master || ctx->nblocks < 1) { ctx->err = "mix_reduce: nothing rendered yet or ZL_OUT_MASTER not enabled"; return ZL_ERR_STATE; }
+    if (root >= ctx->commSize) return invalid(ctx, "mix_reduce: root out of range");
+    const size_t count = (size_t) ctx->cfg.n_sessions * 2 * (size_t) ctx->stride;
+    const int rc = root >= 0 ? nccl().Reduce(ctx->d_master, ctx->d_master, count, kNcclFloat32, kNcclSum, root, ctx->comm, ctx->stream)
+                             : nccl().AllReduce(ctx->d_master, ctx->d_master, count, kNcclFloat32, kNcclSum, ctx->comm, ctx->stream);
+    if (rc != 0) return nccl_fail(ctx, rc, root >= 0 ? "ncclReduce" : "ncclAllReduce");
+    ctx->launches++;
+    return ZL_OK;
+}
+
+int zl_comm_destroy(zl_ctx* ctx) {
+    if (!ctx) return ZL_ERR_INVALID;
+    if (ctx->comm) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); nccl().CommDestroy(ctx->comm); ctx->comm = nullptr; }
     return ZL_OK;
 }
 

@@ -296,6 +296,12 @@ class Engine:
         self._chk(self.lib.read_positions(self.ctx, clip, _fp(g), _fp(p), 32, C.byref(n)), "read_positions")
         return g[:n.value], p[:n.value]
 
+    def clip_peak_gain(self, clip):
+        """ClipAudioSourcePositionsModel::peakGain (0.01 hysteresis, state kept per clip by the library)."""
+        g = C.c_float()
+        self._chk(self.lib.clip_peak_gain(self.ctx, clip, C.byref(g), None), "clip_peak_gain")
+        return g.value
+
     def voice_frames(self):
         v = C.c_uint64()
         self._chk(self.lib.last_voice_frames(self.ctx, C.byref(v)), "last_voice_frames")

@@ -2,7 +2,9 @@
 with no data-path collective; a collective only where ONE stereo mix spans GPUs (the reference's JACK graph sums the
 SamplerChannel ports of all tracks into one master, lib/JackPassthrough.cpp:94-101 + the JACK port mix).
 
-Host logic only (torch.distributed plumbing); the kernels never see the world size."""
+Host logic only; the kernels never see the world size.  On the GPUs the collective is the library's own
+(zl_comm_init / zl_mix_reduce over the NCCL C API, include/zl_b200.h); reduce_mix below is the torch.distributed form of
+the same reduce for hosts that already run a process group (and for the gloo CPU test)."""
 from __future__ import annotations
 
 
@@ -23,15 +25,6 @@ def mix_groups(world: int, span: int) -> list[list[int]]:
     if span < 1 or world % span:
         raise ValueError("span must divide the world size")
     return [list(range(g, g + span)) for g in range(0, world, span)]
-
-
-class DeviceArray:
-    """Zero-copy view of a device buffer owned by the C-ABI library (zl_device_master_ptr / zl_device_bus_ptr) for
-    torch.as_tensor(..., device='cuda'): the NCCL reduce runs in place on the library's own master planes."""
-
-    def __init__(self, ptr: int, shape, typestr="<f4"):
-        self.__cuda_array_interface__ = {"shape": tuple(int(x) for x in shape), "typestr": typestr,
-                                         "data": (int(ptr), False), "version": 2, "strides": None}
 
 
 def reduce_mix(master, group=None, dst=None):

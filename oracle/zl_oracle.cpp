@@ -141,6 +141,7 @@ struct Clip {
     int rootNote = 60;
     float adsrA = 0.0f, adsrD = 0.1f, adsrS = 1.0f, adsrR = 0.05f;           // :164-168
     std::vector<double> slicePositionsCache;
+    float peakGain = 0.0f;          // ClipAudioSourcePositionsModelPrivate::peakGain
 
     float getDuration() const { return (float) ((double) length / rate); }   // :367 (edit length)
     float getStartPosition(int slice) const {                                // :261-268
@@ -945,11 +946,30 @@ int zlo_read_positions(zl_ctx* ctx, int32_t clip, float* gains, float* progress,
             }
     *count = n; return ZL_OK;
 }
+// ClipAudioSourcePositionsModel::peakGain / firstProgress   lib/ClipAudioSourcePositionsModel.cpp:160-185
+int zlo_clip_peak_gain(zl_ctx* ctx, int32_t clip, float* peakOut, double* firstProgress) {
+    Clip* c = ctx ? findClip(ctx, clip) : nullptr; if (!c || !peakOut) return ZL_ERR_INVALID;
+    float peak{0.0f};
+    double progress{-1.0f};
+    int n = 0;
+    for (Channel& ch : ctx->channels)
+        for (Voice& v : ch.voices)
+            if (v.isPlaying && v.clip == c && v.hasPositionId && n < 32) {
+                peak = std::max(peak, v.posGain);
+                if (n == 0) progress = v.posProgress;
+                ++n;
+            }
+    if (std::abs(c->peakGain - peak) > 0.01) c->peakGain = peak;
+    *peakOut = c->peakGain;
+    if (firstProgress) *firstProgress = progress;
+    return ZL_OK;
+}
 int zlo_kernel_timing(zl_ctx* ctx, int32_t) { return ctx ? ZL_OK : ZL_ERR_INVALID; }   // no kernels in the oracle
 int zlo_kernel_time(zl_ctx* ctx, double* ms, uint64_t* n) { if (!ctx) return ZL_ERR_INVALID; if (ms) *ms = 0.0; if (n) *n = 0; return ZL_OK; }
 int zlo_last_voice_frames(zl_ctx* ctx, uint64_t* vf) { if (!ctx || !vf) return ZL_ERR_INVALID; *vf = ctx->voiceFrames; return ZL_OK; }
 int zlo_dropped_commands(zl_ctx* ctx, uint64_t* n) { if (!ctx || !n) return ZL_ERR_INVALID; *n = ctx->dropped; return ZL_OK; }
 int zlo_launch_count(zl_ctx*, uint64_t* n) { if (n) *n = 0; return ZL_OK; }
+int zlo_host_profile(zl_ctx* ctx, double* a, double* b, uint64_t* n) { if (!ctx) return ZL_ERR_INVALID; if (a) *a = 0; if (b) *b = 0; if (n) *n = 0; return ZL_OK; }
 
 int zlo_thumb_build(zl_ctx* ctx, int32_t id, int32_t spt) {
     Clip* c = ctx ? findClip(ctx, id) : nullptr; if (!c || spt < 1) return ZL_ERR_INVALID;
@@ -1237,6 +1257,12 @@ int zlo_bounce_wav(zl_ctx* ctx, int32_t s, int32_t b, int32_t which, int32_t bit
     return wavEncode(l, l + N, N, ctx->cfg.sample_rate, bits, out, cap, size);
 }
 
+// One mix spanning GPUs: the oracle is one process; a group of one reduces to itself, larger groups are summed by the test
+// harness (tests/test_shard_gloo.py) in rank order.
+int zlo_comm_unique_id(void* id128) { if (!id128) return ZL_ERR_INVALID; memset(id128, 0, 128); return ZL_OK; }
+int zlo_comm_init(zl_ctx* ctx, const void* id, int32_t rank, int32_t nranks) { return (ctx && id && nranks >= 1 && rank >= 0 && rank < nranks) ? ZL_OK : ZL_ERR_INVALID; }
+int zlo_mix_reduce(zl_ctx* ctx, int32_t) { return ctx ? ZL_OK : ZL_ERR_INVALID; }
+int zlo_comm_destroy(zl_ctx* ctx) { return ctx ? ZL_OK : ZL_ERR_INVALID; }
 int zlo_host_alloc(void** p, size_t bytes) { if (!p) return ZL_ERR_INVALID; *p = malloc(bytes ? bytes : 1); return *p ? ZL_OK : ZL_ERR_NOMEM; }
 int zlo_host_free(void* p) { free(p); return ZL_OK; }
 
