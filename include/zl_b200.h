@@ -364,6 +364,38 @@ ZL_EXPORT int ZL_FN(wav_encode)(zl_ctx* ctx, const float* l, const float* r, int
 ZL_EXPORT int ZL_FN(bounce_wav)(zl_ctx* ctx, int32_t session, int32_t bus, int32_t which, int32_t bits,
                                 void* out, uint64_t cap, uint64_t* size);
 
+/* ---- n2: the command-scheduling front-end ----------------------- */
+/* SyncTimer's 96-ppqn step ring (32768 steps) as a host object: commands are scheduled `delay` steps ahead
+ * (SyncTimer::scheduleClipCommand, lib/SyncTimer.cpp:1011-1048, same-step merge of equivalentTo commands), and
+ * zl_sched_advance walks the steps that fall due in each of `nblocks` JACK periods the way SyncTimerPrivate::process does
+ * (:452-702): it fills playhead / playhead_usecs / subbeat_usecs of clocks[] (the caller sets current_usecs / next_usecs, what
+ * jack_get_cycle_times would report) and returns the commands that fire, each with its period and the tick
+ * SamplerSynth::handleClipCommand is given (:553-558) - ready for zl_command_batch + zl_render.  Pure host logic. */
+typedef struct zl_sched zl_sched;
+enum { ZL_SCHED_CLIP_COMMAND = 0, ZL_SCHED_CHANNEL_ENABLED = 1 };
+typedef struct {
+    int32_t kind;               /* ZL_SCHED_* */
+    int32_t block;              /* period of this advance the event belongs to */
+    uint64_t tick;              /* jackPlayhead when it fired */
+    zl_clip_command cmd;        /* ZL_SCHED_CLIP_COMMAND */
+    int32_t channel, enabled;   /* ZL_SCHED_CHANNEL_ENABLED: SamplerSynth::setChannelEnabled(channel, enabled) */
+    int32_t reserved;
+} zl_sched_event;
+ZL_EXPORT int ZL_FN(sched_create)(double sample_rate, int32_t buffer_size, zl_sched** out);
+ZL_EXPORT int ZL_FN(sched_destroy)(zl_sched* s);
+ZL_EXPORT int ZL_FN(sched_start)(zl_sched* s, int32_t bpm);                       /* SyncTimer::start  :870-879 */
+ZL_EXPORT int ZL_FN(sched_stop)(zl_sched* s);                                     /* SyncTimer::stop   :881-924: what still waits in the ring is dropped */
+ZL_EXPORT int ZL_FN(sched_set_bpm)(zl_sched* s, int32_t bpm);                     /* SyncTimer::setBpm :955-975 */
+ZL_EXPORT int ZL_FN(sched_schedule)(zl_sched* s, const zl_clip_command* cmd, uint64_t delay);
+ZL_EXPORT int ZL_FN(sched_schedule_channel_enabled)(zl_sched* s, uint64_t delay, int32_t channel, int32_t enabled);
+ZL_EXPORT int ZL_FN(sched_queue_start)(zl_sched* s, int32_t clip, int32_t midi_channel);   /* queueClipToStartOnChannel :816-832 */
+ZL_EXPORT int ZL_FN(sched_queue_stop)(zl_sched* s, int32_t clip, int32_t midi_channel);    /* queueClipToStopOnChannel  :834-860 */
+/* *count = events produced (also when cap was too small: ZL_ERR_STATE, and the ring has moved on - size cap generously) */
+ZL_EXPORT int ZL_FN(sched_advance)(zl_sched* s, int32_t nblocks, int32_t nframes, zl_block_clock* clocks,
+                                   zl_sched_event* events, int32_t cap, int32_t* count);
+ZL_EXPORT int ZL_FN(sched_state)(zl_sched* s, uint64_t* playhead, uint64_t* playhead_usecs, uint64_t* subbeat_usecs,
+                                 uint64_t* cumulative_beat, int32_t* beat, uint64_t* schedule_ahead);
+
 /* ---- one mix spanning GPUs ------------------------------------- */
 /* The only exchange step on the path: when the dry ports of buses rendered on different GPUs feed ONE stereo pair (what JACK
  * does when every track's dryOut is connected to the same system:playback ports, lib/JackPassthrough.cpp:94-101), the

@@ -13,6 +13,7 @@ ZL_Q1_TAP_GAIN, ZL_Q2_PREINC, ZL_Q3_RENOTEOFF, ZL_QUIRKS_FAITHFUL = 1, 2, 4, 7
 ZL_OUT_RAW, ZL_OUT_DRY, ZL_OUT_FX1, ZL_OUT_FX2 = 1, 2, 4, 8
 ZL_OUT_MASTER, ZL_OUT_LEVELS, ZL_OUT_RMS, ZL_OUT_ALL = 16, 32, 64, 127
 ZL_BUS_RAW, ZL_BUS_DRY, ZL_BUS_FX1, ZL_BUS_FX2 = 0, 1, 2, 3
+ZL_SCHED_CLIP_COMMAND, ZL_SCHED_CHANNEL_ENABLED = 0, 1
 
 
 class zl_config(C.Structure):
@@ -41,6 +42,11 @@ class zl_clip_command(C.Structure):
 class zl_block_clock(C.Structure):
     _fields_ = [("current_usecs", C.c_uint64), ("next_usecs", C.c_uint64), ("playhead", C.c_uint64),
                 ("playhead_usecs", C.c_uint64), ("subbeat_usecs", C.c_uint64)]
+
+
+class zl_sched_event(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("block", C.c_int32), ("tick", C.c_uint64), ("cmd", zl_clip_command),
+                ("channel", C.c_int32), ("enabled", C.c_int32), ("reserved", C.c_int32)]
 
 
 class zl_passthrough_params(C.Structure):
@@ -115,6 +121,17 @@ SIGNATURES = {
     "read_positions": (C.c_int, [_ctx, C.c_int32, _f32p, _f32p, C.c_int32, _P(C.c_int32)]),
     "clip_peak_gain": (C.c_int, [_ctx, C.c_int32, _P(C.c_float), _P(C.c_double)]),
     "host_profile": (C.c_int, [_ctx, _P(C.c_double), _P(C.c_double), _P(C.c_uint64)]),
+    "sched_create": (C.c_int, [C.c_double, C.c_int32, _P(C.c_void_p)]),
+    "sched_destroy": (C.c_int, [C.c_void_p]),
+    "sched_start": (C.c_int, [C.c_void_p, C.c_int32]),
+    "sched_stop": (C.c_int, [C.c_void_p]),
+    "sched_set_bpm": (C.c_int, [C.c_void_p, C.c_int32]),
+    "sched_schedule": (C.c_int, [C.c_void_p, _P(zl_clip_command), C.c_uint64]),
+    "sched_schedule_channel_enabled": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int32, C.c_int32]),
+    "sched_queue_start": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "sched_queue_stop": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "sched_advance": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, _P(zl_block_clock), _P(zl_sched_event), C.c_int32, _P(C.c_int32)]),
+    "sched_state": (C.c_int, [C.c_void_p, _P(C.c_uint64), _P(C.c_uint64), _P(C.c_uint64), _P(C.c_uint64), _P(C.c_int32), _P(C.c_uint64)]),
     "comm_unique_id": (C.c_int, [C.c_void_p]),
     "comm_init": (C.c_int, [_ctx, C.c_void_p, C.c_int32, C.c_int32]),
     "mix_reduce": (C.c_int, [_ctx, C.c_int32]),

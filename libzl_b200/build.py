@@ -5,7 +5,7 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SOURCES = ["zl_api.cu", "zl_render.cu", "zl_thumb.cu", "zl_wav.cu"]
+SOURCES = ["zl_api.cu", "zl_render.cu", "zl_thumb.cu", "zl_wav.cu", "zl_sched.cpp"]
 HEADERS = ["zl_device.cuh", "zl_voice.cuh", os.path.join("..", "..", "include", "zl_b200.h")]
 OUT = os.path.join(HERE, "libzl_b200.so")
 # host side above the C ABI: the reference's C++ classes (include/zl/*.h) and its libzl.h-compatible C symbols, plain g++

@@ -11,7 +11,8 @@
 //   * Qt (containers, strings, the object tree; signals get empty bodies below where moc would have generated them),
 //   * JACK: an in-process stand-in - ports are float buffers, the test calls the registered process callbacks in client
 //     order with the cycle times it chooses (jack_get_cycle_times),
-//   * SyncTimer: only the three playhead getters the voice reads and the command pool (the step ring itself is row n2),
+//   * SyncTimer: the reference's own lib/SyncTimer.cpp (see synctimer_ref.cpp); the voice scenarios inject the playhead values
+//     the voice reads, the scheduler scenarios run its step ring for real (row n2),
 //   * ClipAudioSource: lib/ClipAudioSource.cpp is a tracktion_engine Edit wrapper; the voice only calls its getters, so the
 //     class declared by lib/ClipAudioSource.h gets a parameter-holder implementation here (getStartPosition /
 //     getStopPosition restated from lib/ClipAudioSource.cpp:261-277 - row a8 stays a restatement),
@@ -127,6 +128,8 @@ jack_nframes_t jack_frame_time(const jack_client_t*) { return gJack.currentFrame
 jack_nframes_t jack_last_frame_time(const jack_client_t*) { return gJack.currentFrames; }
 jack_time_t jack_frames_to_time(const jack_client_t*, jack_nframes_t) { return gJack.currentUsecs; }
 jack_transport_state_t jack_transport_query(const jack_client_t*, jack_position_t*) { return JackTransportStopped; }
+int jack_set_latency_callback(jack_client_t*, JackLatencyCallback, void*) { return 0; }
+void jack_port_get_latency_range(jack_port_t*, jack_latency_callback_mode_t, jack_latency_range_t* range) { range->min = 0; range->max = 0; }
 uint32_t jack_midi_get_event_count(void*) { return 0; }
 int jack_midi_event_get(jack_midi_event_t*, void*, uint32_t) { return -1; }
 void jack_midi_clear_buffer(void*) {}
@@ -135,26 +138,11 @@ jack_midi_data_t* jack_midi_event_reserve(void*, jack_nframes_t, size_t) { retur
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// SyncTimer: the playhead the voice reads (lib/SyncTimer.cpp:946-1009) and the command pool (:1065-1100)
-class SyncTimerPrivate {
-public:
-    quint64 jackPlayhead = 0, jackPlayheadUsecs = 0, jackSubbeatLengthInMicroseconds = 0, bpm = 120;
-    // SamplerSynth declares SyncTimerPrivate a friend: this is how SyncTimer hands commands over (lib/SyncTimer.cpp:553-558)
-    static void handle(ClipCommand* c, quint64 tick) { SamplerSynth::instance()->handleClipCommand(c, tick); }
-    static void enable(int channel, bool en) { SamplerSynth::instance()->setChannelEnabled(channel, en); }
-};
-namespace { SyncTimerPrivate* gTimerPrivate = nullptr; }
-SyncTimer::SyncTimer(QObject* parent) : QObject(parent), d(new SyncTimerPrivate) { gTimerPrivate = d; }
-SyncTimer::~SyncTimer() { delete d; }
-float SyncTimer::subbeatCountToSeconds(quint64 bpm, quint64 beats) const { return (float) ((beats * 60.0) / (bpm * 96.0)); }   // unused by process()
-int SyncTimer::getMultiplier() { return 96; }                                 // BeatSubdivisions  lib/SyncTimer.cpp:95,946-948
-quint64 SyncTimer::getBpm() const { return d->bpm; }
-const quint64& SyncTimer::jackPlayhead() const { return d->jackPlayhead; }
-const quint64& SyncTimer::jackPlayheadUsecs() const { return d->jackPlayheadUsecs; }
-const quint64& SyncTimer::jackSubbeatLengthInMicroseconds() const { return d->jackSubbeatLengthInMicroseconds; }
-ClipCommand* SyncTimer::getClipCommand() { return new ClipCommand; }
-void SyncTimer::deleteClipCommand(ClipCommand* c) { delete c; }
-extern "C" QObject* SyncTimer_instance() { return SyncTimer::instance(); }
+// SyncTimer is the reference's own lib/SyncTimer.cpp (compiled through synctimer_ref.cpp, which also owns these hooks)
+void zlref_timer_inject(unsigned long long playhead, unsigned long long playhead_usecs, unsigned long long subbeat_usecs);
+void zlref_timer_handle(ClipCommand* c, unsigned long long tick);
+void zlref_timer_enable(int channel, bool enabled);
+void zlref_timer_boot();                            // initJuce()'s "syncTimer = SyncTimer::instance()" (lib/libzl.cpp:388-389)
 
 // ---------------------------------------------------------------------------------------------------------------------
 // ClipAudioSource: the class lib/ClipAudioSource.h declares, as the parameter holder the voice and the sound query
@@ -264,6 +252,7 @@ extern "C" {
 ZLREF int zlref_init(double sample_rate, int max_frames) {
     if (gWorld.ready) return (gJack.sampleRate == (jack_nframes_t) sample_rate && max_frames <= gWorld.nframesMax) ? 0 : -1;
     gJack.sampleRate = (jack_nframes_t) sample_rate; gJack.bufferSize = (jack_nframes_t) max_frames; gWorld.nframesMax = max_frames;
+    zlref_timer_boot();                             // the order of initJuce(): the timer, then SamplerSynth::initialize
     SamplerSynth::instance()->initialize(nullptr);
     for (int b = 0; b < 12; ++b) {
         auto* pt = new JackPassthrough(QString(("ZLRefPassthrough" + std::to_string(b)).c_str()));
@@ -316,10 +305,10 @@ ZLREF int zlref_command(int clip, int midi_note, int midi_channel, int start_pla
     c->clip = gWorld.clips[(size_t) clip]; c->midiNote = midi_note; c->midiChannel = midi_channel;
     c->startPlayback = start_playback; c->stopPlayback = stop_playback; c->changeSlice = change_slice; c->slice = slice;
     c->changeLooping = change_looping; c->looping = looping; c->changeVolume = change_volume; c->volume = volume;
-    SyncTimerPrivate::handle(c, tick);
+    zlref_timer_handle(c, tick);
     return 0;
 }
-ZLREF int zlref_channel_enabled(int midi_channel, int enabled) { SyncTimerPrivate::enable(midi_channel, enabled != 0); return 0; }
+ZLREF int zlref_channel_enabled(int midi_channel, int enabled) { zlref_timer_enable(midi_channel, enabled != 0); return 0; }
 ZLREF int zlref_passthrough_set(int bus, float dry, float fx1, float fx2, float pan, int muted) {
     if (bus < 0 || bus >= 12) return -1;
     JackPassthrough* p = gWorld.passthrough[(size_t) bus];
@@ -332,9 +321,7 @@ ZLREF int zlref_process(int nframes, unsigned long long current_usecs, unsigned 
                         unsigned long long playhead_usecs, unsigned long long subbeat_usecs) {
     if (!gWorld.ready || nframes > gWorld.nframesMax) return -1;
     gJack.currentUsecs = current_usecs; gJack.nextUsecs = next_usecs; gJack.periodUsecs = (float) (next_usecs - current_usecs);
-    SyncTimer::instance();
-    SyncTimerPrivate* st = gTimerPrivate;
-    st->jackPlayhead = playhead; st->jackPlayheadUsecs = playhead_usecs; st->jackSubbeatLengthInMicroseconds = subbeat_usecs;
+    zlref_timer_inject(playhead, playhead_usecs, subbeat_usecs);
     for (int b = 0; b < 12; ++b) { _jack_client* c = channelClient(b); if (c && c->cb) c->cb((jack_nframes_t) nframes, c->arg); }
     for (int b = 0; b < 12; ++b) { _jack_client* c = passthroughClient(b); if (c && c->cb) c->cb((jack_nframes_t) nframes, c->arg); }
     for (auto* c : gJack.clients) if (c->name.rfind("AudioLevels-", 0) == 0 && c->cb) c->cb((jack_nframes_t) nframes, c->arg);
@@ -344,6 +331,22 @@ ZLREF int zlref_process(int nframes, unsigned long long current_usecs, unsigned 
 }
 // which: 0 raw (the SamplerChannel ports), 1 dry, 2 fx1, 3 fx2.  n + 1 floats are available for the raw ports (index n is
 // where quirk Q2 puts the last frame).
+// the JACK cycle times alone (the scheduler driver of synctimer_ref.cpp runs SyncTimer's process itself)
+ZLREF void zlref_set_cycle(unsigned long long current_usecs, unsigned long long next_usecs) {
+    gJack.currentUsecs = current_usecs; gJack.nextUsecs = next_usecs; gJack.periodUsecs = (float) (next_usecs - current_usecs);
+}
+// the sampler side of a cycle without touching the timer: channels, passthroughs, meters
+ZLREF int zlref_process_sampler(int nframes) {
+    if (!gWorld.ready || nframes > gWorld.nframesMax) return -1;
+    for (int b = 0; b < 12; ++b) { _jack_client* c = channelClient(b); if (c && c->cb) c->cb((jack_nframes_t) nframes, c->arg); }
+    for (int b = 0; b < 12; ++b) { _jack_client* c = passthroughClient(b); if (c && c->cb) c->cb((jack_nframes_t) nframes, c->arg); }
+    for (auto* c : gJack.clients) if (c->name.rfind("AudioLevels-", 0) == 0 && c->cb) c->cb((jack_nframes_t) nframes, c->arg);
+    gJack.currentFrames += (jack_nframes_t) nframes;
+    zl_ref_shim_now_msecs += 1;
+    return 0;
+}
+ZLREF void* zlref_clip_ptr(int clip) { return (clip >= 0 && clip < (int) gWorld.clips.size()) ? gWorld.clips[(size_t) clip] : nullptr; }
+ZLREF int zlref_clip_index(const void* clip) { for (size_t i = 0; i < gWorld.clips.size(); ++i) if (gWorld.clips[i] == clip) return (int) i; return -1; }
 ZLREF int zlref_read(int bus, int which, float* left, float* right, int n) {
     static const char* names[4][2] = {{"left_out", "right_out"}, {"dryOutLeft", "dryOutRight"}, {"wetOutFx1Left", "wetOutFx1Right"}, {"wetOutFx2Left", "wetOutFx2Right"}};
     _jack_client* c = which == 0 ? channelClient(bus) : passthroughClient(bus);

@@ -32,6 +32,11 @@ jack_nframes_t jack_frame_time(const jack_client_t* client);
 jack_nframes_t jack_last_frame_time(const jack_client_t* client);
 jack_time_t jack_frames_to_time(const jack_client_t* client, jack_nframes_t frames);
 jack_transport_state_t jack_transport_query(const jack_client_t* client, jack_position_t* pos);
+typedef enum JackLatencyCallbackMode { JackCaptureLatency, JackPlaybackLatency } jack_latency_callback_mode_t;
+typedef struct _jack_latency_range { jack_nframes_t min, max; } jack_latency_range_t;
+typedef void (*JackLatencyCallback)(jack_latency_callback_mode_t mode, void* arg);
+int jack_set_latency_callback(jack_client_t* client, JackLatencyCallback cb, void* arg);
+void jack_port_get_latency_range(jack_port_t* port, jack_latency_callback_mode_t mode, jack_latency_range_t* range);
 #ifdef __cplusplus
 }
 #endif

@@ -18,6 +18,7 @@
 #include <mutex>
 #include <string>
 #include <thread>
+#include <type_traits>
 #include <unordered_map>
 #include <vector>
 
@@ -174,6 +175,7 @@ public:
     T& next() { last_ = i_; return (*l_)[i_++]; }
     void remove() { l_->erase(l_->begin() + (long) last_); i_ = last_; }
     T& value() { return (*l_)[last_]; }
+    void setValue(const T& v) { (*l_)[last_] = v; }
 private:
     QList<T>* l_; size_t i_ = 0, last_ = 0;
 };
@@ -211,9 +213,15 @@ public:
     QVariant(double v) : d_(v), valid_(true) {}
     QVariant(qint64 v) : d_((double) v), valid_(true) {}
     QVariant(const QString& s) : s_(s), valid_(true) {}
-    template <typename T> void setValue(const T& v) { d_ = (double) v; valid_ = true; }
+    template <typename T> void setValue(const T& v) {
+        if constexpr (std::is_pointer<T>::value) p_ = (void*) v; else d_ = (double) v;
+        valid_ = true;
+    }
     template <typename T> static QVariant fromValue(const T& v) { QVariant q; q.setValue<T>(v); return q; }
-    template <typename T> T value() const { return (T) d_; }
+    template <typename T> T value() const {
+        if constexpr (std::is_pointer<T>::value) return (T) p_; else return (T) d_;
+    }
+    void clear() { d_ = 0.0; s_ = QString(); p_ = nullptr; valid_ = false; }
     bool toBool() const { return d_ != 0.0; }
     int toInt() const { return (int) d_; }
     float toFloat() const { return (float) d_; }
@@ -222,7 +230,7 @@ public:
     bool isValid() const { return valid_; }
     bool operator==(const QVariant& o) const { return d_ == o.d_ && s_ == o.s_; }
 private:
-    double d_ = 0.0; QString s_; bool valid_ = false;
+    double d_ = 0.0; QString s_; void* p_ = nullptr; bool valid_ = false;
 };
 typedef QList<QVariant> QVariantList;
 
@@ -257,6 +265,17 @@ public:
     static void msleep(unsigned long) {}
     static void usleep(unsigned long) {}
     static QThread* currentThread() { return nullptr; }
+    void started() {}                                   // signals
+    void finished() {}
+};
+struct QMetaObject {
+    template <typename... A> static bool invokeMethod(A&&...) { return true; }       // queued invocations are never delivered: no event loop here
+};
+class QProcess : public QObject {
+public:
+    void start(const QString&, const QStringList& = QStringList()) {}
+    bool waitForFinished(int = 30000) { return true; }
+    QByteArray readAllStandardOutput() { return QByteArray(); }
 };
 class QCoreApplication : public QObject {
 public:

@@ -2,6 +2,8 @@
 #pragma once
 #include <juce_core/juce_core.h>
 namespace tracktion_engine {
-class Engine; class Edit; class AudioTrack; class AudioFile; class AudioFileInfo;
+class DeviceManager { public: double getCpuUsage() const { return 0.0; } };
+class Engine { public: DeviceManager& getDeviceManager() { static DeviceManager m; return m; } };
+class Edit; class AudioTrack; class AudioFile; class AudioFileInfo;
 class WaveAudioClip : public juce::ReferenceCountedObject { public: using Ptr = juce::ReferenceCountedObjectPtr<WaveAudioClip>; };
 }

@@ -22,6 +22,7 @@
 #include "../include/zl_b200.h"
 
 #include <algorithm>
+#include <array>
 #include <atomic>
 #include <cmath>
 #include <cstdio>
@@ -1255,6 +1256,211 @@ int zlo_bounce_wav(zl_ctx* ctx, int32_t s, int32_t b, int32_t which, int32_t bit
     else if ((ctx->cfg.outputs & (ZL_OUT_RAW << which)) && !ctx->bus[which].empty()) l = ctx->bus[which].data() + ((size_t) s * (size_t) ctx->cfg.buses_per_session + (size_t) b) * 2 * N;
     if (!l || N < 1) return ZL_ERR_STATE;
     return wavEncode(l, l + N, N, ctx->cfg.sample_rate, bits, out, cap, size);
+}
+
+// ---- row n2: SyncTimer's step ring, restated from lib/SyncTimer.cpp ----------------------------------------
+// StepData :42-77, SyncTimerPrivate (ring set-up :279-290, delayedStep :346-362, hiResTimerCallback :392-415, process :452-702,
+// updateScheduleAheadAmount :712-715), SyncTimer::start/stop :870-924, setBpm :955-975, queueClipToStart/StopOnChannel :816-860,
+// scheduleClipCommand :1011-1048.  Pinned against the reference's own compiled SyncTimer.cpp (oracle/ref/synctimer_ref.cpp).
+namespace {
+struct OStepData {
+    std::vector<zl_clip_command> clipCommands;
+    std::vector<std::array<int, 3>> timerCommands;            // (operation, parameter, parameter2)
+    OStepData* previous = nullptr; OStepData* next = nullptr;
+    uint64_t index = 0;
+    bool played = true;
+    void ensureFresh() { if (played) { played = false; timerCommands.clear(); clipCommands.clear(); } }
+};
+const uint64_t OStepRingCount = 32768, OBeatSubdivisions = 96, ONanosecondsPerMinute = 60000000000ull;
+uint64_t oSubbeatCountToNanoseconds(const uint64_t& bpm, const uint64_t& subBeatCount) { return (subBeatCount * ONanosecondsPerMinute) / (bpm * OBeatSubdivisions); }
+float oNanosecondsToSubbeatCount(const uint64_t& bpm, const uint64_t& nanoseconds) { return nanoseconds / (ONanosecondsPerMinute / (bpm * OBeatSubdivisions)); }
+}  // namespace
+struct zl_sched {
+    std::vector<OStepData> stepRing = std::vector<OStepData>(OStepRingCount);
+    OStepData* stepReadHead = nullptr;
+    uint64_t stepNextPlaybackPosition = 0, jackPlayhead = 0, jackNextPlaybackPosition = 0, jackSubbeatLengthInMicroseconds = 0, jackLatency = 0;
+    uint64_t stepReadHeadOnStart = 0, cumulativeBeat = 0, scheduleAheadAmount = 0, timerBpm = 120;
+    double jackPlayheadBpm = 120;
+    int beat = 0;
+    bool isPaused = true;
+    zl_sched() {
+        OStepData* previous = &stepRing[OStepRingCount - 1];
+        for (uint64_t i = 0; i < OStepRingCount; ++i) { stepRing[i].index = i; previous->next = &stepRing[i]; stepRing[i].previous = previous; previous = &stepRing[i]; }
+        stepReadHead = &stepRing[0];
+    }
+    OStepData* delayedStep(uint64_t delay) {
+        uint64_t step = 0;
+        if (isPaused) step = (stepReadHead->index + delay + 1) % OStepRingCount;
+        else step = (stepReadHeadOnStart + std::max(cumulativeBeat + delay, jackPlayhead + 1)) % OStepRingCount;
+        OStepData* stepData = &stepRing[step];
+        stepData->ensureFresh();
+        return stepData;
+    }
+    void updateScheduleAheadAmount() { scheduleAheadAmount = (oNanosecondsToSubbeatCount(timerBpm, jackLatency * (float) 1000000)) + 1; }
+    void setBpm(uint64_t bpm) {
+        if (timerBpm != bpm) {
+            timerBpm = bpm;
+            jackSubbeatLengthInMicroseconds = oSubbeatCountToNanoseconds(timerBpm, 1) / 1000;
+            updateScheduleAheadAmount();
+            delayedStep(0)->timerCommands.push_back({10 /* SetBpmOperation */, (int) bpm, 0});
+        }
+    }
+    void scheduleClipCommand(const zl_clip_command& command, uint64_t delay) {
+        OStepData* stepData = delayedStep(delay);
+        bool foundExisting = false;
+        for (zl_clip_command& existingCommand : stepData->clipCommands) {
+            if (equivalentTo(existingCommand, command)) {
+                if (command.change_looping) { existingCommand.looping = command.looping; existingCommand.change_looping = true; }
+                if (command.change_pitch) { existingCommand.pitch_change = command.pitch_change; existingCommand.change_pitch = true; }
+                if (command.change_speed) { existingCommand.speed_ratio = command.speed_ratio; existingCommand.change_speed = true; }
+                if (command.change_gain_db) { existingCommand.gain_db = command.gain_db; existingCommand.change_gain_db = true; }
+                if (command.change_volume) { existingCommand.volume = command.volume; existingCommand.change_volume = true; }
+                if (command.start_playback) existingCommand.start_playback = true;
+                foundExisting = true;
+            }
+        }
+        if (!foundExisting) stepData->clipCommands.push_back(command);
+    }
+};
+int zlo_sched_create(double sample_rate, int32_t buffer_size, zl_sched** out) {
+    if (!out || !(sample_rate > 0) || buffer_size < 1) return ZL_ERR_INVALID;
+    zl_sched* d = new zl_sched;
+    d->jackSubbeatLengthInMicroseconds = oSubbeatCountToNanoseconds(d->timerBpm, 1) / 1000;
+    d->jackLatency = (1000 * (double) buffer_size) / (double) sample_rate;
+    d->updateScheduleAheadAmount();
+    *out = d; return ZL_OK;
+}
+int zlo_sched_destroy(zl_sched* d) { if (!d) return ZL_ERR_INVALID; delete d; return ZL_OK; }
+int zlo_sched_start(zl_sched* d, int32_t bpm) {
+    if (!d || bpm < 1) return ZL_ERR_INVALID;
+    d->setBpm((uint64_t) bpm);
+    d->stepReadHeadOnStart = d->stepReadHead->index;
+    d->isPaused = false;
+    return ZL_OK;
+}
+int zlo_sched_stop(zl_sched* d) {
+    if (!d) return ZL_ERR_INVALID;
+    d->isPaused = true;
+    d->beat = 0; d->cumulativeBeat = 0; d->jackPlayhead = 0;
+    // :893-917, literally: walk the whole ring from the read head; every command still waiting has its volume forced to 0 and is
+    // re-scheduled at delay 0 - isPaused is already true here (pausedChanged is a direct connection, :750-752), so that is the
+    // step after the read head.  The read head's own commands move there; that step then meets its own commands (merged into
+    // themselves) and is marked played; the first later command finds it played, clears it, and the rest pile up there, muted,
+    // to come out when the read head next passes.
+    for (uint64_t step = 0; step < OStepRingCount; ++step) {
+        OStepData* stepData = &d->stepRing[(step + d->stepReadHead->index) % OStepRingCount];
+        if (!stepData->played) {
+            for (size_t i = 0; i < stepData->clipCommands.size(); ++i) {
+                zl_clip_command c = stepData->clipCommands[i];
+                c.change_volume = 1; c.volume = 0.0f;
+                stepData->clipCommands[i] = c;
+                d->scheduleClipCommand(c, 0);
+            }
+            stepData->played = true;
+        }
+    }
+    return ZL_OK;
+}
+int zlo_sched_set_bpm(zl_sched* d, int32_t bpm) { if (!d || bpm < 1) return ZL_ERR_INVALID; d->setBpm((uint64_t) bpm); return ZL_OK; }
+int zlo_sched_schedule(zl_sched* d, const zl_clip_command* cmd, uint64_t delay) { if (!d || !cmd) return ZL_ERR_INVALID; d->scheduleClipCommand(*cmd, delay); return ZL_OK; }
+int zlo_sched_schedule_channel_enabled(zl_sched* d, uint64_t delay, int32_t channel, int32_t enabled) {
+    if (!d) return ZL_ERR_INVALID;
+    d->delayedStep(delay)->timerCommands.push_back({8 /* SamplerChannelEnabledStateOperation */, channel, enabled});
+    return ZL_OK;
+}
+int zlo_sched_queue_start(zl_sched* d, int32_t clip, int32_t midiChannel) {
+    if (!d) return ZL_ERR_INVALID;
+    zl_clip_command command; zlo_clip_command_default(&command);
+    command.clip = clip; command.midi_channel = midiChannel; command.midi_note = 60; command.change_volume = true; command.volume = 1.0;
+    command.looping = true; command.stop_playback = true; command.start_playback = true;
+    const uint64_t nextZeroBeat = d->isPaused ? 0 : (OBeatSubdivisions * 4) - (d->cumulativeBeat % (OBeatSubdivisions * 4));
+    d->scheduleClipCommand(command, d->cumulativeBeat + nextZeroBeat < d->jackPlayhead ? nextZeroBeat + OBeatSubdivisions * 4 : nextZeroBeat);
+    return ZL_OK;
+}
+int zlo_sched_queue_stop(zl_sched* d, int32_t clip, int32_t midiChannel) {
+    if (!d) return ZL_ERR_INVALID;
+    for (uint64_t step = 0; step < OStepRingCount; ++step) {
+        OStepData* stepData = &d->stepRing[step];
+        if (!stepData->played)
+            for (size_t i = 0; i < stepData->clipCommands.size(); ++i)
+                if (stepData->clipCommands[i].clip == clip) { stepData->clipCommands.erase(stepData->clipCommands.begin() + (long) i); break; }
+    }
+    zl_clip_command command; zlo_clip_command_default(&command);
+    command.clip = clip; command.midi_channel = midiChannel; command.midi_note = 60; command.stop_playback = true;
+    d->delayedStep(0)->clipCommands.push_back(command);
+    return ZL_OK;
+}
+int zlo_sched_advance(zl_sched* d, int32_t nblocks, int32_t nframesI, zl_block_clock* clocks, zl_sched_event* events, int32_t cap, int32_t* count) {
+    if (!d || nblocks < 1 || nframesI < 1 || !clocks || !count || cap < 0 || (cap && !events)) return ZL_ERR_INVALID;
+    std::vector<zl_sched_event> out;
+    const uint32_t nframes = (uint32_t) nframesI;
+    for (int b = 0; b < nblocks; ++b) {
+        const uint64_t current_usecs = clocks[b].current_usecs, next_usecs = clocks[b].next_usecs;
+        const uint64_t microsecondsPerFrame = (next_usecs - current_usecs) / nframes;
+        double thisStepBpm{d->jackPlayheadBpm};
+        double thisStepSubbeatLengthInMicroseconds{double(oSubbeatCountToNanoseconds(d->jackPlayheadBpm, 1)) / 1000.0};
+        if (!d->isPaused) {
+            if (d->jackPlayhead == 0) d->jackNextPlaybackPosition = current_usecs;
+        }
+        if (d->stepNextPlaybackPosition == 0) d->stepNextPlaybackPosition = current_usecs;
+        uint32_t firstAvailableFrame{0}, relativePosition{0};
+        while (d->stepNextPlaybackPosition < next_usecs && firstAvailableFrame < nframes) {
+            OStepData* stepData = d->stepReadHead;
+            d->stepReadHead = d->stepReadHead->next;
+            if (d->stepNextPlaybackPosition <= current_usecs) { relativePosition = firstAvailableFrame; ++firstAvailableFrame; }
+            else {
+                relativePosition = std::clamp<uint32_t>((d->stepNextPlaybackPosition - current_usecs) / microsecondsPerFrame, firstAvailableFrame, nframes - 1);
+                firstAvailableFrame = relativePosition;
+            }
+            if (!stepData->played) {
+                for (const zl_clip_command& clipCommand : stepData->clipCommands) {
+                    zl_sched_event ev; memset(&ev, 0, sizeof ev);
+                    ev.kind = ZL_SCHED_CLIP_COMMAND; ev.block = b; ev.tick = d->jackPlayhead; ev.cmd = clipCommand;
+                    out.push_back(ev);
+                }
+                for (const auto& command : stepData->timerCommands) {
+                    if (command[0] == 8) {
+                        zl_sched_event ev; memset(&ev, 0, sizeof ev);
+                        ev.kind = ZL_SCHED_CHANNEL_ENABLED; ev.block = b; ev.tick = d->jackPlayhead; ev.channel = command[1]; ev.enabled = command[2];
+                        out.push_back(ev);
+                    } else if (command[0] == 10) {
+                        const uint64_t newBpm{std::clamp<uint64_t>(uint64_t(command[1]), 50, 200)};
+                        d->setBpm(newBpm);
+                        thisStepBpm = newBpm;
+                    }
+                }
+                stepData->played = true;
+            }
+            if (d->jackPlayheadBpm != thisStepBpm) {
+                d->jackPlayheadBpm = thisStepBpm;
+                thisStepSubbeatLengthInMicroseconds = oSubbeatCountToNanoseconds(d->jackPlayheadBpm, 1) / 1000;
+            }
+            if (!d->isPaused) {
+                ++d->jackPlayhead;
+                d->jackNextPlaybackPosition += thisStepSubbeatLengthInMicroseconds;
+            }
+            d->stepNextPlaybackPosition += thisStepSubbeatLengthInMicroseconds;
+        }
+        clocks[b].playhead = d->isPaused ? d->stepReadHead->index : d->jackPlayhead;                      // :990-1009
+        clocks[b].playhead_usecs = d->isPaused ? d->stepNextPlaybackPosition : d->jackNextPlaybackPosition;
+        clocks[b].subbeat_usecs = d->jackSubbeatLengthInMicroseconds;
+        if (!d->isPaused)                                                                                  // hiResTimerCallback
+            while (d->cumulativeBeat < (d->jackPlayhead + (d->scheduleAheadAmount * 2))) { d->beat = (d->beat + 1) % (OBeatSubdivisions * 4); ++d->cumulativeBeat; }
+    }
+    *count = (int32_t) out.size();
+    if ((int32_t) out.size() > cap) return ZL_ERR_STATE;
+    if (!out.empty()) memcpy(events, out.data(), out.size() * sizeof(zl_sched_event));
+    return ZL_OK;
+}
+int zlo_sched_state(zl_sched* d, uint64_t* playhead, uint64_t* playhead_usecs, uint64_t* subbeat_usecs, uint64_t* cumulative_beat, int32_t* beat, uint64_t* schedule_ahead) {
+    if (!d) return ZL_ERR_INVALID;
+    if (playhead) *playhead = d->isPaused ? d->stepReadHead->index : d->jackPlayhead;
+    if (playhead_usecs) *playhead_usecs = d->isPaused ? d->stepNextPlaybackPosition : d->jackNextPlaybackPosition;
+    if (subbeat_usecs) *subbeat_usecs = d->jackSubbeatLengthInMicroseconds;
+    if (cumulative_beat) *cumulative_beat = d->cumulativeBeat;
+    if (beat) *beat = d->beat;
+    if (schedule_ahead) *schedule_ahead = d->scheduleAheadAmount;
+    return ZL_OK;
 }
 
 // One mix spanning GPUs: the oracle is one process; a group of one reduces to itself, larger groups are summed by the test

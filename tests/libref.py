@@ -59,7 +59,12 @@ def _ref_worker(ops, sample_rate, max_frames, q):
         d.zlref_connect.argtypes = [C.c_char_p, C.c_char_p]
         d.zlref_levels_tick.argtypes = [C.POINTER(C.c_int), f32p]
         assert d.zlref_init(float(sample_rate), int(max_frames)) == 0
+        d.zlref_sched_schedule.argtypes = [C.c_int] * 10 + [C.c_float, C.c_ulonglong]
+        d.zlref_sched_channel_enabled.argtypes = [C.c_ulonglong, C.c_int, C.c_int]
+        d.zlref_sched_cycle.argtypes = [C.c_int, C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_ulonglong), C.POINTER(C.c_int), f32p, C.c_int]
+        d.zlref_sched_state.argtypes = [C.POINTER(C.c_ulonglong)]
         nclips, pending, results = 0, [], []
+        sched_period = 0
         meters = []
         lv_names = ["AudioLevels-SystemCapture", "AudioLevels-SystemPlayback", "AudioLevels-SystemRecorder"] + [f"AudioLevels-Channel{i}" for i in range(1, 11)]
         clip_par = {}
@@ -104,6 +109,49 @@ def _ref_worker(ops, sample_rate, max_frames, q):
                     meters.append((chan, bus))
             elif op[0] == "cmd":
                 pending.append(op[1:])
+            elif op[0] == "sched_start":
+                d.zlref_sched_start(int(op[1]))
+            elif op[0] == "sched_stop":
+                d.zlref_sched_stop()
+            elif op[0] == "sched_bpm":
+                d.zlref_sched_set_bpm(int(op[1]))
+            elif op[0] == "sched_cmd":
+                g = dict(clip=-1, midi_note=-1, midi_channel=-1, start_playback=0, stop_playback=0, change_slice=0, slice=-1,
+                         change_looping=0, looping=0, change_volume=0, volume=0.0)
+                g.update(op[2])
+                assert d.zlref_sched_schedule(g["clip"], g["midi_note"], g["midi_channel"], g["start_playback"], g["stop_playback"], g["change_slice"],
+                                              g["slice"], g["change_looping"], g["looping"], g["change_volume"], float(g["volume"]), int(op[1])) == 0
+            elif op[0] == "sched_queue_start":
+                d.zlref_sched_queue_start(int(op[1]), int(op[2]))
+            elif op[0] == "sched_queue_stop":
+                d.zlref_sched_queue_stop(int(op[1]), int(op[2]))
+            elif op[0] == "sched_enable":
+                d.zlref_sched_channel_enabled(int(op[1]), int(op[2]), int(op[3]))
+            elif op[0] == "sched_run":
+                _, nper, nf = op
+                n = nper * nf
+                out = {k: np.zeros((BUSES, 2, n), np.float32) for k in ("raw", "dry", "fx1", "fx2")}
+                out["clocks"], out["commands"] = [], []
+                period = int(round(nf * 1e6 / sample_rate))
+                l, r = np.zeros(nf, np.float32), np.zeros(nf, np.float32)
+                for b in range(nper):
+                    cur = 1_000_000 + sched_period * period
+                    sched_period += 1
+                    o3 = (C.c_ulonglong * 3)(); ci = (C.c_int * (11 * 256))(); cv = (C.c_float * 256)()
+                    m = d.zlref_sched_cycle(nf, cur, cur + period, o3, ci, cv, 256)
+                    assert 0 <= m <= 256
+                    out["clocks"].append((cur, cur + period, int(o3[0]), int(o3[1]), int(o3[2])))
+                    out["commands"].append([tuple(ci[11 * k:11 * k + 10]) + (float(cv[k]),) for k in range(m)])
+                    for w, k in enumerate(("raw", "dry", "fx1", "fx2")):
+                        for bus in range(BUSES):
+                            d.zlref_read(bus, w, l.ctypes.data_as(f32p), r.ctypes.data_as(f32p), nf)
+                            out[k][bus, 0, b * nf:(b + 1) * nf] = l
+                            out[k][bus, 1, b * nf:(b + 1) * nf] = r
+                st = (C.c_ulonglong * 4)()
+                d.zlref_sched_state(st)
+                out["state"] = tuple(int(x) for x in st)
+                out["positions"] = []
+                results.append(out)
             elif op[0] == "process":
                 _, nb, nf, ck = op
                 n = nb * nf
@@ -177,7 +225,7 @@ def available():
 
 
 # ---------------------------------------------------------------------------------------------------------------
-def run_engine(lib, ops, sample_rate=48000.0, max_frames=1024, max_blocks=64):
+def run_engine(lib, ops, sample_rate=48000.0, max_frames=1024, max_blocks=64, sched_batch=1):
     """The same operation list through include/zl_b200.h (oracle or product): one session of 12 buses x 8 voices,
     Z-mode, every quirk faithful."""
     from libzl_b200 import _capi as K
@@ -185,9 +233,78 @@ def run_engine(lib, ops, sample_rate=48000.0, max_frames=1024, max_blocks=64):
     e = Engine(lib=lib, n_sessions=1, buses_per_session=BUSES, voices_per_bus=VOICES, mode=K.ZL_MODE_Z, quirks=K.ZL_QUIRKS_FAITHFUL,
                outputs=K.ZL_OUT_ALL, sample_rate=float(sample_rate), max_frames=max_frames, max_blocks=max_blocks)
     results, nclips, meters = [], 0, []
+    sched, sched_period = None, 0
+    if any(op[0].startswith("sched_") for op in ops):
+        sched = C.c_void_p()
+        assert lib.sched_create(float(sample_rate), int(max_frames), C.byref(sched)) == K.ZL_OK
     for op in ops:
         if op[0] == "meters":
             meters = list(op[1])
+        elif op[0] == "sched_start":
+            assert lib.sched_start(sched, int(op[1])) == K.ZL_OK
+        elif op[0] == "sched_stop":
+            assert lib.sched_stop(sched) == K.ZL_OK
+        elif op[0] == "sched_bpm":
+            assert lib.sched_set_bpm(sched, int(op[1])) == K.ZL_OK
+        elif op[0] == "sched_cmd":
+            c = K.zl_clip_command()
+            lib.clip_command_default(C.byref(c))
+            for k_, v_ in op[2].items():
+                setattr(c, k_, v_)
+            assert lib.sched_schedule(sched, C.byref(c), int(op[1])) == K.ZL_OK
+        elif op[0] == "sched_queue_start":
+            assert lib.sched_queue_start(sched, int(op[1]), int(op[2])) == K.ZL_OK
+        elif op[0] == "sched_queue_stop":
+            assert lib.sched_queue_stop(sched, int(op[1]), int(op[2])) == K.ZL_OK
+        elif op[0] == "sched_enable":
+            assert lib.sched_schedule_channel_enabled(sched, int(op[1]), int(op[2]), int(op[3])) == K.ZL_OK
+        elif op[0] == "sched_run":
+            _, nper, nf = op
+            period = int(round(nf * 1e6 / sample_rate))
+            out = {k_: [] for k_ in ("raw", "dry", "fx1", "fx2")}
+            out["clocks"], out["commands"] = [], []
+            done = 0
+            while done < nper:
+                nb = min(sched_batch, nper - done, max_blocks)
+                ck = (K.zl_block_clock * nb)()
+                for i in range(nb):
+                    ck[i].current_usecs = 1_000_000 + (sched_period + i) * period
+                    ck[i].next_usecs = ck[i].current_usecs + period
+                ev = (K.zl_sched_event * 4096)()
+                cnt = C.c_int32()
+                assert lib.sched_advance(sched, nb, nf, ck, ev, 4096, C.byref(cnt)) == K.ZL_OK
+                per_block = [[] for _ in range(nb)]
+                events = [ev[i] for i in range(cnt.value)]
+                # a channel switched on or off takes effect from its own period on: render the batch in segments that start there
+                cuts = sorted({0, nb} | {x.block for x in events if x.kind != K.ZL_SCHED_CLIP_COMMAND})
+                for i in range(nb):
+                    out["clocks"].append((ck[i].current_usecs, ck[i].next_usecs, ck[i].playhead, ck[i].playhead_usecs, ck[i].subbeat_usecs))
+                for lo, hi in zip(cuts[:-1], cuts[1:]):
+                    for x in events:
+                        if not (lo <= x.block < hi):
+                            continue
+                        if x.kind == K.ZL_SCHED_CLIP_COMMAND:
+                            c = x.cmd
+                            per_block[x.block].append((c.clip, c.midi_note, c.midi_channel, c.start_playback, c.stop_playback, c.change_slice, c.slice,
+                                                       c.change_looping, c.looping, c.change_volume, float(c.volume)))
+                            e._chk(lib.command(e.ctx, 0, x.block - lo, x.tick, C.byref(c)), "command")
+                        else:
+                            assert x.block == lo
+                            e.set_bus_enabled(0, x.channel + 2, bool(x.enabled))
+                    seg = (K.zl_block_clock * (hi - lo))(*[ck[i] for i in range(lo, hi)])
+                    e.render(hi - lo, nf, seg)
+                    for w, k_ in ((K.ZL_BUS_RAW, "raw"), (K.ZL_BUS_DRY, "dry"), (K.ZL_BUS_FX1, "fx1"), (K.ZL_BUS_FX2, "fx2")):
+                        out[k_].append(np.stack([np.stack(e.bus(0, b, w)) for b in range(BUSES)]))
+                out["commands"] += per_block
+                sched_period += nb
+                done += nb
+            for k_ in ("raw", "dry", "fx1", "fx2"):
+                out[k_] = np.concatenate(out[k_], axis=-1)
+            st = [C.c_uint64() for _ in range(3)] + [C.c_uint64(), C.c_int32(), C.c_uint64()]
+            lib.sched_state(sched, C.byref(st[0]), C.byref(st[1]), C.byref(st[2]), C.byref(st[3]), C.byref(st[4]), C.byref(st[5]))
+            out["state"] = (int(st[3].value), int(st[4].value), int(st[5].value))
+            out["positions"] = []
+            results.append(out)
         elif op[0] == "clip":
             _, pcm, rate, par = op
             cid = e.add_clip(pcm, rate)
@@ -226,6 +343,8 @@ def run_engine(lib, ops, sample_rate=48000.0, max_frames=1024, max_blocks=64):
                     out["meters"].append((x.peak_a, x.peak_b, x.db_a, x.db_b, x.db_sum, x.hold_a, x.hold_b))
             results.append(out)
     e.close()
+    if sched is not None:
+        lib.sched_destroy(sched)
     return results
 
 
@@ -237,8 +356,19 @@ def disabled_buses(ops):
     for op in ops:
         if op[0] == "enable":
             (off.discard if op[2] else off.add)(op[1] + 2)
-        elif op[0] == "process":
+        elif op[0] == "sched_enable":                 # takes effect some steps into the next run: that run is skipped for the bus
+            off.add(op[2] + 2)
+            if op[3]:
+                pending_on = op[2] + 2
+                out_mark = ("on", pending_on)
+                off.add(pending_on)
+        elif op[0] in ("process", "sched_run"):
             out.append(sorted(off))
+            for b in [x for x in off if any(o[0] == "sched_enable" and o[2] + 2 == x and o[3] for o in ops[:ops.index(op)])]:
+                # re-enabled by a timer command during this run: comparable again from the next run on
+                last = [o for o in ops[:ops.index(op)] if o[0] == "sched_enable" and o[2] + 2 == b][-1]
+                if last[3]:
+                    off.discard(b)
     return out
 
 
@@ -256,6 +386,15 @@ def compare(a, b, check_positions=True, skip_buses=None):
                 bad.append(f"op {i} {k}: shape")
             elif not np.array_equal(x[k][keep], y[k][keep]):
                 bad.append(f"op {i} {k}: not bit-exact, max abs {np.abs(x[k] - y[k]).max():.3g}, first at {np.argwhere(x[k] != y[k])[0].tolist()}")
+        if "clocks" in x or "clocks" in y:
+            if x["clocks"] != y["clocks"]:
+                k_ = next(j for j, (a_, b_) in enumerate(zip(x["clocks"], y["clocks"])) if a_ != b_)
+                bad.append(f"op {i}: block clocks differ first at period {k_}: {x['clocks'][k_]} vs {y['clocks'][k_]}")
+            if x["commands"] != y["commands"]:
+                k_ = next(j for j, (a_, b_) in enumerate(zip(x["commands"], y["commands"])) if a_ != b_)
+                bad.append(f"op {i}: command stream differs first at period {k_}: {x['commands'][k_]} vs {y['commands'][k_]}")
+            if tuple(x["state"][:3]) != tuple(y["state"][:3]):
+                bad.append(f"op {i}: timer state (cumulativeBeat, beat, scheduleAhead) {x['state']} vs {y['state']}")
         if "meters" in x or "meters" in y:
             for c, (ma, mb) in enumerate(zip(x.get("meters", []), y.get("meters", []))):
                 if ma[:2] != mb[:2]:
@@ -357,6 +496,62 @@ def scenario_sketch(beat_aligned=True, nblocks=40, nframes=256):
     return ops
 
 
+def scenario_scheduler(nframes=256):
+    """Row n2: a sketch driven by the command scheduler instead of a hand-written command stream.  Commands scheduled some
+    steps ahead while the timer is paused and while it runs, two equivalent commands landing on one step (merged), clips queued
+    to start on the next bar, a queued stop that removes what is still waiting, a tempo change, a channel switched off by a
+    timer command, stop() with commands still in the ring; beat-aligned loops, so a wrong tick is audible."""
+    ops = []
+    for k in range(4):
+        pcm = np.random.default_rng(1400 + k).uniform(-1, 1, (2, 30000)).astype(np.float32)
+        ops.append(("clip", pcm, 48000.0, dict(length_s=0.5, length_beats=1.0 if k % 2 == 0 else 0.75, pan=0.2 * k - 0.3, volume_abs=0.8,
+                                                attack=0.001, decay=0.05, sustain=0.8, release=0.02)))
+    play = lambda clip, ch, note=60, vol=0.7, loop=1: dict(clip=clip, midi_channel=ch, midi_note=note, change_volume=1, volume=vol, looping=loop,
+                                                           stop_playback=loop, start_playback=1)
+    # paused: delays count from the ring's read head
+    ops += [("sched_cmd", 0, play(0, -2)), ("sched_cmd", 3, play(1, 0, 62, 0.5, 0)), ("sched_cmd", 3, dict(clip=1, midi_channel=0, midi_note=62, change_volume=1, volume=0.9)),
+            ("sched_queue_start", 2, 1), ("sched_run", 12, nframes)]
+    ops += [("sched_start", 120), ("sched_cmd", 10, play(3, 2, 64, 0.6, 0)), ("sched_queue_start", 0, 3), ("sched_run", 40, nframes)]
+    ops += [("sched_queue_start", 2, 4), ("sched_cmd", 96, play(1, 5, 67, 0.4, 0)), ("sched_cmd", 96, dict(clip=1, midi_channel=5, midi_note=67, change_looping=1, looping=1)),
+            ("sched_run", 90, nframes)]
+    ops += [("sched_queue_stop", 2, 1), ("sched_bpm", 90), ("sched_enable", 4, 3, 0), ("sched_run", 30, nframes)]
+    ops += [("sched_enable", 2, 3, 1), ("sched_queue_start", 3, 6), ("sched_cmd", 400, play(0, 7, 55, 0.9, 0)), ("sched_run", 60, nframes)]
+    ops += [("sched_stop",), ("sched_run", 10, nframes)]
+    return ops
+
+
+def random_scheduler_ops(seed, nframes):
+    """Forty random scheduler calls (commands at assorted delays, queued starts/stops, start/stop/tempo changes in any order - so
+    stop() while paused, stop() with a full ring, start() twice - channel switches), each followed by a run of periods."""
+    rng = np.random.default_rng(seed)
+    ops = []
+    for _ in range(40):
+        k = rng.integers(0, 8)
+        cmd = dict(clip=int(rng.integers(0, 4)), midi_channel=int(rng.integers(-2, 10)), midi_note=int(rng.choice([60, 62, 64])),
+                   change_volume=int(rng.integers(0, 2)), volume=float(np.float32(rng.uniform(0, 1))), looping=int(rng.integers(0, 2)),
+                   change_looping=int(rng.integers(0, 2)), start_playback=int(rng.integers(0, 2)), stop_playback=int(rng.integers(0, 2)))
+        if rng.random() < 0.3:
+            cmd.update(change_slice=1, slice=int(rng.integers(0, 4)))
+        if k <= 2:
+            ops.append(("sched_cmd", int(rng.choice([0, 1, 2, 7, 96, 383, 384, 1000])), cmd))
+        elif k == 3:
+            ops.append(("sched_queue_start", int(rng.integers(0, 4)), int(rng.integers(-1, 10))))
+        elif k == 4:
+            ops.append(("sched_queue_stop", int(rng.integers(0, 4)), int(rng.integers(-1, 10))))
+        elif k == 5:
+            ops.append((("sched_start", int(rng.choice([60, 120, 137, 200]))) if rng.random() < 0.7 else ("sched_stop",)))
+        elif k == 6:
+            ops.append(("sched_bpm", int(rng.choice([50, 90, 120, 174]))))
+        else:
+            ops.append(("sched_enable", int(rng.integers(0, 20)), int(rng.integers(-2, 10)), int(rng.integers(0, 2))))
+        ops.append(("sched_run", int(rng.integers(1, 40)), nframes))
+    return ops
+
+
+def scenario_scheduler_random(seed, nframes=256):
+    return [op for op in scenario_scheduler(nframes) if op[0] == "clip"] + random_scheduler_ops(seed, nframes)
+
+
 # ---------------------------------------------------------------------------------------------------------------
 SCENARIOS = {
     "single_one_shot": lambda: scenario_single_voice(),
@@ -365,6 +560,10 @@ SCENARIOS = {
     "polyphonic_seed7_ragged": lambda: scenario_polyphonic(seed=7, nframes=300, nblocks=9),
     "sketch_beat_aligned": lambda: scenario_sketch(True),
     "sketch_position_loops": lambda: scenario_sketch(False, nblocks=60),
+    "scheduler_sketch": lambda: scenario_scheduler(),
+    "scheduler_random_seed3": lambda: scenario_scheduler_random(3),
+    "scheduler_random_seed4_1024": lambda: scenario_scheduler_random(4, 1024),
+    "scheduler_random_seed8_64": lambda: scenario_scheduler_random(8, 64),
 }
 
 
@@ -385,4 +584,11 @@ def digest(results, skip_buses=None):
             h.update(np.asarray(live, np.float32).tobytes())
         for m in r.get("meters", []):
             h.update(np.asarray(m[:2], np.int64).tobytes())
+        if "clocks" in r:
+            h.update(np.asarray(r["clocks"], np.uint64).tobytes())
+            for per in r["commands"]:
+                h.update(np.asarray([len(per)], np.int64).tobytes())
+                for c in per:
+                    h.update(np.asarray(c[:10], np.int64).tobytes() + np.asarray(c[10:], np.float32).tobytes())
+            h.update(np.asarray(r["state"][:3], np.int64).tobytes())
     return h.hexdigest()

@@ -206,17 +206,26 @@ def test_destroying_a_clip_in_use_stops_its_voices(product, oracle):
         assert np.all(run(product)[1]["v_clip"] != 0) and np.any(run(product)[1]["v_clip"] == 1)
 
 
-@pytest.mark.parametrize("name", ["single_one_shot", "single_position_loop", "polyphonic_seed2", "polyphonic_seed7_ragged",
-                                  "sketch_beat_aligned", "sketch_position_loops"])
-def test_device_matches_the_reference_compiled_hot_path(product, name):
+def _reference_scenarios():
+    import libref as R
+    return sorted(R.SCENARIOS)
+
+
+@pytest.mark.parametrize("sched_batch", [1, 8])
+@pytest.mark.parametrize("name", _reference_scenarios())
+def test_device_matches_the_reference_compiled_hot_path(product, name, sched_batch):
     """The product against the reference's OWN compiled SamplerSynthVoice / SamplerChannel / JackPassthrough / positions model
-    / AudioLevels (oracle/ref/libzl_ref.cpp): through the committed digests of the reference's outputs and, where oracle/_ref
-    travelled to this box, against the reference run live - bit for bit (audio planes, integer meter peaks, positions)."""
+    / AudioLevels / SyncTimer (oracle/ref/libzl_ref.cpp, synctimer_ref.cpp): through the committed digests of the reference's
+    outputs and, where oracle/_ref travelled to this box, against the reference run live - bit for bit (audio planes, integer
+    meter peaks, positions; for the scheduler scenarios also every period's clock and emitted command).  sched_batch 8: the
+    scheduler advances eight periods per call and the device renders them as one batch (row n2's point)."""
     import json, os
     import libref as R
     golden = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "libzl_digests.json")))
     ops = R.SCENARIOS[name]()
-    got = R.run_engine(product, ops)
+    if sched_batch != 1 and not name.startswith("scheduler"):
+        pytest.skip("only the scheduler scenarios batch periods")
+    got = R.run_engine(product, ops, sched_batch=sched_batch)
     if R.available():
         assert not R.compare(R.run_reference(ops), got, skip_buses=R.disabled_buses(ops))
     assert R.digest(got, R.disabled_buses(ops)) == golden[name]
