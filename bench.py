@@ -216,7 +216,7 @@ def run_cuda(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=dev)
     S, NB = args.sessions, args.blocks
     total_steps = args.warmup + args.steps
-    wl = Workload(S, NB, total_steps * 2 + 2, args.seed, rank)
+    wl = Workload(S, NB, total_steps * 2 + 2 + args.steps, args.seed, rank)
     outputs = K.ZL_OUT_RAW | K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS | (K.ZL_OUT_RMS if args.rms else 0)
     e = Engine(lib=libzl_b200.load(), n_sessions=S, buses_per_session=BUSES, voices_per_bus=VOICES,
                max_clips=S * CLIPS_PER_SESSION, max_frames=FRAMES, max_blocks=NB, outputs=outputs, device=local_rank,
@@ -374,7 +374,35 @@ def run_cuda(args, rank, world, local_rank):
             parity = {"error": repr(ex)}
     for hp in hostp:
         e.lib.host_free(hp)
-    return dict(e=e, parity=parity, host_loop_ms=host_loop_ms, host_submit_ms=host_submit_ms, kernel_ms=kernel_ms, gather_ms_per_step=gather_ms_per_step, gather_alone_ms=gather_alone_ms, elapsed_ms=elapsed_ms, step_ms=step_ms, timed_vf=timed_vf, timed_src=timed_src, launches=kernel_launches,
+    # ---- e2e with the masters read back as 16-bit PCM (the reference recorder's file format, encoded on the device by the
+    # same conversion zl_bounce_wav uses: half the D2H bytes).  Same loop, same rules; the f32 loop above stays the parity path.
+    pcm_bytes = S * n_per_step * 2 * 2
+    pcmp = [C.c_void_p(), C.c_void_p()]
+    for hp in pcmp:
+        e._chk(e.lib.host_alloc(C.byref(hp), pcm_bytes), "host_alloc")
+    vf2 = e.total_counters()[0]
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        i = 2 * total_steps + 2 + k
+        e.command_batch(*wl.steps[i])
+        e.render(NB, FRAMES, clocks_for(e, i, NB))
+        if span:
+            e._chk(e.lib.mix_reduce(e.ctx, 0), "mix_reduce")
+        if mix_root:
+            e._chk(e.lib.read_master_all_pcm_async(e.ctx, pcmp[k & 1], n_per_step, 16), "read_master_all_pcm_async")
+    e._chk(e.lib.read_wait(e.ctx), "read_wait")
+    barrier()
+    e2e_pcm_s = time.perf_counter() - t0
+    e2e_pcm_vf = e.total_counters()[0] - vf2
+    if mix_root:                                               # the bytes on the host are the data chunk of zl_bounce_wav's file, session by session
+        got = np.ctypeslib.as_array(C.cast(pcmp[(args.steps - 1) & 1], C.POINTER(C.c_uint8)), shape=(S, n_per_step * 4))
+        for sidx in sorted({0, S // 2, S - 1}):
+            wav = e.bounce_wav(sidx, -1, 0, 16)
+            assert np.array_equal(got[sidx], np.frombuffer(wav, np.uint8)[104:104 + n_per_step * 4]), "PCM read-back differs from zl_bounce_wav"
+    for hp in pcmp:
+        e.lib.host_free(hp)
+    return dict(e=e, parity=parity, e2e_pcm_s=e2e_pcm_s, e2e_pcm_vf=e2e_pcm_vf, d2h_pcm=pcm_bytes if mix_root else 0, host_loop_ms=host_loop_ms, host_submit_ms=host_submit_ms, kernel_ms=kernel_ms, gather_ms_per_step=gather_ms_per_step, gather_alone_ms=gather_alone_ms, elapsed_ms=elapsed_ms, step_ms=step_ms, timed_vf=timed_vf, timed_src=timed_src, launches=kernel_launches,
                 clocks=clocks, e2e_s=e2e_s, e2e_vf=e2e_vf, h2d=h2d, d2h=d2h, out_bytes=out_bytes, state_bytes=state_bytes,
                 dist=dist, dev=dev, wl=wl, keep=pcm)
 
@@ -657,13 +685,13 @@ def main():
 
     import torch
     r = run_cuda(args, rank, world, local_rank)
-    elapsed = torch.tensor([r["elapsed_ms"], r["e2e_s"] * 1e3], dtype=torch.float64, device=r["dev"])
-    counts = torch.tensor([r["timed_vf"], r["e2e_vf"], r["timed_src"]], dtype=torch.float64, device=r["dev"])
+    elapsed = torch.tensor([r["elapsed_ms"], r["e2e_s"] * 1e3, r["e2e_pcm_s"] * 1e3], dtype=torch.float64, device=r["dev"])
+    counts = torch.tensor([r["timed_vf"], r["e2e_vf"], r["timed_src"], r["e2e_pcm_vf"]], dtype=torch.float64, device=r["dev"])
     if r["dist"] is not None:
         r["dist"].all_reduce(elapsed, op=r["dist"].ReduceOp.MAX)
         r["dist"].all_reduce(counts, op=r["dist"].ReduceOp.SUM)
-    el_ms, e2e_ms = elapsed.tolist()
-    vf, e2e_vf, src = counts.tolist()
+    el_ms, e2e_ms, e2e_pcm_ms = elapsed.tolist()
+    vf, e2e_vf, src, e2e_pcm_vf = counts.tolist()
     if rank == 0:
         peak, peak_src = peaks()
         # roofline of the dominant kernel (gather_kernel, one launch = one 512-frame period of every session on this GPU):
@@ -680,6 +708,8 @@ def main():
                 "clocks": r["clocks"], "gpu_launches": r["launches"],
                 "e2e": {"value": e2e_vf / (e2e_ms * 1e-3), "unit": "voice-frames/s", "h2d_bytes_per_step": r["h2d"],
                         "d2h_bytes_per_step": r["d2h"], "what": "per step: zl_command_batch (H2D) + zl_render + zl_read_master_all_async (master of every session D2H to pinned host, overlapping the next step's render); zl_read_wait before the clock stops"},
+                "e2e_pcm16": {"value": e2e_pcm_vf / (e2e_pcm_ms * 1e-3), "unit": "voice-frames/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h_pcm"],
+                              "what": "the same loop with zl_read_master_all_pcm_async(bits=16): every session's master leaves the device as the 16-bit data chunk of the reference recorder's WAV file (lib/AudioLevels.cpp:35-119), encoded on the device - half the D2H bytes; checked against zl_bounce_wav after the clock stops"},
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                              "traffic": (ncu_traffic() if (args.sessions, args.blocks, args.quirks) == (4096, 16, 7) else None),
                              "traffic_source": f"{TRAFFIC_FILE} (ncu --set full, builder-run capture of this command; NOT measured by this run)",
@@ -718,6 +748,7 @@ def main():
             line["cpu_baseline"] = {"value": cvf / cdt, "unit": "voice-frames/s", "cores": th, "kind": "port",
                                     "sample": f"{sessions} sessions x {args.blocks} periods x {FRAMES} frames, 2 steps (oracle port, -O3 -mfma contraction on)"}
         print(json.dumps(line), flush=True)
+    r["e"].close()
     if r["dist"] is not None:
         r["dist"].barrier()
         r["dist"].destroy_process_group()

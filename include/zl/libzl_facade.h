@@ -1,7 +1,7 @@
 /*
  * include/zl/libzl_facade.h — the reference's C++ classes for the sampler render path, kept by name and method so that
  * host code written against libzl compiles against this library: SamplerSynth, SamplerSynthVoice, ClipAudioSource,
- * ClipCommand, JackPassthrough, AudioLevels, WaveFormItem, ClipAudioSourcePositionsModel.
+ * ClipCommand, JackPassthrough, AudioLevels, WaveFormItem, ClipAudioSourcePositionsModel, SyncTimer.
  *
  * They are thin host objects over the C ABI of include/zl_b200.h (the CUDA library); no Qt, no JACK, no tracktion:
  *   QObject -> plain class, QString -> std::string, QVariantList -> std::vector<double>, jack_default_audio_sample_t -> float,
@@ -216,6 +216,62 @@ private:
     class Private;
     Private* d{nullptr};
     friend class SamplerSynthVoice;
+};
+
+/* lib/SyncTimer.h:19-223 - the clip-command half of the timer (row n2): the 96-ppqn step ring, scheduleClipCommand with its
+ * same-step merge, clips queued to the next bar, start/stop/bpm, the playhead getters the voices read, and the
+ * SamplerChannelEnabledStateOperation timer command.  The MIDI-note half (scheduleNote, scheduleMidiBuffer, send*Immediately),
+ * the JACK transport and the hardware-device signals are outside SURVEY.md section 8; stopClip is declared by the
+ * reference but never defined (lib/SyncTimer.cpp has no body for it) and is left out.
+ * Where the reference is driven by JACK (SyncTimerPrivate::process, lib/SyncTimer.cpp:452-702) and by its timer thread,
+ * the host calls process()/render(): the steps that fall due are walked, their commands go to
+ * SamplerSynth::instance() with their period and tick, channel switches are applied, and the periods are rendered. */
+class ZL_FACADE_API SyncTimer {
+public:
+    static SyncTimer* instance();
+    explicit SyncTimer(double sampleRate = 48000.0, int bufferSize = 1024);
+    ~SyncTimer();
+    void queueClipToStart(ClipAudioSource* clip);
+    void queueClipToStop(ClipAudioSource* clip);
+    void queueClipToStartOnChannel(ClipAudioSource* clip, int midiChannel);
+    void queueClipToStopOnChannel(ClipAudioSource* clip, int midiChannel);
+    void start(int bpm);
+    void stop();
+    int getInterval(int bpm);
+    float subbeatCountToSeconds(uint64_t bpm, uint64_t beats) const;
+    uint64_t secondsToSubbeatCount(uint64_t bpm, float seconds) const;
+    int getMultiplier();
+    uint64_t getBpm() const;
+    void setBpm(uint64_t bpm);
+    uint64_t scheduleAheadAmount() const;
+    int beat() const;
+    uint64_t cumulativeBeat() const;
+    const uint64_t& jackPlayhead() const;
+    const uint64_t& jackPlayheadUsecs() const;
+    const uint64_t& jackSubbeatLengthInMicroseconds() const;
+    /* takes ownership of the command (merged into an equivalent one waiting on the same step, or queued) */
+    void scheduleClipCommand(ClipCommand* command, uint64_t delay);
+    /* operation: TimerCommand::SamplerChannelEnabledStateOperation (8) - parameter1 the channel (-2..9), parameter2 0 = off.
+     * Other operations are not part of the path and are ignored. */
+    void scheduleTimerCommand(uint64_t delay, int operation, int parameter1 = 0, int parameter2 = 0, int parameter3 = 0);
+    bool timerRunning();
+    ClipCommand* getClipCommand();
+    void deleteClipCommand(ClipCommand* command);
+    /* Q_SIGNAL clipCommandSent(ClipCommand*): called for every command handed to the sampler (the pointer is valid for the call) */
+    std::function<void(ClipCommand*)> clipCommandSent;
+
+    /* one JACK cycle (current_usecs / next_usecs as jack_get_cycle_times gives them), or `nblocks` cycles back to back
+     * starting at firstUsecs with periods of nframes * 1e6 / sampleRate microseconds - the offline form: the scheduler runs
+     * ahead over all of them and the device renders them as one batch (split where a channel is switched). */
+    bool process(uint32_t nframes, uint64_t currentUsecs, uint64_t nextUsecs);
+    bool render(int nblocks, uint32_t nframes, uint64_t firstUsecs);
+    /* commands handed over / periods walked so far */
+    uint64_t commandsSent() const;
+    uint64_t periodsProcessed() const;
+    zl_sched* scheduler() const;
+private:
+    class Private;
+    Private* d{nullptr};
 };
 
 /* lib/JackPassthrough.h:26-58: the passthrough of one SamplerSynth channel (-2, -1 global; 0..9 tracks) */

@@ -265,6 +265,12 @@ ZL_EXPORT int ZL_FN(read_master_all)(zl_ctx* ctx, float* out, int64_t n);
  * zl_render computes into the other of two master buffers meanwhile.  out must be pinned (zl_host_alloc) and is
  * valid after zl_read_wait.  (The reference has no equivalent: JACK hands the period over synchronously.) */
 ZL_EXPORT int ZL_FN(read_master_all_async)(zl_ctx* ctx, float* out, int64_t n);
+/* The batched bounce (row n3 at scale): the same pipelined read-back, but every session's master arrives as 16- or 24-bit
+ * PCM - the data chunk zl_bounce_wav(session, -1, ...) would write after its 104-byte header, i.e. the format of the
+ * reference's recorder files (lib/AudioLevels.cpp:35-119 -> juce::WavAudioFormat, juce_AudioFormatWriter.cpp:64-79) -
+ * encoded on the device: out is [n_sessions][n][L,R] little-endian samples, half (16) or three quarters (24) of the
+ * bytes of the f32 planes.  out must be pinned; valid after zl_read_wait. */
+ZL_EXPORT int ZL_FN(read_master_all_pcm_async)(zl_ctx* ctx, void* out, int64_t n, int32_t bits);
 ZL_EXPORT int ZL_FN(read_wait)(zl_ctx* ctx);
 /* Device pointers of the output planes, for zero-copy consumers (torch / NCCL):
  * bus planes are [n_buses_total][2][stride], master [n_sessions][2][stride]. */
@@ -384,7 +390,7 @@ typedef struct {
 ZL_EXPORT int ZL_FN(sched_create)(double sample_rate, int32_t buffer_size, zl_sched** out);
 ZL_EXPORT int ZL_FN(sched_destroy)(zl_sched* s);
 ZL_EXPORT int ZL_FN(sched_start)(zl_sched* s, int32_t bpm);                       /* SyncTimer::start  :870-879 */
-ZL_EXPORT int ZL_FN(sched_stop)(zl_sched* s);                                     /* SyncTimer::stop   :881-924: what still waits in the ring is dropped */
+ZL_EXPORT int ZL_FN(sched_stop)(zl_sched* s);                                     /* SyncTimer::stop   :881-924: what still waits is muted and re-queued one step behind the read head */
 ZL_EXPORT int ZL_FN(sched_set_bpm)(zl_sched* s, int32_t bpm);                     /* SyncTimer::setBpm :955-975 */
 ZL_EXPORT int ZL_FN(sched_schedule)(zl_sched* s, const zl_clip_command* cmd, uint64_t delay);
 ZL_EXPORT int ZL_FN(sched_schedule_channel_enabled)(zl_sched* s, uint64_t delay, int32_t channel, int32_t enabled);

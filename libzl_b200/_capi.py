@@ -112,6 +112,7 @@ SIGNATURES = {
     "read_master": (C.c_int, [_ctx, C.c_int32, _f32p, _f32p, C.c_int64]),
     "read_master_all": (C.c_int, [_ctx, _f32p, C.c_int64]),
     "read_master_all_async": (C.c_int, [_ctx, _f32p, C.c_int64]),
+    "read_master_all_pcm_async": (C.c_int, [_ctx, C.c_void_p, C.c_int64, C.c_int32]),
     "read_wait": (C.c_int, [_ctx]),
     "device_bus_ptr": (C.c_int, [_ctx, C.c_int32, _P(C.c_void_p), _P(C.c_int64)]),
     "device_master_ptr": (C.c_int, [_ctx, _P(C.c_void_p), _P(C.c_int64)]),

@@ -45,6 +45,7 @@ cudaError_t launch_deinterleave(const float*, int, long long, float*, cudaStream
 int wav_parse(const void* bytes, uint64_t n, zl_wav_format* f);
 cudaError_t launch_wav_decode(const unsigned char* raw, const zl_wav_format& f, int nchOut, long long padded, float* out, cudaStream_t st);
 cudaError_t launch_wav_encode(const float* l, const float* r, long long n, int bits, unsigned char* out, cudaStream_t st);
+cudaError_t launch_master_pcm(const float* master, long long stride, int nSessions, long long n, int bits, unsigned char* out, cudaStream_t st);
 int wav_header(unsigned char* h, int nch, double rate, int bits, uint64_t dataBytes);
 cudaError_t launch_jatm_transpose(const void* in, int nch, int n, int toJatm, void* out, cudaStream_t st);
 }  // namespace zl
@@ -129,6 +130,9 @@ struct zl_ctx {
     int8_t* d_px = nullptr; size_t pxCap = 0;
     uint8_t* d_mask = nullptr; size_t maskCap = 0;
     float* d_tmp = nullptr; size_t tmpCap = 0;  // standalone stages scratch
+    unsigned char* d_io = nullptr; size_t ioCap = 0;   // grow-only scratch of the data-format calls (WAV encode, PCM read, jatm): no cudaMalloc per call
+    cudaEvent_t stageEv[2] = {nullptr, nullptr};       // h_stage: two pinned chunks, pageable caller memory <-> device at DMA rate
+    unsigned char* d_pcmBuf[2] = {nullptr, nullptr}; size_t pcmCap[2] = {0, 0};   // zl_read_master_all_pcm_async: the encoded masters, one per master buffer
     // host mirrors
     std::vector<ClipDev> h_clips;
     std::vector<int32_t> h_slice;
@@ -208,6 +212,68 @@ int ensure_dev(zl_ctx* ctx, T** p, size_t* cap, size_t count) {
     *p = nullptr; *cap = 0;
     CK(cudaMalloc((void**) p, count * sizeof(T)));
     *cap = count;
+    return ZL_OK;
+}
+
+// ---- pageable caller memory <-> device, through two pinned chunks ------------------------------------------------------
+// A cudaMemcpyAsync on pageable memory is staged by the driver a few MB at a time and serialised with the CPU copy; here the
+// DMA of chunk k + 1 runs while the CPU moves chunk k, and nothing is allocated per call.
+constexpr size_t kStageChunk = (size_t) 8 << 20;
+static int ensure_stage(zl_ctx* ctx) {
+    if (ctx->h_stage) return ZL_OK;
+    CK(cudaMallocHost(&ctx->h_stage, 2 * kStageChunk));
+    ctx->stageCap = 2 * kStageChunk;
+    for (int k = 0; k < 2; ++k) CK(cudaEventCreateWithFlags(&ctx->stageEv[k], cudaEventDisableTiming));
+    return ZL_OK;
+}
+static int d2h_staged(zl_ctx* ctx, void* dst, const void* d_src, size_t bytes) {          // returns with the bytes in dst
+    if (bytes == 0) return ZL_OK;
+    if (bytes <= (size_t) 256 << 10) {
+        CK(cudaMemcpyAsync(dst, d_src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        return ZL_OK;
+    }
+    int rc = ensure_stage(ctx);
+    if (rc != ZL_OK) return rc;
+    unsigned char* st = static_cast<unsigned char*>(ctx->h_stage);
+    const unsigned char* src = static_cast<const unsigned char*>(d_src);
+    unsigned char* out = static_cast<unsigned char*>(dst);
+    const size_t n = (bytes + kStageChunk - 1) / kStageChunk;
+    auto issue = [&](size_t k) -> cudaError_t {
+        const size_t len = std::min(kStageChunk, bytes - k * kStageChunk);
+        cudaError_t e = cudaMemcpyAsync(st + (k & 1) * kStageChunk, src + k * kStageChunk, len, cudaMemcpyDeviceToHost, ctx->stream);
+        return e == cudaSuccess ? cudaEventRecord(ctx->stageEv[k & 1], ctx->stream) : e;
+    };
+    CK(issue(0));
+    for (size_t k = 0; k < n; ++k) {
+        if (k + 1 < n) CK(issue(k + 1));
+        CK(cudaEventSynchronize(ctx->stageEv[k & 1]));
+        memcpy(out + k * kStageChunk, st + (k & 1) * kStageChunk, std::min(kStageChunk, bytes - k * kStageChunk));
+    }
+    return ZL_OK;
+}
+static int h2d_staged(zl_ctx* ctx, void* d_dst, const void* src, size_t bytes) {          // returns with the copy queued AND the staging free again
+    if (bytes == 0) return ZL_OK;
+    if (bytes <= (size_t) 256 << 10) {
+        CK(cudaMemcpyAsync(d_dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        return ZL_OK;
+    }
+    int rc = ensure_stage(ctx);
+    if (rc != ZL_OK) return rc;
+    unsigned char* st = static_cast<unsigned char*>(ctx->h_stage);
+    const unsigned char* in = static_cast<const unsigned char*>(src);
+    unsigned char* dst = static_cast<unsigned char*>(d_dst);
+    const size_t n = (bytes + kStageChunk - 1) / kStageChunk;
+    for (size_t k = 0; k < n; ++k) {
+        const size_t len = std::min(kStageChunk, bytes - k * kStageChunk);
+        if (k >= 2) CK(cudaEventSynchronize(ctx->stageEv[k & 1]));
+        memcpy(st + (k & 1) * kStageChunk, in + k * kStageChunk, len);
+        CK(cudaMemcpyAsync(dst + k * kStageChunk, st + (k & 1) * kStageChunk, len, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaEventRecord(ctx->stageEv[k & 1], ctx->stream));
+    }
+    CK(cudaEventSynchronize(ctx->stageEv[0]));
+    if (n > 1) CK(cudaEventSynchronize(ctx->stageEv[1]));
     return ZL_OK;
 }
 
@@ -324,8 +390,8 @@ int zl_ctx_create(const zl_config* cfg, zl_ctx** out) {
     CKC(cudaMallocHost((void**) &ctx->h_clocks, sizeof(zl_block_clock) * 2 * (size_t) cfg->max_blocks));
     CKC(cudaEventCreateWithFlags(&ctx->clkEv[0], cudaEventDisableTiming));
     CKC(cudaEventCreateWithFlags(&ctx->clkEv[1], cudaEventDisableTiming));
-    CKC(cudaMalloc((void**) &ctx->d_counters, 8 * sizeof(unsigned long long)));
-    CKC(cudaMemset(ctx->d_counters, 0, 8 * sizeof(unsigned long long)));
+    CKC(cudaMalloc((void**) &ctx->d_counters, 32 * sizeof(unsigned long long)));
+    CKC(cudaMemset(ctx->d_counters, 0, 32 * sizeof(unsigned long long)));
     {
         double pow2[255];
         for (int k = -127; k <= 127; ++k) pow2[k + 127] = std::pow(2.0, k / 12.0);   // lib/SamplerSynthVoice.cpp:115
@@ -338,6 +404,16 @@ int zl_ctx_create(const zl_config* cfg, zl_ctx** out) {
 }
 
 int zl_ctx_destroy(zl_ctx* ctx) {
+    if (ctx && ctx->d_counters && getenv("ZL_B200_WALK_PROF")) {                  // profiling aid: see walk_kernel
+        unsigned long long v[32] = {0};
+        cudaSetDevice(ctx->device); cudaDeviceSynchronize();
+        cudaMemcpy(v, ctx->d_counters, sizeof v, cudaMemcpyDeviceToHost);
+        static const char* const names[5] = {"attack from 0", "release", "attack/decay", "sustain", "whole warp"};
+        for (int k = 0; k < 5; ++k)
+            fprintf(stderr, "walk prof %-14s n %llu mean %.0f max %llu cycles\n", names[k], v[8 + 3 * k], v[8 + 3 * k] ? (double) v[9 + 3 * k] / (double) v[8 + 3 * k] : 0.0, v[10 + 3 * k]);
+        fprintf(stderr, "walk prof deferred because: envelope %llu, binade %llu, beat-aligned wrap %llu, binade top (loop) %llu, one-shot stop/top %llu, release window %llu, loop end %llu\n",
+                v[24], v[25], v[26], v[27], v[28], v[29], v[30]);
+    }
     if (!ctx) return ZL_ERR_INVALID;
     cudaSetDevice(ctx->device);
     for (cudaStream_t s : {ctx->stream, ctx->own, ctx->planStream, ctx->mixStream, ctx->copyStream})   // nothing may still run on a buffer freed below
@@ -359,6 +435,8 @@ int zl_ctx_destroy(zl_ctx* ctx) {
     for (int k = 0; k < 2; ++k) if (ctx->copyDone[k]) cudaEventDestroy(ctx->copyDone[k]);
     if (ctx->d_walkCount) cudaFree(ctx->d_walkCount);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    for (int k = 0; k < 2; ++k) { if (ctx->stageEv[k]) cudaEventDestroy(ctx->stageEv[k]); if (ctx->d_pcmBuf[k]) cudaFree(ctx->d_pcmBuf[k]); }
+    if (ctx->d_io) cudaFree(ctx->d_io);
     if (ctx->h_clocks) cudaFreeHost(ctx->h_clocks);
     for (int k = 0; k < 2; ++k) { if (ctx->h_slot[k]) cudaFreeHost(ctx->h_slot[k]); if (ctx->d_slot[k]) cudaFree(ctx->d_slot[k]); }
     for (cudaEvent_t e : ctx->tev) cudaEventDestroy(e);
@@ -500,15 +578,14 @@ int zl_clip_read_pcm(zl_ctx* ctx, int32_t id, float* const* planar, int32_t nch,
     BIND();
     ClipHost* c = find_clip(ctx, id);
     if (!c || !planar || nch != c->nch || length != c->length) return invalid(ctx, "clip_read_pcm: unknown clip or shape mismatch");
-    float* d_planar = nullptr;
-    CK(cudaMalloc((void**) &d_planar, sizeof(float) * (size_t) length * nch));
+    int rc = ensure_dev(ctx, &ctx->d_io, &ctx->ioCap, sizeof(float) * (size_t) length * nch);
+    if (rc != ZL_OK) return rc;
+    float* d_planar = reinterpret_cast<float*>(ctx->d_io);
     cudaError_t e = launch_deinterleave(c->d_data, nch, length, d_planar, ctx->stream);
     ctx->launches++;
-    for (int ch = 0; ch < nch && e == cudaSuccess; ++ch)
-        e = cudaMemcpyAsync(planar[ch], d_planar + (size_t) ch * length, sizeof(float) * (size_t) length, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(d_planar);
     if (e != cudaSuccess) return fail(ctx, e, "clip_read_pcm");
+    for (int ch = 0; ch < nch; ++ch)
+        if ((rc = d2h_staged(ctx, planar[ch], d_planar + (size_t) ch * length, sizeof(float) * (size_t) length)) != ZL_OK) return rc;
     return ZL_OK;
 }
 
@@ -957,21 +1034,22 @@ int zl_read_master(zl_ctx* ctx, int32_t s, float* l, float* r, int64_t n) {
 
 // ---- n3: bounce (csrc/zl_wav.cu) ----------------------------------------------------------------------------------
 // device rows l, r (r may be null) -> the writer's file image in host memory `out`
-static int wav_encode_rows(zl_ctx* ctx, const float* d_l, const float* d_r, int64_t N, double rate, int bits, void* out, uint64_t cap, uint64_t* size) {
+static int wav_encode_rows(zl_ctx* ctx, const float* d_l, const float* d_r, int64_t N, double rate, int bits, void* out, uint64_t cap, uint64_t* size, size_t packOffset) {
     const int nch = d_r ? 2 : 1;
     const uint64_t dataBytes = (uint64_t) N * nch * (bits / 8);
     const uint64_t total = 104 + dataBytes + (dataBytes & 1);
     *size = total;
     if (!out || cap < total) { ctx->err = "wav: output buffer too small (size returned)"; return ZL_ERR_STATE; }
-    unsigned char* d_pack = nullptr;
-    CK(cudaMalloc((void**) &d_pack, (size_t) dataBytes));
+    // the packed samples go behind whatever the caller keeps at the front of the io scratch (zl_wav_encode: the uploaded rows,
+    // with the scratch already sized for both, so this never reallocates under them)
+    int rc = ensure_dev(ctx, &ctx->d_io, &ctx->ioCap, packOffset + (size_t) dataBytes);
+    if (rc != ZL_OK) return rc;
+    unsigned char* d_pack = ctx->d_io + packOffset;
     cudaError_t e = launch_wav_encode(d_l, d_r, N, bits, d_pack, ctx->stream);
     ctx->launches++;
-    unsigned char* o = static_cast<unsigned char*>(out);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(o + 104, d_pack, (size_t) dataBytes, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(d_pack);
     if (e != cudaSuccess) return fail(ctx, e, "wav encode");
+    unsigned char* o = static_cast<unsigned char*>(out);
+    if ((rc = d2h_staged(ctx, o + 104, d_pack, (size_t) dataBytes)) != ZL_OK) return rc;
     wav_header(o, nch, rate, bits, dataBytes);
     if (dataBytes & 1) o[104 + dataBytes] = 0;
     return ZL_OK;
@@ -980,14 +1058,17 @@ static int wav_encode_rows(zl_ctx* ctx, const float* d_l, const float* d_r, int6
 int zl_wav_encode(zl_ctx* ctx, const float* l, const float* r, int64_t n, double rate, int32_t bits, void* out, uint64_t cap, uint64_t* size) {
     BIND();
     if (!l || n < 1 || !(rate > 0) || (bits != 16 && bits != 24) || !size) return invalid(ctx, "wav_encode: bad argument");
-    float* d = nullptr;
-    CK(cudaMalloc((void**) &d, sizeof(float) * (size_t) n * 2));
-    cudaError_t e = cudaMemcpyAsync(d, l, sizeof(float) * (size_t) n, cudaMemcpyHostToDevice, ctx->stream);
-    if (e == cudaSuccess && r) e = cudaMemcpyAsync(d + n, r, sizeof(float) * (size_t) n, cudaMemcpyHostToDevice, ctx->stream);
-    int rc = e == cudaSuccess ? wav_encode_rows(ctx, d, r ? d + n : nullptr, n, rate, bits, out, cap, size) : fail(ctx, e, "wav_encode upload");
-    cudaStreamSynchronize(ctx->stream);
-    cudaFree(d);
-    return rc;
+    const size_t rowBytes = (sizeof(float) * (size_t) n + 15) & ~(size_t) 15, rows = r ? 2 : 1;
+    const uint64_t dataBytes = (uint64_t) n * rows * (bits / 8);
+    *size = 104 + dataBytes + (dataBytes & 1);
+    if (!out || cap < *size) { ctx->err = "wav: output buffer too small (size returned)"; return ZL_ERR_STATE; }   // a size query uploads nothing
+    int rc = ensure_dev(ctx, &ctx->d_io, &ctx->ioCap, rows * rowBytes + (size_t) n * rows * (bits / 8) + 16);
+    if (rc != ZL_OK) return rc;
+    float* dl = reinterpret_cast<float*>(ctx->d_io);
+    float* dr = r ? reinterpret_cast<float*>(ctx->d_io + rowBytes) : nullptr;
+    if ((rc = h2d_staged(ctx, dl, l, sizeof(float) * (size_t) n)) != ZL_OK) return rc;
+    if (r && (rc = h2d_staged(ctx, dr, r, sizeof(float) * (size_t) n)) != ZL_OK) return rc;
+    return wav_encode_rows(ctx, dl, dr, n, rate, bits, out, cap, size, rows * rowBytes);
 }
 
 int zl_bounce_wav(zl_ctx* ctx, int32_t s, int32_t b, int32_t which, int32_t bits, void* out, uint64_t cap, uint64_t* size) {
@@ -999,7 +1080,7 @@ int zl_bounce_wav(zl_ctx* ctx, int32_t s, int32_t b, int32_t which, int32_t bits
     if (b < 0) { if (ctx->d_master) l = ctx->d_master + (size_t) s * 2 * ctx->stride; }
     else if (ctx->d_out[which]) l = ctx->d_out[which] + ((size_t) s * ctx->cfg.buses_per_session + b) * 2 * ctx->stride;
     if (!l || N < 1) { ctx->err = "bounce_wav: nothing rendered yet or the plane is not enabled"; return ZL_ERR_STATE; }
-    return wav_encode_rows(ctx, l, l + ctx->stride, N, ctx->cfg.sample_rate, bits, out, cap, size);
+    return wav_encode_rows(ctx, l, l + ctx->stride, N, ctx->cfg.sample_rate, bits, out, cap, size, 0);
 }
 
 // every session's master rows [n_sessions * 2][N] to the host: one flat copy when the rows are contiguous (stride == N)
@@ -1039,6 +1120,38 @@ int zl_read_master_all_async(zl_ctx* ctx, float* out, int64_t n) {
     CK(copy_master_rows(ctx, out, N, ctx->copyStream));
     CK(cudaEventRecord(ctx->copyDone[ctx->masterCur], ctx->copyStream));
     ctx->copyPending[ctx->masterCur] = true;
+    return ZL_OK;
+}
+
+// The batched bounce: every session's master as 16- or 24-bit PCM (the reference recorder's file format,
+// lib/AudioLevels.cpp:35-119 -> juce::WavAudioFormat writer), encoded on the device by the same conversion zl_bounce_wav
+// uses, then copied to the host behind the next render like zl_read_master_all_async.  out: pinned, [n_sessions][n][L,R]
+// little-endian samples = each session's data chunk back to back; half (16) or three quarters (24) of the f32 bytes.
+int zl_read_master_all_pcm_async(zl_ctx* ctx, void* out, int64_t n, int32_t bits) {
+    BIND();
+    if (!out || (bits != 16 && bits != 24)) return invalid(ctx, "read_master_all_pcm_async: bad argument");
+    const int64_t N = (int64_t) ctx->nblocks * ctx->nframes;
+    if (n != N || !ctx->d_master) { ctx->err = "read_master_all_pcm_async: size mismatch or master not enabled"; return ZL_ERR_STATE; }
+    if (!ctx->copyStream) {
+        CK(cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->renderDone, cudaEventDisableTiming));
+        for (int k = 0; k < 2; ++k) CK(cudaEventCreateWithFlags(&ctx->copyDone[k], cudaEventDisableTiming));
+    }
+    const int cur = ctx->masterCur;
+    const size_t bytes = (size_t) ctx->cfg.n_sessions * (size_t) N * 2 * (bits / 8);
+    if (bytes > ctx->pcmCap[cur]) {
+        if (ctx->copyPending[cur]) { CK(cudaEventSynchronize(ctx->copyDone[cur])); ctx->copyPending[cur] = false; }
+        int rc = ensure_dev(ctx, &ctx->d_pcmBuf[cur], &ctx->pcmCap[cur], bytes);
+        if (rc != ZL_OK) return rc;
+    }
+    ctx->pipelined = true;
+    CK(launch_master_pcm(ctx->d_master, ctx->stride, ctx->cfg.n_sessions, N, bits, ctx->d_pcmBuf[cur], ctx->stream));
+    ctx->launches++;
+    CK(cudaEventRecord(ctx->renderDone, ctx->stream));
+    CK(cudaStreamWaitEvent(ctx->copyStream, ctx->renderDone, 0));
+    CK(cudaMemcpyAsync(out, ctx->d_pcmBuf[cur], bytes, cudaMemcpyDeviceToHost, ctx->copyStream));
+    CK(cudaEventRecord(ctx->copyDone[cur], ctx->copyStream));
+    ctx->copyPending[cur] = true;
     return ZL_OK;
 }
 
@@ -1316,15 +1429,12 @@ int zl_thumb_save_jatm(zl_ctx* ctx, int32_t id, void* out, uint64_t cap, uint64_
     put_le(o + 28, (uint32_t) c->nch, 4);
     put_le(o + 32, (uint32_t) (int) c->rate, 4);
     memset(o + 36, 0, 16);
-    void* d_t = nullptr;
-    CK(cudaMalloc(&d_t, (size_t) body));
-    cudaError_t e = launch_jatm_transpose(c->d_thumb, c->nch, c->nThumb, 1, d_t, ctx->stream);
+    int rc = ensure_dev(ctx, &ctx->d_io, &ctx->ioCap, (size_t) body);
+    if (rc != ZL_OK) return rc;
+    cudaError_t e = launch_jatm_transpose(c->d_thumb, c->nch, c->nThumb, 1, ctx->d_io, ctx->stream);
     ctx->launches++;
-    if (e == cudaSuccess) e = cudaMemcpyAsync(o + 52, d_t, (size_t) body, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(d_t);
     if (e != cudaSuccess) return fail(ctx, e, "thumb_save_jatm");
-    return ZL_OK;
+    return d2h_staged(ctx, o + 52, ctx->d_io, (size_t) body);
 }
 
 int zl_thumb_load_jatm(zl_ctx* ctx, int32_t id, const void* jatm, uint64_t nbytes) {
@@ -1337,14 +1447,13 @@ int zl_thumb_load_jatm(zl_ctx* ctx, int32_t id, const void* jatm, uint64_t nbyte
         return invalid(ctx, "thumb_load_jatm: the stream does not describe this clip");
     const size_t body = (size_t) n * nch * 2;
     if (c->d_thumb) { CK(cudaStreamSynchronize(ctx->stream)); cudaFree(c->d_thumb); c->d_thumb = nullptr; c->nThumb = 0; }
-    void* d_t = nullptr;
-    CK(cudaMalloc(&d_t, body));
+    int rc = ensure_dev(ctx, &ctx->d_io, &ctx->ioCap, body);
+    if (rc != ZL_OK) return rc;
+    if ((rc = h2d_staged(ctx, ctx->d_io, p + 52, body)) != ZL_OK) return rc;
     cudaError_t e = cudaMalloc((void**) &c->d_thumb, body);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_t, p + 52, body, cudaMemcpyHostToDevice, ctx->stream);
-    if (e == cudaSuccess) e = launch_jatm_transpose(d_t, nch, n, 0, c->d_thumb, ctx->stream);
+    if (e == cudaSuccess) e = launch_jatm_transpose(ctx->d_io, nch, n, 0, c->d_thumb, ctx->stream);
     ctx->launches++;
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(d_t);
     if (e != cudaSuccess) { if (c->d_thumb) cudaFree(c->d_thumb); c->d_thumb = nullptr; return fail(ctx, e, "thumb_load_jatm"); }
     c->thumbSpt = spt; c->nThumb = n;
     return ZL_OK;

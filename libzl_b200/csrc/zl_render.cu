@@ -313,6 +313,20 @@ __device__ __forceinline__ int plan_voice_block(const RenderParams& P, int vIdx,
     // loop wraps, binade crossings, the frame-by-frame walks of an attack from 0 and of quirk Q3's release window - would
     // drag the other 31 lanes of its warp through the generic planner, so it is queued for walk_kernel, which runs the
     // same code with those voices packed 32 to a warp.  Nothing has been written yet.
+    if (DEFER && active && !fast && (P.dbgFlags & 8)) {          // ZL_B200_WALK_PROF: why the fast path was not taken
+        int why = 0;                                             // 0 envelope, 1 binade, 2 beat-aligned wrap, 3 loop end/top, 4 one-shot stop/top, 5 release window
+        if (envOk) {
+            double R, top;
+            if (!binade_step(h.p, h.ratio, R, top)) why = 1;
+            else {
+                const double q = __fma_rn((double) nframes, R, h.p);
+                if (!JMODE && h.looping) why = bc.beatAligned ? 2 : 3;
+                else why = !(q < fmin(top, bc.stopD)) ? 4 : 5;
+                if (why == 3 && !(q < bc.stopD)) why = 6;        // 6: loop end proper (3: binade top)
+            }
+        }
+        atomicAdd(P.voiceFrames + 24 + why, 1ull);
+    }
     if (DEFER && active && !fast) {
         // kind 1: will step an envelope frame by frame for (most of) the period - quirk Q3's release window of a one-shot
         // (conservative test on p reaching relStart, :253) or an attack from 0; kind 2: everything else (O(1) per tile).
@@ -465,10 +479,32 @@ __global__ void __launch_bounds__(32, ZL_WALK_MINB) walk_kernel(const RenderPara
         int vIdx = -1;
         if (w < wA) { const int i = w * 32 + tid; if (i < cA) vIdx = P.walkQueue[i]; }
         else { const int j = (w - wA) * 32 + tid; if (j < cB) vIdx = P.walkQueue[P.nVoices - 1 - j]; }
+        // ZL_B200_WALK_PROF (profiling aid): cycles per queued voice by what it was doing when the period began -
+        // [0] attack from 0, [1] release (quirk Q3's frame-by-frame window), [2] attack under way / decay, [3] sustain, and
+        // [4] the whole warp - as count | sum | max in P.voiceFrames[8 + 3 k ..]
+        const bool prof = (P.dbgFlags & 8) != 0;
+        long long tw0 = 0;
+        if (prof) tw0 = clock64();
         if (vIdx >= 0) {
+            int cat = 0;
+            long long t0 = 0;
+            if (prof) {
+                const VoiceDev& r = P.voices[vIdx];
+                cat = r.adsrState == kAttack ? (r.env == 0.0f ? 0 : 2) : (r.adsrState == kRelease ? 1 : (r.adsrState == kDecay ? 2 : 3));
+                t0 = clock64();
+            }
             unsigned long long a = 0, b = 0;
             plan_voice_block<JMODE, Q3, false>(P, vIdx, vIdx / P.V, a, b);
             nVoiceFrames += a; nSrcFloats += b;
+            if (prof) {
+                const unsigned long long dt = (unsigned long long) (clock64() - t0);
+                atomicAdd(P.voiceFrames + 8 + 3 * cat, 1ull); atomicAdd(P.voiceFrames + 9 + 3 * cat, dt); atomicMax(P.voiceFrames + 10 + 3 * cat, dt);
+            }
+        }
+        if (prof) {
+            __syncwarp();
+            const unsigned long long dt = (unsigned long long) (clock64() - tw0);
+            if (tid == 0) { atomicAdd(P.voiceFrames + 20, 1ull); atomicAdd(P.voiceFrames + 21, dt); atomicMax(P.voiceFrames + 22, dt); }
         }
     }
     for (int o = 16; o > 0; o >>= 1) {
@@ -913,7 +949,8 @@ cudaError_t launch_plan(RenderParams& P, cudaStream_t stream) {
     static const int dbgSkip = [] { const char* e = getenv("ZL_B200_DEBUG_SKIP"); return e ? atoi(e) : 0; }();
     static int dbgCalls = 0;
     const int skip = (dbgSkip && ++dbgCalls > 96) ? dbgSkip : 0;
-    P.dbgFlags = skip & 4;
+    static const int walkProf = [] { const char* e = getenv("ZL_B200_WALK_PROF"); return e && atoi(e) ? 8 : 0; }();
+    P.dbgFlags = (skip & 4) | walkProf;
     if (skip & 1) {
     } else if (planThreads <= 128) {
         if (P.mode == ZL_MODE_J) ZL_LAUNCH((plan_kernel<true, false, 128>), planGrid, planThreads, stream, P);

@@ -275,10 +275,7 @@ __global__ void __launch_bounds__(256) wav_encode_kernel(const float* __restrict
 
 // Stereo, rows 16-byte aligned: thread = 4 frames -> 16 (16-bit) or 24 (24-bit) packed bytes, vector loads and stores.
 template <int BYTES>
-__global__ void __launch_bounds__(256) wav_encode4_kernel(const float4* __restrict__ l, const float4* __restrict__ r, long long n4, unsigned char* __restrict__ out) {
-    const long long j = (long long) blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n4) return;
-    const float4 a = __ldcs(l + j), b = __ldcs(r + j);
+__device__ __forceinline__ void encode4(const float4 a, const float4 b, unsigned char* __restrict__ out, long long j) {
     const int32_t v[8] = {float_to_fixed(a.x), float_to_fixed(b.x), float_to_fixed(a.y), float_to_fixed(b.y),
                           float_to_fixed(a.z), float_to_fixed(b.z), float_to_fixed(a.w), float_to_fixed(b.w)};
     if (BYTES == 2) {
@@ -297,6 +294,43 @@ __global__ void __launch_bounds__(256) wav_encode4_kernel(const float4* __restri
         uint2* o = reinterpret_cast<uint2*>(out) + j * 3;
         __stcs(o, w0); __stcs(o + 1, w1); __stcs(o + 2, w2);
     }
+}
+template <int BYTES>
+__global__ void __launch_bounds__(256) wav_encode4_kernel(const float4* __restrict__ l, const float4* __restrict__ r, long long n4, unsigned char* __restrict__ out) {
+    const long long j = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n4) return;
+    encode4<BYTES>(__ldcs(l + j), __ldcs(r + j), out, j);
+}
+
+// Every session's master pair at once (the batched bounce): rows [session][L|R][stride] -> [session][n frames][L,R] samples of
+// BYTES bytes, i.e. the data chunk of each session's file back to back.  blockIdx.y = session.  VEC: n, stride multiples of 4.
+template <int BYTES, bool VEC>
+__global__ void __launch_bounds__(256) master_pcm_kernel(const float* __restrict__ master, long long stride, long long n, unsigned char* __restrict__ out) {
+    const long long j = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    const float* l = master + (size_t) blockIdx.y * 2 * stride;
+    unsigned char* o = out + (size_t) blockIdx.y * n * 2 * BYTES;
+    if (VEC) {
+        if (j >= n / 4) return;
+        encode4<BYTES>(__ldcs(reinterpret_cast<const float4*>(l) + j), __ldcs(reinterpret_cast<const float4*>(l + stride) + j), o, j);
+    } else {
+        if (j >= n) return;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const int32_t v = float_to_fixed(__ldcs(l + c * stride + j));
+            unsigned char* q = o + ((size_t) j * 2 + c) * BYTES;
+            if (BYTES == 2) *reinterpret_cast<uint16_t*>(q) = (uint16_t) (v >> 16);
+            else { const int32_t t = v >> 8; q[0] = (unsigned char) t; q[1] = (unsigned char) (t >> 8); q[2] = (unsigned char) (t >> 16); }
+        }
+    }
+}
+cudaError_t launch_master_pcm(const float* master, long long stride, int nSessions, long long n, int bits, unsigned char* out, cudaStream_t st) {
+    if (n <= 0 || nSessions <= 0) return cudaSuccess;
+    if (bits != 16 && bits != 24) return cudaErrorInvalidValue;
+    const bool vec = (n % 4) == 0 && (stride % 4) == 0 && (reinterpret_cast<uintptr_t>(master) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+    const dim3 grid((unsigned) (((vec ? n / 4 : n) + 255) / 256), (unsigned) nSessions);
+    if (vec) { if (bits == 16) master_pcm_kernel<2, true><<<grid, 256, 0, st>>>(master, stride, n, out); else master_pcm_kernel<3, true><<<grid, 256, 0, st>>>(master, stride, n, out); }
+    else { if (bits == 16) master_pcm_kernel<2, false><<<grid, 256, 0, st>>>(master, stride, n, out); else master_pcm_kernel<3, false><<<grid, 256, 0, st>>>(master, stride, n, out); }
+    return cudaGetLastError();
 }
 
 cudaError_t launch_wav_encode(const float* l, const float* r, long long n, int bits, unsigned char* out, cudaStream_t st) {

@@ -143,6 +143,21 @@ class Engine:
         self._chk(self.lib.bounce_wav(self.ctx, session, bus, which, bits, out.ctypes.data_as(C.c_void_p), out.size, C.byref(size)), "bounce_wav")
         return out
 
+    def masters_pcm(self, bits=16):
+        """Every session's master of the last render as PCM (zl_read_master_all_pcm_async + zl_read_wait):
+        uint8 [n_sessions][frames * 2 * bits/8], each row the data chunk of that session's bounced WAV file."""
+        n = self.nblocks * self.nframes
+        rows = self.cfg.n_sessions
+        nbytes = rows * n * 2 * (bits // 8)
+        hp = C.c_void_p()
+        self._chk(self.lib.host_alloc(C.byref(hp), max(nbytes, 16)), "host_alloc")
+        try:
+            self._chk(self.lib.read_master_all_pcm_async(self.ctx, hp, n, bits), "read_master_all_pcm_async")
+            self._chk(self.lib.read_wait(self.ctx), "read_wait")
+            return np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(rows, nbytes // rows)).copy()
+        finally:
+            self.lib.host_free(hp)
+
     def thumb_save_jatm(self, clip):
         """The clip's thumbnail as a JUCE `jatm` stream (AudioThumbnail::saveTo)."""
         size = C.c_uint64(0)

@@ -883,6 +883,22 @@ int zlo_read_master_all(zl_ctx* ctx, float* out, int64_t n) {
     memcpy(out, ctx->master.data(), ctx->master.size() * 4); return ZL_OK;
 }
 int zlo_read_master_all_async(zl_ctx* ctx, float* out, int64_t n) { return zlo_read_master_all(ctx, out, n); }   // nothing to overlap on the CPU
+int zlo_bounce_wav(zl_ctx* ctx, int32_t s, int32_t b, int32_t which, int32_t bits, void* out, uint64_t cap, uint64_t* size);
+// every session's master as the data chunk the reference's writer would produce for it: zlo_bounce_wav's bytes without the header
+int zlo_read_master_all_pcm_async(zl_ctx* ctx, void* out, int64_t n, int32_t bits) {
+    if (!ctx || !out || (bits != 16 && bits != 24)) return ZL_ERR_INVALID;
+    const size_t N = (size_t) ctx->nblocks * (size_t) ctx->nframes;
+    if ((size_t) n != N || !(ctx->cfg.outputs & ZL_OUT_MASTER)) return ZL_ERR_STATE;
+    const size_t body = N * 2 * (size_t) (bits / 8);
+    std::vector<unsigned char> file(104 + body + 1);
+    for (int s = 0; s < ctx->cfg.n_sessions; ++s) {
+        uint64_t size = 0;
+        const int rc = zlo_bounce_wav(ctx, s, -1, 0, bits, file.data(), file.size(), &size);
+        if (rc != ZL_OK) return rc;
+        memcpy(static_cast<unsigned char*>(out) + (size_t) s * body, file.data() + 104, body);
+    }
+    return ZL_OK;
+}
 int zlo_read_wait(zl_ctx* ctx) { return ctx ? ZL_OK : ZL_ERR_INVALID; }
 int zlo_device_bus_ptr(zl_ctx*, int32_t, float**, int64_t*) { return ZL_ERR_INVALID; }
 int zlo_device_master_ptr(zl_ctx*, float**, int64_t*) { return ZL_ERR_INVALID; }

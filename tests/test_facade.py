@@ -12,10 +12,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "libzl_b200")
 
 
-def _build_cxx(tmp_path):
-    exe = str(tmp_path / "facade_cfg1")
+def _build_cxx(tmp_path, name="facade_cfg1"):
+    exe = str(tmp_path / name)
     subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-I" + os.path.join(ROOT, "include"),
-                           os.path.join(ROOT, "tests", "cxx", "facade_cfg1.cpp"), "-o", exe, "-L" + PKG, "-l:libzl_b200_host.so",
+                           os.path.join(ROOT, "tests", "cxx", name + ".cpp"), "-o", exe, "-L" + PKG, "-l:libzl_b200_host.so",
                            "-l:libzl_b200.so", "-Wl,-rpath," + PKG])
     return exe
 
@@ -43,6 +43,8 @@ def test_facade_compiles_links_and_fails_loudly_without_a_device(tmp_path):
         pass
     r = subprocess.run([exe, "a.wav", "b.wav", str(tmp_path / "o.bin")], capture_output=True, text=True)
     assert r.returncode == 3 and "no CUDA device" in r.stderr          # no CPU fallback
+    r = subprocess.run([_build_cxx(tmp_path, "facade_sched"), "a.wav", "b.wav", str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert r.returncode == 3 and "no CUDA device" in r.stderr
 
 
 def test_host_library_exports_the_reference_c_symbols():
@@ -52,7 +54,7 @@ def test_host_library_exports_the_reference_c_symbols():
                  "ClipAudioSource_getDuration", "JackPassthrough_setPanAmount", "JackPassthrough_getDryAmount", "initJuce", "stopClips",
                  "dBFromVolume"):                                     # lib/libzl.h:18-179, bound by test/playtest.py:25-47
         assert f" T {name}\n" in syms, name
-    for cls in ("SamplerSynth", "ClipAudioSource", "JackPassthrough", "AudioLevels", "WaveFormItem", "SamplerSynthVoice"):
+    for cls in ("SamplerSynth", "ClipAudioSource", "JackPassthrough", "AudioLevels", "WaveFormItem", "SamplerSynthVoice", "SyncTimer"):
         assert cls in syms
 
 
@@ -119,3 +121,104 @@ def test_facade_cfg1_and_a_sketch_track_equal_the_oracle(tmp_path, oracle, produ
         assert np.array_equal(a[n_audio + 20:], b[n_audio + 20:]), f"render {rr}: positions model differs"
     assert np.array_equal(got[3 * per:], exp[3 * per:]) and got[3 * per:].sum() > 100
     assert np.abs(got[:n_audio].view(np.float32)).max() > 0.05
+
+
+@pytest.mark.gpu
+def test_facade_synctimer_session_equals_the_oracle(tmp_path, oracle, product):
+    """tests/cxx/facade_sched.cpp (SyncTimer + SamplerSynth + ClipAudioSource, period by period and batched) against the
+    same calls on the oracle's scheduler and renderer through the C ABI, one period per call: ports, clocks, command count."""
+    import ctypes as C
+    from libzl_b200 import _capi as K
+    from libzl_b200.engine import Engine
+    import thumbref as T
+    rng = np.random.default_rng(78)
+    img_clip = T.wav_image(rng.uniform(-1, 1, (2, 9000)).astype(np.float32), 48000, 16)
+    img_loop = T.wav_image(rng.uniform(-1, 1, (2, 48000)).astype(np.float32), 48000, -32)
+    (tmp_path / "clip.wav").write_bytes(img_clip.tobytes())
+    (tmp_path / "loop.wav").write_bytes(img_loop.tobytes())
+    out = tmp_path / "sched.bin"
+    r = subprocess.run([_build_cxx(tmp_path, "facade_sched"), str(tmp_path / "clip.wav"), str(tmp_path / "loop.wav"), str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    got = np.frombuffer(out.read_bytes(), np.uint8)
+
+    NF, PERIOD = 256, 5333
+    e = Engine(lib=oracle, n_sessions=1, buses_per_session=12, voices_per_bus=8, sample_rate=48000.0, max_frames=NF, max_blocks=16)
+    clip, loop = e.add_clip_wav(img_clip), e.add_clip_wav(img_loop)
+    sl = [k / 16.0 for k in range(16)]
+    e.set_clip_params(clip, slice_pos=sl)
+    e.set_clip_params(loop, slice_pos=sl, attack=float(np.float32(0.002)), decay=float(np.float32(0.05)), sustain=float(np.float32(0.7)),
+                      release=float(np.float32(0.03)), length_s=0.75, length_beats=1.5, volume_abs=float(np.float32(0.8)))
+    s = C.c_void_p()
+    assert oracle.sched_create(48000.0, 1024, C.byref(s)) == K.ZL_OK
+    exp, state = [], {"period": 0, "sent": 0}
+
+    def cmd(**f):
+        c = K.zl_clip_command()
+        oracle.clip_command_default(C.byref(c))
+        for k, v in f.items():
+            setattr(c, k, v)
+        return c
+
+    def play(cl, ch, note, vol, lp):
+        return cmd(clip=cl, midi_channel=ch, midi_note=note, change_volume=1, volume=vol, looping=lp, stop_playback=lp, start_playback=1)
+
+    def run(periods):
+        for _ in range(periods):
+            ck = (K.zl_block_clock * 1)()
+            ck[0].current_usecs = 1_000_000 + state["period"] * PERIOD
+            ck[0].next_usecs = ck[0].current_usecs + PERIOD
+            ev = (K.zl_sched_event * 256)()
+            n = C.c_int32()
+            assert oracle.sched_advance(s, 1, NF, ck, ev, 256, C.byref(n)) == K.ZL_OK
+            for i in range(n.value):
+                if ev[i].kind == K.ZL_SCHED_CLIP_COMMAND:
+                    e._chk(oracle.command(e.ctx, 0, 0, ev[i].tick, C.byref(ev[i].cmd)), "command")
+                    state["sent"] += 1
+                else:
+                    e.set_bus_enabled(0, ev[i].channel + 2, bool(ev[i].enabled))
+            e.render(1, NF, ck)
+            state["period"] += 1
+            yield
+
+    def dump(nb, planes):
+        for ch in (-2, 0, 1, 2, 3):
+            exp.append(np.concatenate([p[ch + 2][0] for p in planes]).tobytes())
+            exp.append(np.concatenate([p[ch + 2][1] for p in planes]).tobytes())
+        st = [C.c_uint64() for _ in range(4)]
+        oracle.sched_state(s, C.byref(st[0]), C.byref(st[1]), C.byref(st[2]), C.byref(st[3]), None, None)
+        exp.append(np.array([x.value for x in st], np.uint64).tobytes())
+
+    def periods(total, batch):
+        done = 0
+        while done < total:
+            nb = min(batch, total - done)
+            planes = []
+            for _ in run(nb):
+                planes.append([e.bus(0, b, K.ZL_BUS_RAW) for b in range(12)])
+            dump(nb, planes)
+            done += nb
+
+    oracle.sched_schedule(s, C.byref(play(clip, -2, 60, 0.7, 0)), 0)
+    oracle.sched_schedule(s, C.byref(play(loop, 0, 62, 0.5, 1)), 3)
+    oracle.sched_schedule(s, C.byref(cmd(clip=loop, midi_channel=0, midi_note=62, change_volume=1, volume=0.9)), 3)
+    oracle.sched_queue_start(s, loop, 1)
+    periods(12, 1)
+    oracle.sched_start(s, 120)
+    oracle.sched_schedule(s, C.byref(play(clip, 2, 64, 0.6, 0)), 10)
+    oracle.sched_queue_start(s, clip, 3)
+    periods(40, 8)
+    oracle.sched_set_bpm(s, 90)
+    oracle.sched_schedule_channel_enabled(s, 4, 3, 0)
+    oracle.sched_queue_stop(s, loop, 1)
+    oracle.sched_schedule(s, C.byref(play(loop, 2, 67, 0.4, 0)), 96)
+    periods(30, 1)
+    oracle.sched_schedule(s, C.byref(play(clip, 0, 55, 0.9, 0)), 400)
+    oracle.sched_stop(s)
+    periods(10, 10)
+    exp.append(np.array([state["sent"], state["sent"], state["period"]], np.uint64).tobytes())
+    oracle.sched_destroy(s)
+    e.close()
+    exp = np.frombuffer(b"".join(exp), np.uint8)
+    assert got.size == exp.size
+    assert np.array_equal(got, exp), f"first difference at byte {int(np.argmax(got != exp))} of {got.size}"
+    assert state["sent"] >= 8 and np.abs(got[:12 * 10 * NF * 4].view(np.float32)).max() > 0.05

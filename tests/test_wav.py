@@ -219,3 +219,44 @@ def test_wav_file_plays_like_the_pcm_clip_and_bounces_like_the_oracle(product, o
     m = outs[0]["master"][0]
     q = np.floor(np.clip(m.astype(np.float64), -1, 1) * 2147483647.0 + 0.5)   # not the tie rule; ties are measure zero here
     assert np.abs(back - (np.floor(q / 65536.0) / 32768.0)).max() <= 1.0 / 32768.0
+
+
+def _pcm_case(lib, nframes, nblocks=3):
+    """Three sessions, two buses each carrying a clip, rendered; returns the engine."""
+    e = Engine(lib=lib, mode=K.ZL_MODE_Z, quirks=K.ZL_QUIRKS_FAITHFUL, n_sessions=3, max_frames=nframes, max_blocks=nblocks)
+    rng = np.random.default_rng(5)
+    for s_ in range(3):
+        c = e.add_clip(rng.uniform(-1.2, 1.2, (2, 6000)).astype(np.float32), rate=48000.0)   # beyond full scale: the writer's clamps
+        e.play(c, session=s_, note=60 + s_, volume=1.0)
+        e.play(c, session=s_, note=67, volume=0.8, midi_channel=1)
+    e.render(nblocks, nframes, e.make_clocks(nblocks, nframes))
+    return e
+
+
+@pytest.mark.parametrize("nframes", [256, 131])
+def test_batched_pcm_read_back_is_the_bounced_files_data_chunk_oracle(oracle, nframes):
+    """zl_read_master_all_pcm_async restated: row s = bytes 104.. of zl_bounce_wav(s, master) (CPU; the GPU twin is below)."""
+    e = _pcm_case(oracle, nframes)
+    for bits in (16, 24):
+        rows = e.masters_pcm(bits)
+        assert rows.shape == (3, 3 * nframes * 2 * bits // 8)
+        for s_ in range(3):
+            assert np.array_equal(rows[s_], e.bounce_wav(s_, -1, 0, bits)[104:104 + rows.shape[1]])
+    e.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nframes", [256, 131])
+def test_batched_pcm_read_back_on_the_device(product, oracle, nframes):
+    """Vector (frames % 4 == 0) and scalar encode paths of the batched bounce: bytes equal to the oracle's and to the
+    device's own per-session zl_bounce_wav; a second render reuses the other PCM buffer."""
+    e, o = _pcm_case(product, nframes), _pcm_case(oracle, nframes)
+    for rep in range(3):
+        for bits in (16, 24):
+            rows = e.masters_pcm(bits)
+            assert np.array_equal(rows, o.masters_pcm(bits))
+            assert np.array_equal(rows[1], e.bounce_wav(1, -1, 0, bits)[104:104 + rows.shape[1]])
+            assert len(np.unique(rows)) > 100
+        for x in (e, o):
+            x.render(3, nframes, x.make_clocks(3, nframes))
+    e.close(); o.close()
