@@ -216,7 +216,7 @@ def run_cuda(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=dev)
     S, NB = args.sessions, args.blocks
     total_steps = args.warmup + args.steps
-    wl = Workload(S, NB, total_steps * 2 + 2 + args.steps, args.seed, rank)
+    wl = Workload(S, NB, total_steps * 2 + 4 + args.steps, args.seed, rank)
     outputs = K.ZL_OUT_RAW | K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS | (K.ZL_OUT_RMS if args.rms else 0)
     e = Engine(lib=libzl_b200.load(), n_sessions=S, buses_per_session=BUSES, voices_per_bus=VOICES,
                max_clips=S * CLIPS_PER_SESSION, max_frames=FRAMES, max_blocks=NB, outputs=outputs, device=local_rank,
@@ -380,11 +380,20 @@ def run_cuda(args, rank, world, local_rank):
     pcmp = [C.c_void_p(), C.c_void_p()]
     for hp in pcmp:
         e._chk(e.lib.host_alloc(C.byref(hp), pcm_bytes), "host_alloc")
-    vf2 = e.total_counters()[0]
+    for k in range(2):                                         # untimed: both device-side PCM buffers get allocated
+        i = 2 * total_steps + 2 + k
+        e.command_batch(*wl.steps[i])
+        e.render(NB, FRAMES, clocks_for(e, i, NB))
+        if span:
+            e._chk(e.lib.mix_reduce(e.ctx, 0), "mix_reduce")
+        if mix_root:
+            e._chk(e.lib.read_master_all_pcm_async(e.ctx, pcmp[k & 1], n_per_step, 16), "read_master_all_pcm_async")
+    e._chk(e.lib.read_wait(e.ctx), "read_wait")
     barrier()
+    vf2 = e.total_counters()[0]
     t0 = time.perf_counter()
     for k in range(args.steps):
-        i = 2 * total_steps + 2 + k
+        i = 2 * total_steps + 4 + k
         e.command_batch(*wl.steps[i])
         e.render(NB, FRAMES, clocks_for(e, i, NB))
         if span:
@@ -497,7 +506,7 @@ def latency_probe(local_rank, iters=1500):
     import libzl_b200
     from libzl_b200 import _capi as K
     from libzl_b200.engine import Engine
-    wl = Workload(1, 1, iters + 20, 99, 0)
+    wl = Workload(1, 1, 2 * (iters + 20), 99, 0)
     e = Engine(lib=libzl_b200.load(), n_sessions=1, buses_per_session=BUSES, voices_per_bus=VOICES, max_clips=8,
                max_frames=FRAMES, max_blocks=1, outputs=K.ZL_OUT_MASTER | K.ZL_OUT_LEVELS, device=local_rank)
     pcm = wl.clip_pcm_numpy(0, CLIPS_PER_SESSION)
@@ -508,18 +517,25 @@ def latency_probe(local_rank, iters=1500):
     hostp = C.c_void_p()
     e._chk(e.lib.host_alloc(C.byref(hostp), 2 * FRAMES * 4), "host_alloc")
     hp = C.cast(hostp, C.POINTER(C.c_float))
-    ts = []
-    for i in range(iters + 20):
-        clk = clocks_for(e, i, 1)
-        t0 = time.perf_counter()
-        e.lib.render(e.ctx, 1, FRAMES, clk)
-        e.lib.read_master_all(e.ctx, hp, FRAMES)
-        ts.append(time.perf_counter() - t0)
+    out = {}
+    step = 0
+    for name, graph in (("graph", 1), ("plain_launches", 0)):           # SURVEY.md 8d defines the metric as graph-launched; the other for comparison
+        e._chk(e.lib.ctx_set_graph(e.ctx, graph), "ctx_set_graph")
+        ts = []
+        for i in range(iters + 20):
+            clk = clocks_for(e, step, 1)
+            step += 1
+            t0 = time.perf_counter()
+            e.lib.render(e.ctx, 1, FRAMES, clk)
+            e.lib.read_master_all(e.ctx, hp, FRAMES)
+            ts.append(time.perf_counter() - t0)
+        ts = sorted(ts[20:])
+        out[name] = {"p50_us": round(1e6 * ts[len(ts) // 2], 2), "p99_us": round(1e6 * ts[int(len(ts) * 0.99)], 2)}
     e.lib.host_free(hostp)
     e.close()
-    ts = sorted(ts[20:])
-    return {"p50_us": round(1e6 * ts[len(ts) // 2], 2), "p99_us": round(1e6 * ts[int(len(ts) * 0.99)], 2),
-            "what": "one 512-frame period of one 128-voice session: zl_render + zl_read_master_all to pinned host"}
+    return {"p50_us": out["graph"]["p50_us"], "p99_us": out["graph"]["p99_us"], "plain_launches": out["plain_launches"],
+            "what": "one 512-frame period of one 128-voice session: zl_render (one CUDA-graph launch: counter resets, plan, walk, gather, port mix) "
+                    "+ zl_read_master_all to pinned host; plain_launches = the same with the graph switched off (zl_ctx_set_graph 0)"}
 
 
 def cpu_latency_probe(iters=300):

@@ -179,6 +179,11 @@ ZL_EXPORT int ZL_FN(ctx_set_stream)(zl_ctx* ctx, void* cuda_stream);
 /* Two-stream render (default on): the planner of period b + 1 runs beside the gather of period b.  0 = everything on
  * the context stream in order (used by bench.py to time gather_kernel alone). */
 ZL_EXPORT int ZL_FN(ctx_set_overlap)(zl_ctx* ctx, int32_t enable);
+/* A render of ONE period (the live JACK cycle) is submitted as one CUDA-graph launch - the two
+ * counter resets, plan_kernel, walk_kernel, gather_kernel and the port mix captured once per command slot and replayed
+ * while the kernel arguments stay the same.  On by default (environment ZL_B200_GRAPH=0 turns it off); this switch is
+ * for measuring the difference. */
+ZL_EXPORT int ZL_FN(ctx_set_graph)(zl_ctx* ctx, int32_t enable);
 ZL_EXPORT int ZL_FN(sync)(zl_ctx* ctx);
 
 /* ---- clips: ClipAudioSource + SamplerSynthSound ------------------------------------- */

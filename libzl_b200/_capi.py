@@ -83,6 +83,7 @@ SIGNATURES = {
     "config_default": (C.c_int, [_P(zl_config)]),
     "ctx_set_stream": (C.c_int, [_ctx, C.c_void_p]),
     "ctx_set_overlap": (C.c_int, [_ctx, C.c_int32]),
+    "ctx_set_graph": (C.c_int, [_ctx, C.c_int32]),
     "sync": (C.c_int, [_ctx]),
     "clip_create_from_pcm": (C.c_int, [_ctx, _P(_f32p), C.c_int32, C.c_int64, C.c_double, _P(C.c_int32)]),
     "clip_create_from_device": (C.c_int, [_ctx, C.c_void_p, C.c_int32, C.c_int64, C.c_double, _P(C.c_int32)]),

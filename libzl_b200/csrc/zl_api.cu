@@ -140,6 +140,16 @@ struct zl_ctx {
     std::vector<Meter> meters;
     std::vector<Pending> pending;
     bool clipsDirty = true, busesDirty = true;
+    // The tables live twice on the device and in pinned memory: a change is staged into the copy the device is NOT reading
+    // and uploaded by an asynchronous copy ahead of the planner - no pageable copy, no stream synchronise, so a host that
+    // turns a passthrough knob every period (JackPassthrough_setPanAmount, lib/libzl.cpp:476-575) keeps the pipeline full.
+    ClipDev* d_clipsBuf[2] = {nullptr, nullptr}; int32_t* d_sliceBuf[2] = {nullptr, nullptr}; BusDev* d_busesBuf[2] = {nullptr, nullptr};
+    ClipDev* h_clipPin[2] = {nullptr, nullptr}; int32_t* h_slicePin[2] = {nullptr, nullptr}; BusDev* h_busPin[2] = {nullptr, nullptr};
+    int clipTab = 0, busTab = 0;
+    // nblocks == 1 (the live period): plan + walk + gather + mix and the two counter resets as ONE graph launch per command slot,
+    // re-captured whenever any kernel argument differs from the captured ones
+    struct GraphSlot { cudaGraphExec_t exec = nullptr; RenderParams P; float* master = nullptr; bool valid = false; } graph[2];
+    bool graphEnabled = true; uint64_t graphLaunches = 0, graphCaptures = 0;
     // pinned staging
     void* h_stage = nullptr; size_t stageCap = 0;
     zl_block_clock* h_clocks = nullptr;   // unused since the slots below carry the clocks
@@ -369,8 +379,13 @@ int zl_ctx_create(const zl_config* cfg, zl_ctx** out) {
     ctx->sliceStride = 2 * (cfg->max_slices + 1);
     ctx->h_clips.assign((size_t) cfg->max_clips, ClipDev{});
     ctx->h_slice.assign((size_t) cfg->max_clips * ctx->sliceStride, 0);
-    CKC(cudaMalloc((void**) &ctx->d_clips, sizeof(ClipDev) * (size_t) cfg->max_clips));
-    CKC(cudaMalloc((void**) &ctx->d_slice, sizeof(int32_t) * ctx->h_slice.size()));
+    for (int k = 0; k < 2; ++k) {
+        CKC(cudaMalloc((void**) &ctx->d_clipsBuf[k], sizeof(ClipDev) * (size_t) cfg->max_clips));
+        CKC(cudaMalloc((void**) &ctx->d_sliceBuf[k], sizeof(int32_t) * ctx->h_slice.size()));
+        CKC(cudaMallocHost((void**) &ctx->h_clipPin[k], sizeof(ClipDev) * (size_t) cfg->max_clips));
+        CKC(cudaMallocHost((void**) &ctx->h_slicePin[k], sizeof(int32_t) * ctx->h_slice.size()));
+    }
+    ctx->d_clips = ctx->d_clipsBuf[0]; ctx->d_slice = ctx->d_sliceBuf[0];
     CKC(cudaMalloc((void**) &ctx->d_voices, sizeof(VoiceDev) * (size_t) ctx->nvoices()));
     CKC(cudaMemsetAsync(ctx->d_voices, 0, sizeof(VoiceDev) * (size_t) ctx->nvoices(), ctx->stream));
     {   // idle voices: sound = clip = -1
@@ -385,7 +400,11 @@ int zl_ctx_create(const zl_config* cfg, zl_ctx** out) {
     }
     ctx->h_buses.assign((size_t) ctx->nbus(), BusDev{{1.0f, 1.0f, 1.0f, 0.0f, 0}, 1, 0, 0});   // lib/JackPassthrough.cpp:27-31
     ctx->meters.assign((size_t) ctx->nbus(), Meter{});
-    CKC(cudaMalloc((void**) &ctx->d_buses, sizeof(BusDev) * (size_t) ctx->nbus()));
+    for (int k = 0; k < 2; ++k) {
+        CKC(cudaMalloc((void**) &ctx->d_busesBuf[k], sizeof(BusDev) * (size_t) ctx->nbus()));
+        CKC(cudaMallocHost((void**) &ctx->h_busPin[k], sizeof(BusDev) * (size_t) ctx->nbus()));
+    }
+    ctx->d_buses = ctx->d_busesBuf[0];
     CKC(cudaMalloc((void**) &ctx->d_clocks, sizeof(zl_block_clock) * 2 * (size_t) cfg->max_blocks));
     CKC(cudaMallocHost((void**) &ctx->h_clocks, sizeof(zl_block_clock) * 2 * (size_t) cfg->max_blocks));
     CKC(cudaEventCreateWithFlags(&ctx->clkEv[0], cudaEventDisableTiming));
@@ -420,7 +439,12 @@ int zl_ctx_destroy(zl_ctx* ctx) {
         if (s) cudaStreamSynchronize(s);
     if (ctx->comm) { nccl_destroy_comm(ctx->comm); ctx->comm = nullptr; }
     for (ClipHost& c : ctx->clips) { if (c.owned && c.d_data) cudaFree(c.d_data); if (c.d_thumb) cudaFree(c.d_thumb); }
-    void* frees[] = {ctx->d_clips, ctx->d_slice, ctx->d_voices, ctx->d_buses, ctx->d_cmds, ctx->d_clocks, ctx->d_pow2,
+    for (int k = 0; k < 2; ++k) {
+        if (ctx->h_clipPin[k]) cudaFreeHost(ctx->h_clipPin[k]);
+        if (ctx->h_slicePin[k]) cudaFreeHost(ctx->h_slicePin[k]);
+        if (ctx->h_busPin[k]) cudaFreeHost(ctx->h_busPin[k]);
+    }
+    void* frees[] = {ctx->d_clipsBuf[0], ctx->d_clipsBuf[1], ctx->d_sliceBuf[0], ctx->d_sliceBuf[1], ctx->d_voices, ctx->d_busesBuf[0], ctx->d_busesBuf[1], ctx->d_cmds, ctx->d_clocks, ctx->d_pow2,
                      ctx->d_counters, ctx->d_bnd, ctx->d_px, ctx->d_mask, ctx->d_tmp, ctx->d_out[0], ctx->d_out[1],
                      ctx->d_out[2], ctx->d_out[3], ctx->d_masterBuf[0], ctx->d_masterBuf[1], ctx->d_peaks, ctx->d_sumsq};
     for (void* p : frees) if (p) cudaFree(p);
@@ -437,6 +461,7 @@ int zl_ctx_destroy(zl_ctx* ctx) {
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     for (int k = 0; k < 2; ++k) { if (ctx->stageEv[k]) cudaEventDestroy(ctx->stageEv[k]); if (ctx->d_pcmBuf[k]) cudaFree(ctx->d_pcmBuf[k]); }
     if (ctx->d_io) cudaFree(ctx->d_io);
+    for (int k = 0; k < 2; ++k) if (ctx->graph[k].exec) cudaGraphExecDestroy(ctx->graph[k].exec);
     if (ctx->h_clocks) cudaFreeHost(ctx->h_clocks);
     for (int k = 0; k < 2; ++k) { if (ctx->h_slot[k]) cudaFreeHost(ctx->h_slot[k]); if (ctx->d_slot[k]) cudaFree(ctx->d_slot[k]); }
     for (cudaEvent_t e : ctx->tev) cudaEventDestroy(e);
@@ -452,6 +477,12 @@ const char* zl_last_error(zl_ctx* ctx) { return ctx ? ctx->err.c_str() : "null c
 int zl_ctx_set_overlap(zl_ctx* ctx, int32_t enable) {
     if (!ctx) return ZL_ERR_INVALID;
     ctx->overlapEnabled = enable != 0;
+    return ZL_OK;
+}
+
+int zl_ctx_set_graph(zl_ctx* ctx, int32_t enable) {
+    if (!ctx) return ZL_ERR_INVALID;
+    ctx->graphEnabled = enable != 0;
     return ZL_OK;
 }
 
@@ -747,13 +778,6 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     if (rc != ZL_OK) return rc;
     cudaStream_t st = ctx->stream;
     const size_t NB = (size_t) ctx->nbus();
-    // clip table
-    if (ctx->clipsDirty) {
-        CK(cudaMemcpyAsync(ctx->d_clips, ctx->h_clips.data(), sizeof(ClipDev) * ctx->h_clips.size(), cudaMemcpyHostToDevice, st));
-        CK(cudaMemcpyAsync(ctx->d_slice, ctx->h_slice.data(), sizeof(int32_t) * ctx->h_slice.size(), cudaMemcpyHostToDevice, st));
-        CK(cudaStreamSynchronize(st));   // pageable sources: keep the host mirrors free to change
-        ctx->clipsDirty = false;
-    }
     // commands: stable by arrival, then by block; ring capacity 256 per bus per period (lib/SamplerSynth.cpp:32,332-334)
     size_t nCmds = 0;
     std::vector<int> count, begin;
@@ -786,19 +810,35 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
             }
         }
     }
-    if (ctx->busesDirty) {
-        CK(cudaMemcpyAsync(ctx->d_buses, ctx->h_buses.data(), sizeof(BusDev) * NB, cudaMemcpyHostToDevice, st));
-        CK(cudaStreamSynchronize(st));   // pageable source
-        ctx->busesDirty = false;
-    }
     // one pinned slot = clocks | ranges | commands, one H2D copy, no host wait on the device
     const int slot = ctx->clkSlot; ctx->clkSlot ^= 1;
     const size_t offRanges = (sizeof(zl_block_clock) * (size_t) nblocks + 15) & ~size_t(15);
-    const size_t offCmds = offRanges + (nCmds ? ((sizeof(int32_t) * 2 * NB + 15) & ~size_t(15)) : 0);
+    // graph mode (one period, one stream): the per-bus ranges are always there, so the kernel arguments do not depend on
+    // whether this period happens to carry commands
+    static const bool graphEnv = env_int("ZL_B200_GRAPH", 1) != 0;
+    const bool useGraph = graphEnv && ctx->graphEnabled && nblocks == 1 && ctx->timing == 0 && !getenv("ZL_B200_TIMELINE");
+    const bool haveRanges = nCmds > 0 || useGraph;
+    const size_t offCmds = offRanges + (haveRanges ? ((sizeof(int32_t) * 2 * NB + 15) & ~size_t(15)) : 0);
     const size_t slotBytes = offCmds + sizeof(CmdDev) * nCmds;
     auto hp1 = std::chrono::steady_clock::now();
     CK(cudaEventSynchronize(ctx->clkEv[slot]));   // the render that used this slot two calls ago is done
     auto hp2 = std::chrono::steady_clock::now();
+    // Changed clip / bus tables: staged into the copy that the render two calls ago was the last to read (it is done, see the
+    // wait above); the upload itself is queued with the commands below, ahead of this render's planner.
+    int upClips = -1, upBuses = -1;
+    if (ctx->clipsDirty) {
+        upClips = ctx->clipTab ^= 1;
+        memcpy(ctx->h_clipPin[upClips], ctx->h_clips.data(), sizeof(ClipDev) * ctx->h_clips.size());
+        memcpy(ctx->h_slicePin[upClips], ctx->h_slice.data(), sizeof(int32_t) * ctx->h_slice.size());
+        ctx->d_clips = ctx->d_clipsBuf[upClips]; ctx->d_slice = ctx->d_sliceBuf[upClips];
+        ctx->clipsDirty = false;
+    }
+    if (ctx->busesDirty) {
+        upBuses = ctx->busTab ^= 1;
+        memcpy(ctx->h_busPin[upBuses], ctx->h_buses.data(), sizeof(BusDev) * NB);
+        ctx->d_buses = ctx->d_busesBuf[upBuses];
+        ctx->busesDirty = false;
+    }
     if (slotBytes > ctx->slotCap[slot]) {
         if (ctx->h_slot[slot]) cudaFreeHost(ctx->h_slot[slot]);
         if (ctx->d_slot[slot]) cudaFree(ctx->d_slot[slot]);
@@ -811,6 +851,7 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     unsigned char* hs = static_cast<unsigned char*>(ctx->h_slot[slot]);
     unsigned char* ds = static_cast<unsigned char*>(ctx->d_slot[slot]);
     memcpy(hs, clocks, sizeof(zl_block_clock) * (size_t) nblocks);
+    if (haveRanges && !nCmds) memset(hs + offRanges, 0, sizeof(int32_t) * 2 * NB);
     if (nCmds) {
         int32_t* hr = reinterpret_cast<int32_t*>(hs + offRanges);
         int acc = 0;
@@ -829,10 +870,11 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     auto hp3 = std::chrono::steady_clock::now();
     const zl_block_clock* dck = reinterpret_cast<const zl_block_clock*>(ds);
 
-    RenderParams P{};
+    RenderParams P;
+    memset(&P, 0, sizeof P);                        // padding too: the graph cache compares the bytes
     P.voices = ctx->d_voices; P.clips = ctx->d_clips; P.sliceBounds = ctx->d_slice; P.buses = ctx->d_buses;
     P.cmds = reinterpret_cast<const CmdDev*>(ds + offCmds); P.clocks = dck; P.pow2 = ctx->d_pow2;
-    P.cmdRange = nCmds ? reinterpret_cast<const int32_t*>(ds + offRanges) : nullptr;
+    P.cmdRange = haveRanges ? reinterpret_cast<const int32_t*>(ds + offRanges) : nullptr;
     for (int w = 0; w < 4; ++w) P.out[w] = ctx->d_out[w];
     P.master = nullptr; P.peaks = ctx->d_peaks; P.sumsq = ctx->d_sumsq;
     P.voiceFrames = ctx->d_counters;
@@ -898,6 +940,48 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     // wait above: d_counters and d_walkCount are shared across renders, so a first two-stream render must not reset them
     // under a one-stream render still running on the context stream.
     CK(cudaMemcpyAsync(ds, hs, slotBytes, cudaMemcpyHostToDevice, ps));
+    if (upClips >= 0) {
+        CK(cudaMemcpyAsync(ctx->d_clips, ctx->h_clipPin[upClips], sizeof(ClipDev) * ctx->h_clips.size(), cudaMemcpyHostToDevice, ps));
+        CK(cudaMemcpyAsync(ctx->d_slice, ctx->h_slicePin[upClips], sizeof(int32_t) * ctx->h_slice.size(), cudaMemcpyHostToDevice, ps));
+    }
+    if (upBuses >= 0) CK(cudaMemcpyAsync(ctx->d_buses, ctx->h_busPin[upBuses], sizeof(BusDev) * NB, cudaMemcpyHostToDevice, ps));
+    if (useGraph && !overlap) {
+        // ---- the live period as one graph launch ("CUDA-graph launched") -----------------------------------
+        P.blk = 0; P.planCtaCap = 0; P.walkCtaCap = 0;
+        render_bind_scratch(P, static_cast<unsigned char*>(ctx->d_scratch), (int) (NB * ctx->cfg.voices_per_bus), nframes);
+        zl_ctx::GraphSlot& g = ctx->graph[slot];
+        const RenderParams key = P;                 // launch_plan fills in its grid fields: compare and keep what went in
+        if (!g.valid || g.master != ctx->d_master || memcmp(&g.P, &key, sizeof key) != 0) {
+            if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
+            g.valid = false;
+            cudaGraph_t graph = nullptr;
+            CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            cudaError_t ce = cudaMemsetAsync(ctx->d_counters, 0, 2 * sizeof(unsigned long long), st);
+            if (ce == cudaSuccess) ce = cudaMemsetAsync(ctx->d_walkCount, 0, sizeof(int32_t) * 2, st);
+            if (ce == cudaSuccess) ce = launch_plan(P, st);
+            if (ce == cudaSuccess) ce = launch_gather(P, st, nullptr, nullptr);
+            if (ce == cudaSuccess && ctx->d_master)
+                ce = launch_master_mix(ctx->d_out[0], ctx->d_buses, ctx->d_master, ctx->cfg.n_sessions, ctx->cfg.buses_per_session, ctx->stride, (int64_t) nframes, st);
+            const cudaError_t ee = cudaStreamEndCapture(st, &graph);
+            if (ce != cudaSuccess || ee != cudaSuccess) { if (graph) cudaGraphDestroy(graph); return fail(ctx, ce != cudaSuccess ? ce : ee, "graph capture"); }
+            ce = cudaGraphInstantiate(&g.exec, graph, 0);
+            cudaGraphDestroy(graph);
+            if (ce != cudaSuccess) { g.exec = nullptr; return fail(ctx, ce, "cudaGraphInstantiate"); }
+            memcpy(&g.P, &key, sizeof key); g.master = ctx->d_master; g.valid = true;
+            ctx->graphCaptures++;
+        }
+        CK(cudaGraphLaunch(g.exec, st));
+        ctx->graphLaunches++;
+        ctx->launches += ctx->d_master ? 4 : 3;
+        ctx->nblocks = nblocks; ctx->nframes = nframes;
+        ctx->lvlCached = false; ctx->vfCached = false;
+        CK(cudaEventRecord(ctx->clkEv[slot], st));
+        const auto hpEnd = std::chrono::steady_clock::now();
+        ctx->hostSubmitMs += std::chrono::duration<double, std::milli>(hpEnd - hp0).count();
+        ctx->hostWaitMs += std::chrono::duration<double, std::milli>(hp2 - hp1).count();
+        ctx->hostRenders++;
+        return ZL_OK;
+    }
     CK(cudaMemsetAsync(ctx->d_counters, 0, 2 * sizeof(unsigned long long), ps));
     CK(cudaMemsetAsync(ctx->d_walkCount, 0, sizeof(int32_t) * 2 * (size_t) nblocks, ps));
     const char* tl = ctx->timing == 2 ? nullptr : getenv("ZL_B200_TIMELINE");

@@ -305,6 +305,54 @@ __device__ __forceinline__ int plan_voice_block(const RenderParams& P, int vIdx,
                 }
                 h.p = q; h.env = envLast;
                 nrendBlock = nframes;
+            } else if (q >= top) {
+                // ---- one binade crossing, nothing else --------------------------------------------------------
+                // The positions run into the top of their binade inside this period (a looping voice does that five or six
+                // times per pass over a half-second clip: at 1024, 2048, ... frames - half of all the voices that used to leave
+                // the fast path).  Frames [0, kx) are the run below the top; the increment after frame kx - 1 is the
+                // reference's own RN(p + ratio), which lands on the next binade's grid; frames [kx, nframes) are the run
+                // from there.  With no other event on either side (loop end / wrap, stop position, release window) this is
+                // exactly what plan_positions + pos_explicit_step produce tile by tile: one segment per tile, two in the
+                // tile that holds the crossing.
+                const bool la = !JMODE && h.looping;
+                const bool lim = la && bc.beatAligned ? bc.fWrap >= nframes : top <= bc.stopD;
+                if (lim && (JMODE || la || top <= bc.relStart)) {
+                    const int kx = first_k_reaching(h.p, R, top, nframes);          // 1 .. nframes
+                    const double plast = __fma_rn((double) (kx - 1), R, h.p);
+                    const double pn = __dadd_rn(plast, h.ratio);
+                    double Rb, topb;
+                    if (binade_step(pn, h.ratio, Rb, topb)) {
+                        const double qb = __fma_rn((double) (nframes - kx), Rb, pn);
+                        bool ok = qb < topb;
+                        if (!(la && bc.beatAligned)) ok = ok && pn < bc.stopD && qb < bc.stopD;
+                        if (!JMODE && !la) ok = ok && pn < bc.relStart && qb < bc.relStart;
+                        if (ok) {
+                            fast = true;
+                            for (int t = 0; t < P.tilesPerBlock; ++t) {
+                                const int t0 = t * kT;
+                                const int n = min(kT, nframes - t0);
+                                TileDesc d;
+                                d.e0a = __fmaf_rn((float) t0, envE, envE0); d.Ea = envE; d.e0b = 0.0f; d.Eb = 0.0f;
+                                d.ce = n; d.ct = INT_MAX; d.cb = n; d.p0b = 0.0; d.Rb = 0.0;
+                                const int last = t0 + n - 1;
+                                const int lastPos = (int) (last < kx ? __fma_rn((double) last, R, h.p) : __fma_rn((double) (last - kx), Rb, pn));
+                                if (t0 + n <= kx || t0 >= kx) {
+                                    if (t0 >= kx) { d.p0a = __fma_rn((double) (t0 - kx), Rb, pn); d.Ra = Rb; }
+                                    else { d.p0a = __fma_rn((double) t0, R, h.p); d.Ra = R; }
+                                    d.nrend = n | ((bc.nch == 2 && (JMODE || lastPos < sampleDuration)) ? kSimpleBit : 0);
+                                    mark_ring(d, g.data, sampleDuration, n, lastPos);
+                                } else {
+                                    d.p0a = __fma_rn((double) t0, R, h.p); d.Ra = R; d.cb = kx - t0; d.p0b = pn; d.Rb = Rb;
+                                    d.nrend = n;
+                                }
+                                P.descs[(size_t) t * P.nVoices + vIdx] = d;
+                                bc.lastPos = lastPos;
+                            }
+                            h.p = qb; h.env = envLast;
+                            nrendBlock = nframes;
+                        }
+                    }
+                }
             }
         }
     }

@@ -721,6 +721,7 @@ int zlo_ctx_destroy(zl_ctx* c) { if (!c) return ZL_ERR_INVALID; for (Clip* k : c
 const char* zlo_last_error(zl_ctx* c) { return c ? c->err.c_str() : "null ctx"; }
 int zlo_ctx_set_stream(zl_ctx*, void*) { return ZL_OK; }
 int zlo_ctx_set_overlap(zl_ctx*, int32_t) { return ZL_OK; }
+int zlo_ctx_set_graph(zl_ctx*, int32_t) { return ZL_OK; }
 int zlo_sync(zl_ctx*) { return ZL_OK; }
 ZL_EXPORT int zlo_set_threads(zl_ctx* c, int n) { if (!c || n < 1) return ZL_ERR_INVALID; c->threads = n; return ZL_OK; }
 

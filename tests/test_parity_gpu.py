@@ -400,3 +400,37 @@ def test_command_ring_overflow_and_late_commands_are_dropped_like_the_reference(
         assert not S.compare(a, b, exact_audio=True)
         assert int(a["dropped"][0]) == (300 - 256 + 2 if not split else 2)
         assert np.abs(a["raw"]).max() > 0.01
+
+
+def test_live_period_as_a_graph_launch_with_a_knob_turned_every_period(product, oracle):
+    """nblocks == 1 renders go out as one CUDA-graph launch per command slot (re-captured when an argument changes), and a
+    passthrough / clip parameter changed between periods reaches the device through the double-buffered pinned tables
+    without a stream synchronise: 40 periods with a pan knob moved every period, commands in some, a clip parameter and the
+    frame count changed mid-way - graph on, graph off and the oracle give the same bytes."""
+    outs = []
+    for lib, graph in ((product, 1), (product, 0), (oracle, 1)):
+        e = Engine(lib=lib, mode=K.ZL_MODE_Z, quirks=K.ZL_QUIRKS_FAITHFUL, max_frames=256, max_blocks=4)
+        e._chk(lib.ctx_set_graph(e.ctx, graph), "ctx_set_graph")
+        a = e.add_clip(S.noise_clip(3, 9000))
+        b = e.add_clip(S.noise_clip(4, 30000))
+        e.set_clip_params(b, length_s=0.25, length_beats=0.5, attack=0.01, release=0.05)
+        e.play(a, note=60, volume=0.9)
+        res = []
+        for i in range(40):
+            nf = 256 if i < 25 else 192
+            e.set_passthrough(0, 3, dry=0.5 + 0.01 * i, fx1=0.3, fx2=0.1, pan=-0.8 + 0.04 * i)
+            if i % 7 == 3:
+                e.play(b, loop=True, note=57 + i % 5, volume=0.7, midi_channel=1)
+            if i == 20:
+                e.set_clip_params(b, pan=0.5)
+            if i == 30:
+                e.render(2, nf, e.make_clocks(2, nf, first_block=1000))      # a two-period render in between: the plain path
+                res.append(S.collect(e))
+            e.render(1, nf, e.make_clocks(1, nf, first_block=i))
+            res.append(S.collect(e))
+        outs.append(res)
+        e.close()
+    for k in (1, 2):
+        for x, y in zip(outs[0], outs[k]):
+            assert not S.compare(x, y, exact_audio=True)
+    assert max(float(np.abs(r["raw"]).max()) for r in outs[0]) > 0.05
