@@ -361,6 +361,17 @@ ZL_EXPORT int ZL_FN(passthrough_process)(zl_ctx* ctx, const zl_passthrough_param
 /* Peak scan of one period (lib/AudioLevels.cpp:365-382) + sum of squares, HOST buffers. */
 ZL_EXPORT int ZL_FN(levels_scan)(zl_ctx* ctx, const float* l, const float* r, int64_t n,
                                  int32_t* peak_a, int32_t* peak_b, double* sumsq_a, double* sumsq_b);
+/* The same scan without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that may not call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Input staging and accumulators live in a file-scope static __device__ array of 256 + 8 * ZL_STATIC_SCAN_MAX_FRAMES bytes
+ * (2 MiB + 256 B), held by every GPU that loads the library until the process exits; the call makes no cudaMalloc, cudaFree
+ * or allocating library call.  n > ZL_STATIC_SCAN_MAX_FRAMES is refused with ZL_ERR_INVALID (zl_last_error says why).
+ * All calls on a device share the one array (the accumulators are cleared at every call): calls that overlap on the GPU -
+ * two contexts or two streams scanning at the same time on one device - race; serialise them.  Same results as
+ * zl_levels_scan: peaks bit-equal, sums of squares equal up to f64 summation order. */
+#define ZL_STATIC_SCAN_MAX_FRAMES 262144
+ZL_EXPORT int ZL_FN(levels_scan_static)(zl_ctx* ctx, const float* l, const float* r, int64_t n,
+                                        int32_t* peak_a, int32_t* peak_b, double* sumsq_a, double* sumsq_b);
 
 /* ---- n3: bounce ------------------------------------------------------ */
 /* The last render of one stereo port as the WAV file the reference's DiskWriter leaves on disk (lib/AudioLevels.cpp:35-119:

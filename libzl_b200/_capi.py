@@ -152,6 +152,8 @@ SIGNATURES = {
     "passthrough_process": (C.c_int, [_ctx, _P(zl_passthrough_params), _f32p, _f32p, C.c_int64, _f32p]),
     "levels_scan": (C.c_int, [_ctx, _f32p, _f32p, C.c_int64, _P(C.c_int32), _P(C.c_int32), _P(C.c_double),
                               _P(C.c_double)]),
+    "levels_scan_static": (C.c_int, [_ctx, _f32p, _f32p, C.c_int64, _P(C.c_int32), _P(C.c_int32), _P(C.c_double),
+                              _P(C.c_double)]),
     "host_alloc": (C.c_int, [_P(C.c_void_p), C.c_size_t]),
     "host_free": (C.c_int, [C.c_void_p]),
 }

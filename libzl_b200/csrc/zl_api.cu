@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 #include <chrono>
@@ -1631,6 +1632,68 @@ int zl_levels_scan(zl_ctx* ctx, const float* l, const float* r, int64_t n, int32
     }
     struct { double sq[2]; int pk[2]; } res;
     CK(cudaMemcpyAsync(&res, ctx->d_tmp, sizeof res, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (pa) *pa = res.pk[0];
+    if (pb) *pb = res.pk[1];
+    if (sa) *sa = res.sq[0];
+    if (sb) *sb = res.sq[1];
+    return ZL_OK;
+}
+
+// ---- zl_levels_scan_static: the peak / sum-of-squares scan without any allocation ------------------------------------
+// No counterpart in the reference; added for callers that may not call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  zl_levels_scan stages its input and keeps
+// its accumulators in a grow-only cudaMalloc'ed scratch; this variant runs the same kernel (launch_levels) on a FILE-SCOPE
+// device array of fixed size, which every GPU that loads the library holds until the process exits:
+//   bytes [0, 256): accumulators (2 double sums, 2 int peaks), cleared at every call;  then the left row, then the right row.
+// In host code `g_scanScratch` is only a host-side stand-in for the symbol, NOT a device address: the address each device
+// gave the array is looked up once per device, with that device current, by cudaGetSymbolAddress, and that pointer is
+// what the copies and the kernel get.
+}  // extern "C"
+constexpr int64_t kStaticScanMaxFrames = ZL_STATIC_SCAN_MAX_FRAMES;
+constexpr size_t kStaticScanHeader = 256;
+static __device__ __align__(256) unsigned char g_scanScratch[kStaticScanHeader + 2 * sizeof(float) * (size_t) kStaticScanMaxFrames];
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_scanMutex;
+unsigned char* g_scanPtr[kMaxDevices] = {nullptr};
+// the array's address on `device`, which must be the current device; cached after the first successful look-up
+cudaError_t static_scan_scratch(int device, unsigned char** out) {
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_scanMutex);
+    if (!g_scanPtr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_scanScratch);
+        if (e != cudaSuccess) return e;
+        g_scanPtr[device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_scanPtr[device];
+    return cudaSuccess;
+}
+}  // namespace
+extern "C" {
+int zl_levels_scan_static(zl_ctx* ctx, const float* l, const float* r, int64_t n, int32_t* pa, int32_t* pb, double* sa, double* sb) {
+    BIND();
+    if (!l || !r || n < 0) return invalid(ctx, "levels_scan_static: bad argument");
+    if (n > kStaticScanMaxFrames) {
+        ctx->err = "levels_scan_static: more than ZL_STATIC_SCAN_MAX_FRAMES (262144) frames - the static scratch is fixed; use zl_levels_scan";
+        return ZL_ERR_INVALID;
+    }
+    unsigned char* scratch = nullptr;
+    CK(static_scan_scratch(ctx->device, &scratch));
+    double* dsq = reinterpret_cast<double*>(scratch);                  // [0..1] sums, then 2 int peaks (the layout zl_levels_scan uses)
+    int* dpk = reinterpret_cast<int*>(scratch + 16);
+    float* dl = reinterpret_cast<float*>(scratch + kStaticScanHeader);
+    float* dr = dl + n;
+    CK(cudaMemsetAsync(scratch, 0, kStaticScanHeader, ctx->stream));   // the array keeps the last call's contents: the accumulators start at zero
+    if (n) {
+        CK(cudaMemcpyAsync(dl, l, sizeof(float) * (size_t) n, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(dr, r, sizeof(float) * (size_t) n, cudaMemcpyHostToDevice, ctx->stream));
+        CK(launch_levels(dl, dr, n, dpk, dsq, ctx->stream));
+        ctx->launches++;
+    }
+    struct { double sq[2]; int pk[2]; } res;
+    CK(cudaMemcpyAsync(&res, scratch, sizeof res, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     if (pa) *pa = res.pk[0];
     if (pb) *pb = res.pk[1];

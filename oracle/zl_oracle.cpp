@@ -1087,6 +1087,11 @@ int zlo_levels_scan(zl_ctx*, const float* l, const float* r, int64_t n, int32_t*
     if (sb) *sb = sumSquares(r, (size_t) n);
     return ZL_OK;
 }
+// the product's allocation-free variant (no counterpart in the reference): the same scan, refused beyond the fixed scratch
+int zlo_levels_scan_static(zl_ctx* ctx, const float* l, const float* r, int64_t n, int32_t* pa, int32_t* pb, double* sa, double* sb) {
+    if (n > ZL_STATIC_SCAN_MAX_FRAMES) return ZL_ERR_INVALID;
+    return zlo_levels_scan(ctx, l, r, n, pa, pb, sa, sb);
+}
 
 // ---- rows n1 / n3: WAV in, WAV out — restated from the reference's reader and writer ----------------
 // Reader: juce::WavAudioFormatReader ctor (juce_WavAudioFormat.cpp:933-1190) walks the chunks; readSamples/copySampleData
