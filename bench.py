@@ -722,10 +722,16 @@ def main():
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": el_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32 (f64 positions)", "data": "synthetic", "config": config,
                 "clocks": r["clocks"], "gpu_launches": r["launches"],
-                "e2e": {"value": e2e_vf / (e2e_ms * 1e-3), "unit": "voice-frames/s", "h2d_bytes_per_step": r["h2d"],
-                        "d2h_bytes_per_step": r["d2h"], "what": "per step: zl_command_batch (H2D) + zl_render + zl_read_master_all_async (master of every session D2H to pinned host, overlapping the next step's render); zl_read_wait before the clock stops"},
-                "e2e_pcm16": {"value": e2e_pcm_vf / (e2e_pcm_ms * 1e-3), "unit": "voice-frames/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h_pcm"],
-                              "what": "the same loop with zl_read_master_all_pcm_async(bits=16): every session's master leaves the device as the 16-bit data chunk of the reference recorder's WAV file (lib/AudioLevels.cpp:35-119), encoded on the device - half the D2H bytes; checked against zl_bounce_wav after the clock stops"},
+                # end to end = the offline bounce a host makes: commands in (pinned host, H2D), every session's mix out as the
+                # 16-bit PCM of the reference recorder's WAV files (lib/AudioLevels.cpp:35-119), on the host when the clock stops.
+                # The same loop with the masters read back as f32 planes (the parity path) is reported beside it as e2e_f32:
+                # at 8 GPUs behind one host it is bound by the host's memory/PCIe, not by anything on the devices.
+                "e2e": {"value": e2e_pcm_vf / (e2e_pcm_ms * 1e-3), "unit": "voice-frames/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h_pcm"],
+                        "what": "per step: zl_command_batch (H2D from pinned host memory) + zl_render + zl_read_master_all_pcm_async(bits=16) - every session's master "
+                                "leaves the device as the 16-bit data chunk of the reference recorder's WAV file, encoded on the device, D2H into pinned host memory "
+                                "overlapping the next step's render; zl_read_wait before the clock stops; bytes checked against zl_bounce_wav afterwards"},
+                "e2e_f32": {"value": e2e_vf / (e2e_ms * 1e-3), "unit": "voice-frames/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                            "what": "the same loop with zl_read_master_all_async: the masters as f32 planes (twice the D2H bytes; the path the parity_at_size check reads)"},
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                              "traffic": (ncu_traffic() if (args.sessions, args.blocks, args.quirks) == (4096, 16, 7) else None),
                              "traffic_source": f"{TRAFFIC_FILE} (ncu --set full, builder-run capture of this command; NOT measured by this run)",

@@ -13,6 +13,7 @@
 #include <vector>
 #include <chrono>
 
+#include <cuda_profiler_api.h>
 #include <dlfcn.h>
 #include <fcntl.h>
 #include <sys/mman.h>
@@ -147,6 +148,7 @@ struct zl_ctx {
     ClipDev* d_clipsBuf[2] = {nullptr, nullptr}; int32_t* d_sliceBuf[2] = {nullptr, nullptr}; BusDev* d_busesBuf[2] = {nullptr, nullptr};
     ClipDev* h_clipPin[2] = {nullptr, nullptr}; int32_t* h_slicePin[2] = {nullptr, nullptr}; BusDev* h_busPin[2] = {nullptr, nullptr};
     int clipTab = 0, busTab = 0;
+    bool skipSlotWait = false;                          // profiling aid (ZL_B200_PROFILE_RENDER)
     // nblocks == 1 (the live period): plan + walk + gather + mix and the two counter resets as ONE graph launch per command slot,
     // re-captured whenever any kernel argument differs from the captured ones
     struct GraphSlot { cudaGraphExec_t exec = nullptr; RenderParams P; float* master = nullptr; bool valid = false; } graph[2];
@@ -769,7 +771,25 @@ static int ensure_outputs(zl_ctx* ctx, int nblocks, int nframes) {
     return ZL_OK;
 }
 
+static int render_impl(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_clock* clocks);
+// Profiling aid: ZL_B200_PROFILE_RENDER=k brackets the k-th multi-period zl_render of the process with cudaProfilerStart /
+// cudaProfilerStop (device idle on both sides), so `ncu --replay-mode range` measures the streams of one render TOGETHER -
+// the planner beside the gather - which kernel-by-kernel replay cannot.
 int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_clock* clocks) {
+    static const int profAt = env_int("ZL_B200_PROFILE_RENDER", 0);
+    static int calls = 0;
+    const bool prof = profAt > 0 && nblocks > 1 && ++calls == profAt;
+    if (prof) {
+        // the device is idle: forget every event recorded before the range (range replay cannot capture waits on them)
+        cudaDeviceSynchronize();
+        ctx->planChained = false; ctx->copyPending[0] = ctx->copyPending[1] = false; ctx->skipSlotWait = true;
+        cudaProfilerStart();
+    }
+    const int rc = render_impl(ctx, nblocks, nframes, clocks);
+    if (prof) { cudaDeviceSynchronize(); cudaProfilerStop(); }
+    return rc;
+}
+static int render_impl(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_clock* clocks) {
     BIND();
     if (nblocks < 1 || nframes < 1 || !clocks || nblocks > ctx->cfg.max_blocks || nframes > ctx->cfg.max_frames)
         return invalid(ctx, "render: nblocks/nframes out of range or null clocks");
@@ -822,7 +842,8 @@ int zl_render(zl_ctx* ctx, int32_t nblocks, int32_t nframes, const zl_block_cloc
     const size_t offCmds = offRanges + (haveRanges ? ((sizeof(int32_t) * 2 * NB + 15) & ~size_t(15)) : 0);
     const size_t slotBytes = offCmds + sizeof(CmdDev) * nCmds;
     auto hp1 = std::chrono::steady_clock::now();
-    CK(cudaEventSynchronize(ctx->clkEv[slot]));   // the render that used this slot two calls ago is done
+    if (!ctx->skipSlotWait) CK(cudaEventSynchronize(ctx->clkEv[slot]));   // the render that used this slot two calls ago is done
+    ctx->skipSlotWait = false;
     auto hp2 = std::chrono::steady_clock::now();
     // Changed clip / bus tables: staged into the copy that the render two calls ago was the last to read (it is done, see the
     // wait above); the upload itself is queued with the commands below, ahead of this render's planner.

@@ -980,6 +980,29 @@ void render_bind_scratch(RenderParams& P, void* scratch, int nVoices, int nframe
     P.tilesPerBlock = (nframes + kT - 1) / kT;
 }
 
+// Profiling aid (ZL_B200_DEBUG_SKIP bits 8 / 16, results become wrong): stand-ins for walk_kernel that keep its shape - 625
+// one-warp CTAs busy for about as long - but (8) run a dependent FMA chain in a 4-instruction loop, i.e. no instruction-cache
+// footprint and no memory traffic, or (16) additionally wander through a large body of straight-line code.
+__global__ void __launch_bounds__(32, 1) spin_small_kernel(float* sink, int iters) {
+    float x = (float) threadIdx.x, y = 1.0001f;
+#pragma unroll 1
+    for (int i = 0; i < iters; ++i) x = __fmaf_rn(x, y, 0.5f);
+    if (x == 12345.678f) *sink = x;
+}
+__device__ __forceinline__ float big_body(float x, float y) {
+#pragma unroll
+    for (int k = 1; k <= 600; ++k) {
+        x = __fmaf_rn(x, y, (float) k); x = __fmaf_rn(x, x, 0.25f); x = __fmul_rn(x, 0.5f); x = __fadd_rn(x, (float) (k * 3));
+    }
+    return x;
+}
+__global__ void __launch_bounds__(32, 1) spin_big_kernel(float* sink, int iters) {
+    float x = (float) threadIdx.x, y = 1.0001f;
+#pragma unroll 1
+    for (int i = 0; i < iters; ++i) x = big_body(x, y);       // 2400 dependent instructions = 38 KB of code per iteration
+    if (x == 12345.678f) *sink = x;
+}
+
 // One block (P.blk) of every session: launch_plan (plan_kernel + walk_kernel), then launch_gather.  The two may sit on
 // different streams (zl_api.cu orders them with events and double-buffers the hand-over), so that the latency-bound
 // planner of period b + 1 fills the issue slots the gather of period b leaves idle.
@@ -1012,7 +1035,11 @@ cudaError_t launch_plan(RenderParams& P, cudaStream_t stream) {
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     const int wGrid = min((P.nVoices + 31) / 32 + 1, P.walkCtaCap > 0 ? P.walkCtaCap : 148 * 16);
-    if (skip & 2) return cudaSuccess;
+    if (skip & 2) {
+        if (skip & 8) spin_small_kernel<<<625, 32, 0, stream>>>(reinterpret_cast<float*>(P.walkQueue), 60000);     // ~60000 x 4 cycles = 120 us
+        if (skip & 16) spin_big_kernel<<<625, 32, 0, stream>>>(reinterpret_cast<float*>(P.walkQueue), 25);          // 25 x 2400 x 4 cycles = 120 us
+        return cudaGetLastError();
+    }
     if (P.mode == ZL_MODE_J) ZL_LAUNCH((walk_kernel<true, false>), wGrid, 32, stream, P);
     else if (q3) ZL_LAUNCH((walk_kernel<false, true>), wGrid, 32, stream, P);
     else ZL_LAUNCH((walk_kernel<false, false>), wGrid, 32, stream, P);
