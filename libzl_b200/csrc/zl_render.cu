@@ -1003,6 +1003,25 @@ __global__ void __launch_bounds__(32, 1) spin_big_kernel(float* sink, int iters)
     if (x == 12345.678f) *sink = x;
 }
 
+// (32): the small spin plus walk-like memory traffic - every lane loads a 224-byte voice record piece by piece (32 sectors per
+// instruction) and stores 16-byte pieces of its own 2 KB envelope row, as plan_voice_block / plan_envelope_walk do.
+__global__ void __launch_bounds__(32, 1) spin_mem_kernel(const RenderParams P, int iters) {
+    const unsigned v = ((blockIdx.x * 32u + threadIdx.x) * 7919u) % (unsigned) P.nVoices;
+    const int4* rec = reinterpret_cast<const int4*>(P.voices + v);
+    float4* row = reinterpret_cast<float4*>(P.te + (size_t) v * kT);
+    float x = (float) threadIdx.x;
+    int acc = 0;
+#pragma unroll 1
+    for (int k = 0; k < 14; ++k) acc += __ldg(rec + k).x;               // the record: 14 x 16 B
+#pragma unroll 1
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll 1
+        for (int k = 0; k < 64; ++k) x = __fmaf_rn(x, 1.0001f, 0.5f);
+        row[i & 127] = make_float4(x, x, x, (float) acc);               // 8 frames of envelope per 2 stores in the real thing
+    }
+    if (x == 12345.678f) P.walkQueue[0] = acc;
+}
+
 // One block (P.blk) of every session: launch_plan (plan_kernel + walk_kernel), then launch_gather.  The two may sit on
 // different streams (zl_api.cu orders them with events and double-buffers the hand-over), so that the latency-bound
 // planner of period b + 1 fills the issue slots the gather of period b leaves idle.
@@ -1038,6 +1057,7 @@ cudaError_t launch_plan(RenderParams& P, cudaStream_t stream) {
     if (skip & 2) {
         if (skip & 8) spin_small_kernel<<<625, 32, 0, stream>>>(reinterpret_cast<float*>(P.walkQueue), 60000);     // ~60000 x 4 cycles = 120 us
         if (skip & 16) spin_big_kernel<<<625, 32, 0, stream>>>(reinterpret_cast<float*>(P.walkQueue), 25);          // 25 x 2400 x 4 cycles = 120 us
+        if (skip & 32) spin_mem_kernel<<<625, 32, 0, stream>>>(P, 128);                                              // 128 x 64 FMAs + 128 scattered 16-byte stores per lane
         return cudaGetLastError();
     }
     if (P.mode == ZL_MODE_J) ZL_LAUNCH((walk_kernel<true, false>), wGrid, 32, stream, P);
