@@ -538,6 +538,43 @@ def latency_probe(local_rank, iters=1500):
                     "+ zl_read_master_all to pinned host; plain_launches = the same with the graph switched off (zl_ctx_set_graph 0)"}
 
 
+def sched_probe(steps=200):
+    """Row n2: the command scheduler (host code inside the product library) feeding one session - 96 commands scheduled per
+    step onto a running timer, zl_sched_advance over the step's 16 periods."""
+    import libzl_b200
+    from libzl_b200 import _capi as K
+    lib = libzl_b200.load()
+    s = C.c_void_p()
+    assert lib.sched_create(RATE, FRAMES, C.byref(s)) == K.ZL_OK
+    lib.sched_start(s, 120)
+    c = K.zl_clip_command()
+    lib.clip_command_default(C.byref(c))
+    rng = np.random.default_rng(1)
+    nb = 16
+    period = int(round(FRAMES * 1e6 / RATE))
+    ck = (K.zl_block_clock * nb)()
+    ev = (K.zl_sched_event * 8192)()
+    n = C.c_int32()
+    t_sched = t_adv = 0.0
+    ncmd = nev = per = 0
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        for k in range(96):
+            c.clip, c.midi_channel, c.midi_note, c.start_playback, c.change_volume, c.volume = k % 8, k % 12 - 2, 48 + k // 12, 1, 1, 0.5
+            lib.sched_schedule(s, C.byref(c), int(rng.integers(0, 64)))
+        t1 = time.perf_counter()
+        for i in range(nb):
+            ck[i].current_usecs = 1_000_000 + (per + i) * period
+            ck[i].next_usecs = ck[i].current_usecs + period
+        lib.sched_advance(s, nb, FRAMES, ck, ev, 8192, C.byref(n))
+        t2 = time.perf_counter()
+        per += nb; ncmd += 96; nev += n.value; t_sched += t1 - t0; t_adv += t2 - t1
+    lib.sched_destroy(s)
+    return {"advance_us_per_step": round(t_adv / steps * 1e6, 1), "commands_scheduled": ncmd, "commands_emitted": nev,
+            "schedule_calls_per_s_through_ctypes": round(ncmd / t_sched),
+            "what": "zl_sched_*: 96 commands scheduled per step onto a running 120 bpm timer, zl_sched_advance over 16 periods x 512 frames; one host core"}
+
+
 def cpu_latency_probe(iters=300):
     """The same single period of one 128-voice session on ONE host thread with the oracle port (contraction on, as the
     reference is built): the CPU figure that stands beside the device latency."""
@@ -752,6 +789,7 @@ def main():
             try:
                 line["latency"] = latency_probe(local_rank)
                 line["cpu_latency"] = cpu_latency_probe()
+                line["scheduler"] = sched_probe()
             except Exception as ex:   # noqa: BLE001
                 line["latency"] = {"error": str(ex)}
         if world == 1 and not args.no_thumb:
