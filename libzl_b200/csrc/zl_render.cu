@@ -63,6 +63,10 @@ constexpr int kSlots = ZL_SLOTS;             // staging slots per warp: kSlots -
 #ifndef ZL_TMA
 #define ZL_TMA 1
 #endif
+// Experiment switch: L2 prefetch of a tile's later windows at tile start (0 off, 1 bulk prefetch per window, 2 per-line prefetch).
+#ifndef ZL_L2PF
+#define ZL_L2PF 0
+#endif
 constexpr int kWantPeak = 1 << 8;     // VoiceGather.nch flag: the positions model takes this block's peak  :265-267
 
 // The gather of one voice x one tile is split in two so all of the tile's loads are in flight together:
@@ -150,9 +154,10 @@ __device__ __forceinline__ void gather_issue_simple(const TileDesc& d, const Voi
 // (FMUL2 / FADD2: two independently IEEE-rounded f32 operations per lane per issue slot; no contraction, _rn intrinsics).
 // acc[ch] = (L, R) of the bus for this lane's frame of chunk ch.
 template <bool JMODE, bool Q1, bool FULL>
-__device__ __forceinline__ float gather_finish(const VoiceGather& g, const Taps& t, int nchunks, float nz, float2* __restrict__ acc) {
+__device__ __forceinline__ float gather_finish(const VoiceGather& g, const Taps& t, int nchunks, float nz, float2 pm1, float2* __restrict__ acc) {
     float vmax = 0.0f;
     const float2 g2 = make_float2(g.gain, g.gain), vol2 = make_float2(g.vol, g.vol), nz2 = make_float2(nz, nz);
+    const float2 pan2 = make_float2(g.lPan, g.rPan);                  // pm1 = (1, -1), opaque like nz (kept in a uniform register pair)
 #pragma unroll
     for (int ch = 0; ch < kG; ++ch) {
         if (FULL || ch < nchunks) {                                   // warp-uniform
@@ -173,10 +178,13 @@ __device__ __forceinline__ float gather_finish(const VoiceGather& g, const Taps&
                                     __ffma2_rn(__fmul2_rn(__fmul2_rn(__fmul2_rn(t.b[ch], al2), g2), env2), vol2, nz2));
                 else
                     lr = __fmul2_rn(__fmul2_rn(__fmul2_rn(__fadd2_rn(__ffma2_rn(t.a[ch], ia2, nz2), __ffma2_rn(t.b[ch], al2, nz2)), g2), env2), vol2);
-                const float m = __fmul_rn(0.5f, __fadd_rn(lr.x, lr.y));   // :208 (0.5*(l+r) in f64 is exact)
-                const float sd = __fsub_rn(lr.x, lr.y);
-                lr.x = __fadd_rn(__fmul_rn(g.lPan, m), sd);
-                lr.y = __fsub_rn(__fmul_rn(g.rPan, m), sd);
+                // M/S pan  :208-216:  m = 0.5 (l + r), s = l - r, l' = lPan m + s, r' = rPan m - s, every operation rounded on
+                // its own.  Packed: (l + r, l - r) = fma((1, -1), r, l) and (l', r') = fma((1, -1), s, (lPan m, rPan m)) - a
+                // product with +-1 is exact, so each half is exactly the rounded sum / difference (zero signs included: the
+                // product -1 * s carries the sign a subtraction of s would see).
+                const float2 ss = __ffma2_rn(pm1, make_float2(lr.y, lr.y), make_float2(lr.x, lr.x));
+                const float m = __fmul_rn(0.5f, ss.x);                    // 0.5*(l+r) in f64 is exact
+                lr = __ffma2_rn(pm1, make_float2(ss.y, ss.y), __fmul2_rn(pan2, make_float2(m, m)));
             }
             acc[ch] = __fadd2_rn(acc[ch], lr);                      // lanes past the voice's end add +0
             vmax = fmaxf(vmax, __fadd_rn(lr.x, lr.y));
@@ -210,6 +218,12 @@ __device__ __forceinline__ void mark_ring(TileDesc& d, const float* data, int sa
     d.nrend |= kRingBit;
     d.p0b = __longlong_as_double((long long) (reinterpret_cast<uintptr_t>(data) + (size_t) base * 8));
     d.Rb = __hiloint2double(base, bytes);
+    // The tile's first position relative to the window, p0a - base, in the two unused floats of envelope segment b
+    // (a ring tile has one envelope segment).  Exact: both are multiples of the binade's ulp u and the difference is < 2^9,
+    // so it needs no more than 53 bits; the same holds for every p_k - base of the tile, and frac(p_k - base) = frac(p_k).
+    const double prel = __dsub_rn(d.p0a, (double) base);
+    d.e0b = __int_as_float(__double2loint(prel));
+    d.Eb = __int_as_float(__double2hiint(prel));
 }
 
 // What a position plan may change before it is accepted.
@@ -628,30 +642,45 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         "}" :: "r"(bar), "r"(parity) : "memory");
 }
 __device__ __forceinline__ void stage_window_tma(const TileDesc& d, int lane, uint32_t slot, uint32_t bar) {
-    if (lane == 0) {
-        const uint64_t src = (uint64_t) __double_as_longlong(d.p0b);
-        const uint32_t bytes = (uint32_t) __double2loint(d.Rb);          // whole 512-byte rows, 16-byte aligned source (mark_ring)
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                     :: "r"(slot), "l"(src), "r"(bytes), "r"(bar) : "memory");
-    }
+    // Every lane holds the same descriptor (a shared-memory broadcast), so the operands are warp-uniform and the issuing
+    // lane is picked by elect.sync inside the warp-convergent code: ptxas then feeds UBLKCP from uniform registers directly
+    // instead of wrapping it in the loop it builds around a divergent `if (lane == 0)`.
+    const uint64_t src = (uint64_t) __double_as_longlong(d.p0b);
+    const uint32_t bytes = (uint32_t) __double2loint(d.Rb);              // whole 512-byte rows, 16-byte aligned source (mark_ring)
+    (void) lane;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "@p mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n"
+        "@p cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%2], [%3], %1, [%0];\n"
+        "}" :: "r"(bar), "r"(bytes), "r"(slot), "l"(src) : "memory");
 }
 #endif
 
 // One group (kG chunks from tile frame c0) of a window-staged voice-tile.
+// Positions run in the window's own frame: p'_k = (p0a - base) + k R (mark_ring), so floor(p'_k) indexes the slot directly
+// and the fraction is that of p_k.  Every p'_k of the tile is exactly representable (zl_voice.cuh: multiples of the binade's
+// ulp, one binade per segment), so the lane's first position is one DFMA and each further chunk ONE exact DADD of 32 R
+// instead of a DADD + DFMA pair; the envelope e_k = e0a + k Ea is exact on its f32 grid the same way (Ea = 0: sustain).
 template <bool JMODE, bool Q1>
 __device__ __forceinline__ float gather_finish_ring(const TileDesc& d, const VoiceGather& g, const unsigned char* slot, double laneD, float laneF,
-                                                    float nz, int c0, float2* __restrict__ acc) {
+                                                    float nz, float2 pm1, int c0, float2* __restrict__ acc) {
     Taps t;
-    const float2* win = reinterpret_cast<const float2*>(slot) - __double2hiint(d.Rb);   // win[pos] = source frame pos
+    const float2* win = reinterpret_cast<const float2*>(slot);                          // win[pos'] = source frame base + pos'
+    const double prel = __hiloint2double(__float_as_int(d.Eb), __float_as_int(d.e0b));
+    const double R32 = __dmul_rn(d.Ra, 32.0);
+    const float E32 = __fmul_rn(d.Ea, 32.0f);
+    double p = __fma_rn(c0 ? __dadd_rn(laneD, (double) c0) : laneD, d.Ra, prel);
+    float e = __fmaf_rn(c0 ? __fadd_rn(laneF, (float) c0) : laneF, d.Ea, d.e0a);
 #pragma unroll
     for (int ch = 0; ch < kG; ++ch) {
-        const double p = __fma_rn(__dadd_rn(laneD, (double) (c0 + ch * 32)), d.Ra, d.p0a);
+        if (ch) { p = __dadd_rn(p, R32); e = __fadd_rn(e, E32); }
         const int pos = split_pos(p, t.alpha[ch]);
         t.a[ch] = win[pos]; t.b[ch] = win[pos + 1];
-        t.env[ch] = __fmaf_rn(__fadd_rn(laneF, (float) (c0 + ch * 32)), d.Ea, d.e0a);     // Ea == 0 (sustain): exactly e0a
+        t.env[ch] = e;
     }
-    return gather_finish<JMODE, Q1, true>(g, t, kG, nz, acc);
+    return gather_finish<JMODE, Q1, true>(g, t, kG, nz, pm1, acc);
 }
 
 // LEAN: only the raw SamplerChannel ports (and what the master mix and the meters need) are materialised - no dry / fx planes,
@@ -680,6 +709,8 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
     const double laneD = (double) lane;
     const float laneF = (float) lane;
     const float nz = __int_as_float((int) (0x80000000u | ((unsigned) P.nframes >> 31)));   // -0.0f, opaque to the compiler (see gather_finish)
+    const unsigned opq = (unsigned) P.nframes >> 31;                                       // 0, opaque
+    const float2 pm1 = make_float2(__int_as_float((int) (0x3f800000u | opq)), __int_as_float((int) (0xbf800000u | opq)));   // (1, -1) for the packed M/S pan
     const zl_passthrough_params pt = P.buses[gbw].pt;
     const int64_t off = (int64_t) blk * nframes;
     const int64_t rowL = ((int64_t) gbw * 2) * P.stride + off, rowR = rowL + P.stride;
@@ -778,6 +809,28 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
             toStage = __ballot_sync(FULL, (fl & kCountMask) != 0 && (fl & kRingBit) != 0);
 #pragma unroll
             for (int k = 0; k < kSlots - 1; ++k) stage_next();
+#if ZL_L2PF == 1
+            // the windows that will be staged later in this tile start their way from DRAM to L2 now (one bulk prefetch each)
+            for (unsigned m = toStage; m; m &= m - 1) {
+                const TileDesc& sd = sDesc[warp][__ffs(m) - 1];
+                const uint64_t src = (uint64_t) __double_as_longlong(sd.p0b);
+                const uint32_t bytes = (uint32_t) __double2loint(sd.Rb);
+                asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\n@p cp.async.bulk.prefetch.L2.global [%0], %1;\n}" :: "l"(src), "r"(bytes) : "memory");
+            }
+#elif ZL_L2PF == 2
+            // same, line by line: four lanes per voice, lane part p takes the 128-byte lines p, p + 4, ... of its voice's window
+            for (int vb = 0; vb < V; vb += 8) {
+                const int pv = vb + (lane >> 2);
+                if (pv < V && ((toStage >> pv) & 1u)) {
+                    const int4 q = reinterpret_cast<const int4*>(&sDesc[warp][pv])[1];       // p0b = window address, Rb = (base, bytes)
+                    const int o = (lane & 3) * 128;
+                    const char* a = reinterpret_cast<const char*>(((uint64_t) (uint32_t) q.y << 32) | (uint32_t) q.x) + o;
+#pragma unroll
+                    for (int k = 0; k < kSlotBytes / 512; ++k)
+                        if (o + k * 512 < q.z) asm volatile("prefetch.global.L2 [%0];" :: "l"(a + k * 512) : "memory");
+                }
+            }
+#endif
         }
         for (;;) {
             if (STAGED) { if (!act) break; vs = __ffs(act) - 1; act &= act - 1; }   // silent voices are never visited
@@ -801,7 +854,7 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
                 float vmax = 0.0f;
 #pragma unroll
                 for (int gi = 0; gi < kNG; ++gi)
-                    vmax = fmaxf(vmax, gather_finish_ring<JMODE, Q1>(d, g, win, laneD, laneF, nz, gi * kG * 32, acc + gi * kG));
+                    vmax = fmaxf(vmax, gather_finish_ring<JMODE, Q1>(d, g, win, laneD, laneF, nz, pm1, gi * kG * 32, acc + gi * kG));
                 take_peak(vmax, vs, g.nch);
                 __syncwarp();                                 // every lane is done with the slot before it is staged again
                 continue;
@@ -814,7 +867,7 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
                 Taps tp;
                 if ((d.nrend & kSimpleBit) && nr >= c0 + kG * 32) {
                     gather_issue_simple<true>(d, g, lane, laneD, laneF, c0, tp);
-                    vmax = fmaxf(vmax, gather_finish<JMODE, Q1, true>(g, tp, kG, nz, acc + gi * kG));
+                    vmax = fmaxf(vmax, gather_finish<JMODE, Q1, true>(g, tp, kG, nz, pm1, acc + gi * kG));
                 } else {
                     const int nchunks = min(kG, (min(n, nr) - c0 + 31) >> 5);
                     if (d.nrend & kSimpleBit) gather_issue_simple<false>(d, g, lane, laneD, laneF, c0, tp);
@@ -822,7 +875,7 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
                         const size_t vt = (size_t) t * P.nVoices + v0 + vs;
                         gather_issue<JMODE>(d, g, P.te + vt * kT, P.ps + vt * kT, lane, nchunks, c0, tp);
                     }
-                    vmax = fmaxf(vmax, gather_finish<JMODE, Q1, false>(g, tp, nchunks, nz, acc + gi * kG));
+                    vmax = fmaxf(vmax, gather_finish<JMODE, Q1, false>(g, tp, nchunks, nz, pm1, acc + gi * kG));
                 }
             }
             take_peak(vmax, vs, g.nch);
