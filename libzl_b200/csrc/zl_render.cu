@@ -67,6 +67,10 @@ constexpr int kSlots = ZL_SLOTS;             // staging slots per warp: kSlots -
 #ifndef ZL_L2PF
 #define ZL_L2PF 0
 #endif
+// The window queue runs across tile boundaries: the next tile's first window is staged while the last one of this tile is gathered.
+#ifndef ZL_PRESTAGE
+#define ZL_PRESTAGE 1
+#endif
 constexpr int kWantPeak = 1 << 8;     // VoiceGather.nch flag: the positions model takes this block's peak  :265-267
 
 // The gather of one voice x one tile is split in two so all of the tile's loads are in flight together:
@@ -641,6 +645,15 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         "ZL_DONE:\n"
         "}" :: "r"(bar), "r"(parity) : "memory");
 }
+__device__ __forceinline__ void stage_window_tma_raw(uint64_t src, uint32_t bytes, uint32_t slot, uint32_t bar) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "@p mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n"
+        "@p cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%2], [%3], %1, [%0];\n"
+        "}" :: "r"(bar), "r"(bytes), "r"(slot), "l"(src) : "memory");
+}
 __device__ __forceinline__ void stage_window_tma(const TileDesc& d, int lane, uint32_t slot, uint32_t bar) {
     // Every lane holds the same descriptor (a shared-memory broadcast), so the operands are warp-uniform and the issuing
     // lane is picked by elect.sync inside the warp-convergent code: ptxas then feeds UBLKCP from uniform registers directly
@@ -744,6 +757,7 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
         if (lane < V * 2) reinterpret_cast<int4*>(sVg[warp])[lane] = __ldg(reinterpret_cast<const int4*>(P.vgs + v0) + lane);
     }
 
+    int preV = -1;                                            // ZL_TMA: voice of THIS tile whose window the previous tile already staged
     for (int t = 0; t < P.tilesPerBlock; ++t) {
         const int t0 = t * kT;
         const int n = min(kT, nframes - t0);
@@ -787,6 +801,10 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
         uint32_t wrSlot = slot0;
         int rdOff = 0;
 #endif
+#if ZL_TMA && ZL_PRESTAGE
+        int nextV = -1;                                       // voice of the NEXT tile staged from this one (-1: not yet / none)
+        bool mayPre = t + 1 < P.tilesPerBlock;
+#endif
         auto stage_next = [&]() {
             if (toStage) {
                 const TileDesc& sd = sDesc[warp][__ffs(toStage) - 1];
@@ -799,6 +817,24 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
                 wrSlot = wrSlot == slot0 + (kSlots - 1) * kSlotBytes ? slot0 : wrSlot + kSlotBytes;
 #endif
             }
+#if ZL_TMA && ZL_PRESTAGE
+            else if (mayPre) {
+                // Nothing of this tile is left to stage and a slot is free: the queue runs on into the NEXT tile, whose
+                // descriptors already travel in nx0 (lane 4 v + q holds quad q of voice v, v < 8) - its first window-staged
+                // voice starts its way here, one voice-tile and an epilogue ahead, instead of being waited for at the tile start.
+                mayPre = false;
+                const bool ring = (lane & 3) == 3 && lane < V * 4 && (nx0.w & kCountMask) != 0 && (nx0.w & kRingBit) != 0;
+                const unsigned m = __ballot_sync(FULL, ring);
+                if (m) {
+                    const int src = __ffs(m) - 3;             // lane 4 v + 1: quad 1 = (p0b, Rb) = window address, (bytes | base)
+                    const uint32_t alo = (uint32_t) __shfl_sync(FULL, nx0.x, src), ahi = (uint32_t) __shfl_sync(FULL, nx0.y, src);
+                    const uint32_t bytes = (uint32_t) __shfl_sync(FULL, nx0.z, src);
+                    stage_window_tma_raw(((uint64_t) ahi << 32) | alo, bytes, slot0 + wrIdx * kSlotBytes, bar0 + 8 * wrIdx);
+                    wrIdx = wrIdx == kSlots - 1 ? 0 : wrIdx + 1;
+                    nextV = src >> 2;
+                }
+            }
+#endif
 #if !ZL_TMA
             cp_async_commit();
 #endif
@@ -807,8 +843,14 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
             const int fl = lane < V ? sDesc[warp][lane].nrend : 0;
             act = __ballot_sync(FULL, (fl & kCountMask) != 0);
             toStage = __ballot_sync(FULL, (fl & kCountMask) != 0 && (fl & kRingBit) != 0);
+            bool prime = true;
+#if ZL_TMA && ZL_PRESTAGE
+            if (preV >= 0) { toStage &= ~(1u << preV); prime = false; }   // already on its way (or landed): the queue is one ahead
+#endif
+            if (prime) {
 #pragma unroll
-            for (int k = 0; k < kSlots - 1; ++k) stage_next();
+                for (int k = 0; k < kSlots - 1; ++k) stage_next();
+            }
 #if ZL_L2PF == 1
             // the windows that will be staged later in this tile start their way from DRAM to L2 now (one bulk prefetch each)
             for (unsigned m = toStage; m; m &= m - 1) {
@@ -880,6 +922,9 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
             }
             take_peak(vmax, vs, g.nch);
         }
+#if ZL_TMA && ZL_PRESTAGE
+        preV = nextV;
+#endif
         // raw SamplerChannel ports, then JackPassthrough and the meters on the register accumulators
 #pragma unroll
         for (int ch = 0; ch < kNC; ++ch) {
