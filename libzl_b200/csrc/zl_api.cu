@@ -24,6 +24,7 @@
 
 namespace zl {
 cudaError_t launch_plan(RenderParams& P, cudaStream_t stream);
+void render_dump_trace(const char* path);   // diagnostic builds (-DZL_CTA_TRACE=1) only; a no-op otherwise
 #ifndef ZL_PLAN_CTAS_PER_SM
 #define ZL_PLAN_CTAS_PER_SM 0      // plan_kernel CTAs per SM beside a running gather (0 = whole grid)
 #endif
@@ -438,6 +439,7 @@ int zl_ctx_destroy(zl_ctx* ctx) {
     }
     if (!ctx) return ZL_ERR_INVALID;
     cudaSetDevice(ctx->device);
+    if (const char* tr = getenv("ZL_B200_CTA_TRACE")) render_dump_trace(tr);
     for (cudaStream_t s : {ctx->stream, ctx->own, ctx->planStream, ctx->mixStream, ctx->copyStream})   // nothing may still run on a buffer freed below
         if (s) cudaStreamSynchronize(s);
     if (ctx->comm) { nccl_destroy_comm(ctx->comm); ctx->comm = nullptr; }

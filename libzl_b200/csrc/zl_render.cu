@@ -21,6 +21,7 @@
 //                  stores.  No shared memory, no barriers; small enough to stay in the instruction cache and to run at
 //                  high occupancy, which is what hides the HBM latency of the gather.
 //   master_mix_kernel  the JACK port mix of each session's dry outputs (the only cross-bus step), once per launch.
+#include <cstdio>
 #include <cstdlib>
 
 #include "zl_voice.cuh"
@@ -41,6 +42,23 @@ namespace zl {
 #define ZL_GATHER_MINB 28
 #endif
 #define ZL_LAUNCH(kernel, grid, block, stream, ...) kernel<<<grid, block, 0, stream>>>(__VA_ARGS__)
+
+// Diagnostic build only (-DZL_CTA_TRACE=1, never shipped): every CTA of gather_kernel of period 8 and of plan_kernel /
+// walk_kernel of period 9 (which run beside it) leaves (SM id, clock64 at entry, clock64 at exit); render_dump_trace writes the
+// table of the last render to a file.  profiles/r02/cta_trace.py turns it into resident-CTA counts per SM over time.
+#ifndef ZL_CTA_TRACE
+#define ZL_CTA_TRACE 0
+#endif
+#if ZL_CTA_TRACE
+constexpr int kTraceMax = 70000;
+__device__ unsigned long long g_trace[3][kTraceMax][3];
+__device__ __forceinline__ unsigned trace_smid() { unsigned r; asm volatile("mov.u32 %0, %%smid;" : "=r"(r)); return r; }
+#define ZL_TRACE_BEGIN(cond) const bool trOn = (cond); long long trT0 = 0; if (trOn) trT0 = clock64();
+#define ZL_TRACE_END(kind) if (trOn && (threadIdx.x == 0) && blockIdx.x < kTraceMax) { g_trace[kind][blockIdx.x][0] = trace_smid(); g_trace[kind][blockIdx.x][1] = (unsigned long long) trT0; g_trace[kind][blockIdx.x][2] = (unsigned long long) clock64(); }
+#else
+#define ZL_TRACE_BEGIN(cond)
+#define ZL_TRACE_END(kind)
+#endif
 
 constexpr int kT = ZL_KT;            // frames per tile (multiple of 128)
 constexpr int kNC = kT / 32;         // 32-frame chunks per tile
@@ -308,18 +326,29 @@ __device__ __forceinline__ int plan_voice_block(const RenderParams& P, int vIdx,
             if (!JMODE && h.looping) fast = bc.beatAligned ? (bc.fWrap >= nframes && q < top) : (q < fmin(top, bc.stopD));
             else fast = q < fmin(top, bc.stopD) && (JMODE || q < bc.relStart);
             if (fast) {
+                // Tile t starts at p_(t kT) = h.p + t kT R and e_(t kT) = envE0 + t kT envE.  Both runs stay on one grid for the
+                // whole period, so every one of these values is representable and the running sums below ARE them: the
+                // same bits as fma(t0, R, h.p) / fmaf(t0, envE, envE0), without an int -> f64 conversion per tile.
+                double pT = h.p;
+                float eT = envE0;
+                const double RT = __dmul_rn(R, (double) kT);
+                const float ET = __fmul_rn(envE, (float) kT);
+                const int simple = bc.nch == 2 ? kSimpleBit : 0;
+                TileDesc* dst = P.descs + vIdx;
+                int left = nframes;
                 for (int t = 0; t < P.tilesPerBlock; ++t) {
-                    const int t0 = t * kT;
-                    const int n = min(kT, nframes - t0);
+                    const int n = min(kT, left);
                     TileDesc d;
-                    d.p0a = __fma_rn((double) t0, R, h.p); d.Ra = R; d.p0b = 0.0; d.Rb = 0.0;
-                    d.e0a = __fmaf_rn((float) t0, envE, envE0); d.Ea = envE; d.e0b = 0.0f; d.Eb = 0.0f;   // exact: the run stays on one grid
+                    d.p0a = pT; d.Ra = R; d.p0b = 0.0; d.Rb = 0.0;
+                    d.e0a = eT; d.Ea = envE; d.e0b = 0.0f; d.Eb = 0.0f;
                     d.cb = n; d.ce = n; d.ct = INT_MAX;
-                    const int lastPos = (int) __fma_rn((double) (t0 + n - 1), R, h.p);
-                    d.nrend = n | ((bc.nch == 2 && (JMODE || lastPos < sampleDuration)) ? kSimpleBit : 0);
+                    const int lastPos = (int) __fma_rn(n == kT ? (double) (kT - 1) : (double) (n - 1), R, pT);
+                    d.nrend = n | ((JMODE || lastPos < sampleDuration) ? simple : 0);
                     mark_ring(d, g.data, sampleDuration, n, lastPos);
-                    P.descs[(size_t) t * P.nVoices + vIdx] = d;
+                    *dst = d;
                     bc.lastPos = lastPos;
+                    dst += P.nVoices; left -= kT;
+                    pT = __dadd_rn(pT, RT); eT = __fadd_rn(eT, ET);       // not used after the last tile
                 }
                 h.p = q; h.env = envLast;
                 nrendBlock = nframes;
@@ -477,6 +506,7 @@ __global__ void __launch_bounds__(MAXT, MAXT == 128 ? ZL_PLAN_MINB : 1) plan_ker
     const int tid = threadIdx.x;
     const int lb = tid / V, slot = tid - lb * V;              // bus within the CTA, voice slot within the bus
     const int blk = P.blk;
+    ZL_TRACE_BEGIN(P.blk == 9)
     const unsigned FULL = 0xffffffffu;
     unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
     // grid-stride over the bus groups: beside a running gather the grid is capped (launch_plan) so that the planner
@@ -526,6 +556,7 @@ __global__ void __launch_bounds__(MAXT, MAXT == 128 ? ZL_PLAN_MINB : 1) plan_ker
         atomicAdd(P.voiceFrames, nVoiceFrames); atomicAdd(P.voiceFrames + 1, nSrcFloats);
         atomicAdd(P.voiceFrames + 2, nVoiceFrames); atomicAdd(P.voiceFrames + 3, nSrcFloats);
     }
+    ZL_TRACE_END(1)
 }
 
 
@@ -538,6 +569,7 @@ template <bool JMODE, bool Q3>
 __global__ void __launch_bounds__(32, ZL_WALK_MINB) walk_kernel(const RenderParams P) {
     const unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x;
+    ZL_TRACE_BEGIN(P.blk == 9)
     const int cA = P.walkCount[2 * P.blk], cB = P.walkCount[2 * P.blk + 1];
     const int wA = (cA + 31) >> 5, wB = (cB + 31) >> 5;
     unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
@@ -581,6 +613,7 @@ __global__ void __launch_bounds__(32, ZL_WALK_MINB) walk_kernel(const RenderPara
         atomicAdd(P.voiceFrames, nVoiceFrames); atomicAdd(P.voiceFrames + 1, nSrcFloats);
         atomicAdd(P.voiceFrames + 2, nVoiceFrames); atomicAdd(P.voiceFrames + 3, nSrcFloats);
     }
+    ZL_TRACE_END(2)
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -717,6 +750,7 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
     const uint32_t slot0 = (uint32_t) __cvta_generic_to_shared(&sWin[warp][0][0]);
     const int gbw = blockIdx.x * W + (threadIdx.x >> 5);      // global bus
     if (gbw >= P.nSessions * P.B) return;
+    ZL_TRACE_BEGIN(P.blk == 8)
     const unsigned FULL = 0xffffffffu;
     const int V = P.V, nframes = P.nframes, blk = P.blk;
     const double laneD = (double) lane;
@@ -983,6 +1017,7 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
         }
         if (lane == 0) { P.sumsq[idx] = sqL; P.sumsq[idx + 1] = sqR; }
     }
+    ZL_TRACE_END(0)
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1123,6 +1158,22 @@ __global__ void __launch_bounds__(32, 1) spin_mem_kernel(const RenderParams P, i
 // One block (P.blk) of every session: launch_plan (plan_kernel + walk_kernel), then launch_gather.  The two may sit on
 // different streams (zl_api.cu orders them with events and double-buffers the hand-over), so that the latency-bound
 // planner of period b + 1 fills the issue slots the gather of period b leaves idle.
+#if ZL_CTA_TRACE
+void render_dump_trace(const char* path) {
+    static unsigned long long h[3][kTraceMax][3];
+    cudaDeviceSynchronize();
+    if (cudaMemcpyFromSymbol(h, g_trace, sizeof h) != cudaSuccess) return;
+    FILE* f = fopen(path, "w");
+    if (!f) return;
+    for (int k = 0; k < 3; ++k)
+        for (int i = 0; i < kTraceMax; ++i)
+            if (h[k][i][2]) fprintf(f, "%d %d %llu %llu %llu\n", k, i, h[k][i][0], h[k][i][1], h[k][i][2]);
+    fclose(f);
+}
+#else
+void render_dump_trace(const char*) {}
+#endif
+
 cudaError_t launch_plan(RenderParams& P, cudaStream_t stream) {
     const int V = P.V, nBuses = P.nSessions * P.B;
     if (V < 1 || V > 1024) return cudaErrorInvalidValue;
