@@ -60,6 +60,20 @@ __device__ __forceinline__ unsigned trace_smid() { unsigned r; asm volatile("mov
 #define ZL_TRACE_END(kind)
 #endif
 
+// Diagnostic build only (-DZL_BOUNDS_CHECK=1, never shipped; compute-sanitizer is closed on this pool): every address the render
+// kernels form from planner data is tested against the object it must stay in - source taps against the clip's length + 8
+// frames, staged windows against the clip and the slot, table rows against the tile, queue slots against the queue, output
+// indices against the period - and violations are counted per site; render_dump_trace prints the counters.
+#ifndef ZL_BOUNDS_CHECK
+#define ZL_BOUNDS_CHECK 0
+#endif
+#if ZL_BOUNDS_CHECK
+__device__ unsigned long long g_bounds[16];                   // [0] checks made, [k] violations at site k
+#define ZL_CHECK(site, cond) do { atomicAdd(&g_bounds[0], 1ull); if (!(cond)) atomicAdd(&g_bounds[site], 1ull); } while (0)
+#else
+#define ZL_CHECK(site, cond)
+#endif
+
 constexpr int kT = ZL_KT;            // frames per tile (multiple of 128)
 constexpr int kNC = kT / 32;         // 32-frame chunks per tile
 constexpr int kG = 4;                // chunks gathered together (all their loads in flight at once); a tile is kNG such groups
@@ -120,6 +134,7 @@ __device__ __forceinline__ void gather_issue(const TileDesc& d, const VoiceGathe
             const int c = c0 + ch * 32 + lane;
             const bool v = c < nrend;
             double p;
+            ZL_CHECK(1, c >= 0 && c < kT);
             if (slotPos) p = v ? psrow[c] : 0.0;
             else {
                 const bool sb = c >= d.cb;
@@ -135,6 +150,7 @@ __device__ __forceinline__ void gather_issue(const TileDesc& d, const VoiceGathe
             t.env[ch] = env;
             const bool inR = v && (JMODE || g.sampleDuration > pos);      // Z: taps outside the sample read as 0  (:204-205)
             if (inR) {
+                ZL_CHECK(2, pos >= 0 && pos + 1 <= g.sampleDuration + 8);   // frames 0 .. length + 7 exist (sampleDuration = length - 1)
                 if (nch > 1) {
                     t.a[ch] = __ldg(reinterpret_cast<const float2*>(g.data) + pos);
                     t.b[ch] = __ldg(reinterpret_cast<const float2*>(g.data) + pos + 1);
@@ -160,6 +176,7 @@ __device__ __forceinline__ void gather_issue_simple(const TileDesc& d, const Voi
         const double p = __fma_rn(__dadd_rn(laneD, (double) (c0 + ch * 32)), d.Ra, d.p0a);
         int pos = split_pos(p, t.alpha[ch]);
         if (!FULL) pos = (c0 + ch * 32 + lane < nrend) ? pos : zeroPos;
+        ZL_CHECK(3, pos >= 0 && pos + 1 <= g.sampleDuration + 8);
         t.a[ch] = __ldg(src + pos); t.b[ch] = __ldg(src + pos + 1);
     }
     if (d.Ea == 0.0f) {                                               // warp-uniform (sustain, J-mode idle)
@@ -544,6 +561,8 @@ __global__ void __launch_bounds__(MAXT, MAXT == 128 ? ZL_PLAN_MINB : 1) plan_ker
             if (mB) baseB = atomicAdd(P.walkCount + 2 * blk + 1, __popc(mB));
         }
         baseA = __shfl_sync(FULL, baseA, 0); baseB = __shfl_sync(FULL, baseB, 0);
+        ZL_CHECK(6, kind == 0 || (kind == 1 ? baseA + __popc(mA & lt) : P.nVoices - 1 - (baseB + __popc(mB & lt))) >= 0);
+        ZL_CHECK(6, kind == 0 || (kind == 1 ? baseA + __popc(mA & lt) : P.nVoices - 1 - (baseB + __popc(mB & lt))) < P.nVoices);
         if (kind == 1) P.walkQueue[baseA + __popc(mA & lt)] = vIdx;
         if (kind == 2) P.walkQueue[P.nVoices - 1 - (baseB + __popc(mB & lt))] = vIdx;
     }
@@ -575,6 +594,7 @@ __global__ void __launch_bounds__(32, ZL_WALK_MINB) walk_kernel(const RenderPara
     unsigned long long nVoiceFrames = 0, nSrcFloats = 0;
     for (int w = blockIdx.x; w < wA + wB; w += gridDim.x) {
         int vIdx = -1;
+        ZL_CHECK(7, cA >= 0 && cB >= 0 && cA + cB <= P.nVoices);
         if (w < wA) { const int i = w * 32 + tid; if (i < cA) vIdx = P.walkQueue[i]; }
         else { const int j = (w - wA) * 32 + tid; if (j < cB) vIdx = P.walkQueue[P.nVoices - 1 - j]; }
         // ZL_B200_WALK_PROF (profiling aid): cycles per queued voice by what it was doing when the period began -
@@ -694,6 +714,7 @@ __device__ __forceinline__ void stage_window_tma(const TileDesc& d, int lane, ui
     const uint64_t src = (uint64_t) __double_as_longlong(d.p0b);
     const uint32_t bytes = (uint32_t) __double2loint(d.Rb);              // whole 512-byte rows, 16-byte aligned source (mark_ring)
     (void) lane;
+    ZL_CHECK(5, (src & 15) == 0 && (bytes & 15) == 0 && bytes > 0 && bytes <= (uint32_t) kSlotBytes);
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
@@ -723,6 +744,7 @@ __device__ __forceinline__ float gather_finish_ring(const TileDesc& d, const Voi
     for (int ch = 0; ch < kG; ++ch) {
         if (ch) { p = __dadd_rn(p, R32); e = __fadd_rn(e, E32); }
         const int pos = split_pos(p, t.alpha[ch]);
+        ZL_CHECK(4, pos >= 0 && (pos + 2) * 8 <= __double2loint(d.Rb) && __double2loint(d.Rb) <= kSlotBytes);
         t.a[ch] = win[pos]; t.b[ch] = win[pos + 1];
         t.env[ch] = e;
     }
@@ -842,6 +864,14 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
         auto stage_next = [&]() {
             if (toStage) {
                 const TileDesc& sd = sDesc[warp][__ffs(toStage) - 1];
+#if ZL_BOUNDS_CHECK
+                {
+                    const VoiceGather& sg = sVg[warp][__ffs(toStage) - 1];
+                    const uintptr_t w0 = (uintptr_t) __double_as_longlong(sd.p0b), w1 = w0 + (uintptr_t) (uint32_t) __double2loint(sd.Rb);
+                    const uintptr_t c0 = reinterpret_cast<uintptr_t>(sg.data), c1 = c0 + (uintptr_t) (sg.sampleDuration + 9) * 8u;   // length + 8 stereo frames
+                    ZL_CHECK(9, w0 >= c0 && w1 <= c1 && (sg.nch & 0xff) == 2);
+                }
+#endif
                 toStage &= toStage - 1;
 #if ZL_TMA
                 stage_window_tma(sd, lane, slot0 + wrIdx * kSlotBytes, bar0 + 8 * wrIdx);
@@ -967,12 +997,14 @@ __global__ void __launch_bounds__(ZL_GATHER_THREADS, ZL_GATHER_MINB) gather_kern
             if (LEAN) {
                 if (c < n && j < nframes) {
                     float dL, dR;
+                    ZL_CHECK(8, t0 + c + QS >= 0 && t0 + c + QS < nframes && off + nframes <= P.stride);
                     if (out0L) { out0L[t0 + c] = acc[ch].x; out0R[t0 + c] = acc[ch].y; }
                     passthrough_pair(pt, pt.dry_amount, acc[ch].x, acc[ch].y, dL, dR);
                     pkL = max(pkL, peak_int(dL)); pkR = max(pkR, peak_int(dR));
                 }
             } else if (c < n && j < nframes) {
                 float dL, dR;
+                ZL_CHECK(8, j >= 0 && j < nframes && off + nframes <= P.stride);
                 if (P.out[0]) { P.out[0][rowL + j] = acc[ch].x; P.out[0][rowR + j] = acc[ch].y; }
                 passthrough_pair(pt, pt.dry_amount, acc[ch].x, acc[ch].y, dL, dR);
                 if (P.out[1]) { P.out[1][rowL + j] = dL; P.out[1][rowR + j] = dR; }
@@ -1158,7 +1190,18 @@ __global__ void __launch_bounds__(32, 1) spin_mem_kernel(const RenderParams P, i
 // One block (P.blk) of every session: launch_plan (plan_kernel + walk_kernel), then launch_gather.  The two may sit on
 // different streams (zl_api.cu orders them with events and double-buffers the hand-over), so that the latency-bound
 // planner of period b + 1 fills the issue slots the gather of period b leaves idle.
-#if ZL_CTA_TRACE
+#if ZL_BOUNDS_CHECK
+void render_dump_trace(const char* path) {
+    unsigned long long h[16] = {0};
+    cudaDeviceSynchronize();
+    if (cudaMemcpyFromSymbol(h, g_bounds, sizeof h) != cudaSuccess) return;
+    FILE* f = fopen(path, "a");
+    if (!f) return;
+    fprintf(f, "bounds checks %llu; violations: table row %llu, tap (generic) %llu, tap (simple) %llu, tap (staged window) %llu, window size/alignment %llu, "
+               "queue write %llu, queue length %llu, output index %llu, window vs clip %llu\n", h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7], h[8], h[9]);
+    fclose(f);
+}
+#elif ZL_CTA_TRACE
 void render_dump_trace(const char* path) {
     static unsigned long long h[3][kTraceMax][3];
     cudaDeviceSynchronize();
