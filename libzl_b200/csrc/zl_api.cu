@@ -26,7 +26,7 @@ namespace zl {
 cudaError_t launch_plan(RenderParams& P, cudaStream_t stream);
 void render_dump_trace(const char* path);   // diagnostic builds (-DZL_CTA_TRACE=1) only; a no-op otherwise
 #ifndef ZL_PLAN_CTAS_PER_SM
-#define ZL_PLAN_CTAS_PER_SM 0      // plan_kernel CTAs per SM beside a running gather (0 = whole grid)
+#define ZL_PLAN_CTAS_PER_SM 12     // plan_kernel CTAs per SM beside a running gather (0 = whole grid): a persistent grid that fills the SMs once (80 registers x 64 threads: 12 fit) and strides over the bus groups saves the dispatch of 8192 short CTAs (batch49, A/B on one box: 11.26 -> 11.17 ms per step; within the run-to-run spread across boxes)
 #endif
 #ifndef ZL_WALK_CTAS_PER_SM
 #define ZL_WALK_CTAS_PER_SM 0      // walk_kernel one-warp CTAs per SM beside a running gather (0 = default grid)
